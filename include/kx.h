@@ -1,0 +1,96 @@
+/*
+ * kx.h -- C ABI of libkx_b200.so, the B200 (sm_100a) implementation of the hot
+ * path of mrankitvish/ai-agent-kubectl.
+ *
+ * The reference's own boundary for this path is Python-level (a LangChain
+ * Runnable in the `llm` slot of `template | llm | KubectlOutputParser()`,
+ * app.py:118); it has no FFI.  This header is what a binding of that path would
+ * load: plain pointers and sizes, no torch types.  INTEGRATION.md shows the
+ * ctypes stub a maintainer of the reference would add.
+ *
+ * Conventions: every function returns 0 on success and a negative KX_E* code on
+ * failure; kx_last_error() returns a thread-local message for the last failure.
+ * Pointers named d_* are device pointers on the current CUDA device, h_* are host
+ * pointers.  `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ * Device entry points only enqueue work; they do not synchronise.
+ */
+#ifndef KX_H_
+#define KX_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KX_OK            0
+#define KX_EINVAL       -1   /* bad argument */
+#define KX_ECUDA        -2   /* a CUDA runtime call failed */
+#define KX_ENOMEM       -3
+#define KX_ETOOBIG      -4   /* exceeds a stated limit */
+
+const char *kx_last_error(void);
+int kx_version(void);
+
+/* ------------------------------------------------------------------------- *
+ * String path: validator + parser + sanitiser + cache-key hash
+ * ------------------------------------------------------------------------- */
+
+/* verdict codes: why is_safe_kubectl_command (app.py:72-88) returns False */
+#define KX_SAFE          0   /* the reference returns True                        */
+#define KX_BAD_PREFIX    1   /* app.py:75-77  does not start with "kubectl "      */
+#define KX_METACHAR      2   /* app.py:79-81  ; && || ` $ ( ) < >                 */
+#define KX_BAD_QUOTING   3   /* app.py:83-87  shlex.split raised ValueError       */
+
+/* flags */
+#define KX_FLAG_PARSE    1u  /* validate as KubectlOutputParser.parse does
+                                (app.py:95-104): strip, drop a ```...``` fence,
+                                strip again, then validate                        */
+
+/*
+ * kx_validate_hash -- batched replacement for, per string s of a CSR batch:
+ *     verdict[i]  = reason code of is_safe_kubectl_command(s)       app.py:72-88
+ *                   (with KX_FLAG_PARSE: of the command parse() would validate,
+ *                    app.py:95-104)
+ *     span[2i..]  = byte range [begin,end) inside s of that command (what
+ *                   parse() returns when verdict is KX_SAFE)
+ *     hash[i]     = hash(sanitize_query(s)) as CPython computes it with
+ *                   PYTHONHASHSEED=0 -- the key hash TTLCache's dict uses for
+ *                   cache.get / cache[...] at app.py:312,322 (sanitize_query is
+ *                   app.py:60-68)
+ *     san, san_len= sanitize_query(s) itself, UTF-8, written at d_san + off[i]
+ *                   (never longer than s), and its byte length
+ * d_data holds the UTF-8 bytes of all strings back to back; string i is
+ * d_data[d_off[i] .. d_off[i+1]).  d_off has n+1 entries, d_off[0] need not be 0.
+ * Any of the five output pointers may be NULL to skip that output.  Strings must
+ * be shorter than 2^31-16 bytes.  Input that is not valid UTF-8 is processed by
+ * a fixed, documented rule rather than rejected.
+ * The kernel reads d_data in aligned 16-byte units, so the bytes up to the next
+ * 16-byte boundary after the last string must be readable (true of any CUDA
+ * allocation).
+ */
+int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32_t flags,
+                     uint8_t *d_verdict, int64_t *d_hash, int32_t *d_span,
+                     uint8_t *d_san, int32_t *d_san_len, void *stream);
+
+/*
+ * kx_validate_hash_host -- same contract with HOST buffers: copies the batch to
+ * `device` in chunks over two streams (copy of chunk k+1 overlaps the kernel on
+ * chunk k), runs kx_validate_hash and copies the requested outputs back.
+ * Blocks until the outputs are in host memory.  This is the call a Python
+ * binding of the reference would make with the strings it already holds
+ * (app.py:102 and app.py:305,312).  Staging buffers are cached per device and
+ * released by kx_release_host_staging().  h_off[0] must be 0.
+ */
+int kx_validate_hash_host(const uint8_t *h_data, const int64_t *h_off, int64_t n, uint32_t flags,
+                          uint8_t *h_verdict, int64_t *h_hash, int32_t *h_span,
+                          uint8_t *h_san, int32_t *h_san_len, int device);
+void kx_release_host_staging(void);
+
+/* number of kernels this library has launched in this process (for bench.py) */
+int64_t kx_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KX_H_ */
