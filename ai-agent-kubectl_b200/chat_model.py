@@ -1,0 +1,323 @@
+"""Drop-in occupant of the reference's ``llm`` slot.
+
+The reference builds ``chain = template | llm | KubectlOutputParser()`` with
+``llm = ChatOpenAI(temperature=0, api_key=..., model=..., request_timeout=...,
+[base_url=...])`` (app.py:108-118) and awaits ``chain.ainvoke({"query": q})`` under
+``asyncio.wait_for`` (app.py:183-186).  ``B200ChatModel`` takes exactly those
+keyword arguments and speaks the LangChain Runnable protocol
+(``invoke / ainvoke / batch / abatch / |``), so the unmodified ``app.py`` can use it
+(INTEGRATION.md).  ``api_key`` and ``base_url`` are accepted and ignored; ``model``
+selects the architecture; ``request_timeout`` is a per-request deadline.
+
+Many ``ainvoke`` coroutines run on one event loop (one per in-flight HTTP request,
+app.py:299).  They are batched: each call enqueues (prompt, future) and a single
+engine thread drains the queue into ``engine.generate(list_of_prompts)`` and
+resolves the futures with ``loop.call_soon_threadsafe``.  When ``wait_for`` times
+out it cancels the awaiting task (-> HTTP 504, app.py:189-191); the request is then
+marked cancelled, dropped before scheduling, and the engine is told so it can free
+that request's KV pages.
+
+Error contract (app.py:189-197): ``ValueError`` is reserved for the parser (-> 422),
+so engine failures surface as ``RuntimeError`` (-> 500 with str(e) in the detail).
+"""
+from __future__ import annotations
+
+import asyncio
+import logging
+import queue
+import threading
+import time
+from concurrent.futures import Future
+from typing import Any, Callable, List, Optional, Sequence
+
+logger = logging.getLogger(__name__)
+
+try:  # real LangChain, if the deployment has it (it is not in this image)
+    from langchain_core.runnables import Runnable as _LCRunnable  # type: ignore
+    from langchain_core.messages import AIMessage as _AIMessage  # type: ignore
+    _HAVE_LANGCHAIN = True
+except Exception:  # noqa: BLE001
+    _LCRunnable = object
+    _AIMessage = None
+    _HAVE_LANGCHAIN = False
+
+
+class Message:
+    """Minimal chat message (what ``StrOutputParser`` reads: ``.content``)."""
+
+    def __init__(self, content: str, response_metadata: Optional[dict] = None):
+        self.content = content
+        self.type = "ai"
+        self.response_metadata = response_metadata or {}
+
+    def __repr__(self):
+        return f"Message(content={self.content!r})"
+
+
+def _make_message(text: str, meta: dict):
+    if _HAVE_LANGCHAIN:
+        return _AIMessage(content=text, response_metadata=meta)
+    return Message(text, meta)
+
+
+def prompt_to_text(value: Any) -> str:
+    """Accepts what a Runnable in the ``llm`` position can receive: a prompt value
+    (``to_string()``), a plain ``str``, or a list of messages."""
+    if isinstance(value, str):
+        return value
+    if hasattr(value, "to_string"):
+        return value.to_string()
+    if isinstance(value, (list, tuple)):
+        return "\n".join(prompt_to_text(getattr(m, "content", m)) for m in value)
+    if hasattr(value, "content"):
+        return str(value.content)
+    return str(value)
+
+
+class _Sequence:
+    """``a | b`` when LangChain's own RunnableSequence is not available."""
+
+    def __init__(self, *steps):
+        self.steps = []
+        for s in steps:
+            self.steps.extend(s.steps if isinstance(s, _Sequence) else [s])
+
+    def __or__(self, other):
+        return _Sequence(self, other)
+
+    def __ror__(self, other):
+        return _Sequence(other, self)
+
+    def invoke(self, value, config=None, **kw):
+        for s in self.steps:
+            value = s.invoke(value, config) if hasattr(s, "invoke") else s(value)
+        return value
+
+    async def ainvoke(self, value, config=None, **kw):
+        for s in self.steps:
+            if hasattr(s, "ainvoke"):
+                value = await s.ainvoke(value, config)
+            elif hasattr(s, "invoke"):
+                value = s.invoke(value, config)
+            else:
+                value = s(value)
+        return value
+
+    def batch(self, values, config=None, **kw):
+        values = list(values)
+        for s in self.steps:
+            values = s.batch(values, config) if hasattr(s, "batch") else [s.invoke(v, config) for v in values]
+        return values
+
+    async def abatch(self, values, config=None, **kw):
+        return list(await asyncio.gather(*(self.ainvoke(v, config) for v in values)))
+
+
+class Engine:
+    """What the chat model drives.  ``generate`` maps prompts to completions for one
+    batch; ``cancel`` is advisory (a request that no longer has a waiter)."""
+
+    max_batch = 64
+
+    def generate(self, prompts: Sequence[str], cancelled: Optional[Sequence[Callable[[], bool]]] = None) -> List[str]:
+        raise NotImplementedError
+
+    def close(self) -> None:
+        pass
+
+
+class CallableEngine(Engine):
+    """Engine from a plain function prompt -> completion (stub LLM of config 1)."""
+
+    def __init__(self, fn: Callable[[str], str], max_batch: int = 64):
+        self.fn, self.max_batch, self.batches = fn, max_batch, []
+
+    def generate(self, prompts, cancelled=None):
+        self.batches.append(len(prompts))
+        return [self.fn(p) for p in prompts]
+
+
+class _Request:
+    __slots__ = ("prompt", "future", "loop", "afuture", "deadline", "t_enqueue")
+
+    def __init__(self, prompt, deadline):
+        self.prompt, self.deadline = prompt, deadline
+        self.future: Future = Future()
+        self.loop = None
+        self.afuture = None
+        self.t_enqueue = time.monotonic()
+
+    def cancelled(self) -> bool:
+        if self.afuture is not None and self.afuture.cancelled():
+            return True
+        if self.future.cancelled():
+            return True
+        return self.deadline is not None and time.monotonic() > self.deadline
+
+
+class BatchingFrontend:
+    """Single consumer thread that turns concurrent requests into engine batches."""
+
+    def __init__(self, engine: Engine, max_wait_ms: float = 2.0):
+        self.engine, self.max_wait = engine, max_wait_ms / 1e3
+        self.q: "queue.Queue[Optional[_Request]]" = queue.Queue()
+        self.dropped = 0
+        self._thr = threading.Thread(target=self._run, name="kx-engine", daemon=True)
+        self._thr.start()
+
+    def submit(self, req: _Request) -> None:
+        self.q.put(req)
+
+    def close(self):
+        self.q.put(None)
+        self._thr.join(timeout=5)
+        self.engine.close()
+
+    def _resolve(self, req: _Request, result=None, exc: Optional[BaseException] = None):
+        def set_async():
+            if req.afuture.done():
+                return
+            if exc is not None:
+                req.afuture.set_exception(exc)
+            else:
+                req.afuture.set_result(result)
+
+        if req.afuture is not None:
+            req.loop.call_soon_threadsafe(set_async)
+        elif not req.future.done():
+            if exc is not None:
+                req.future.set_exception(exc)
+            else:
+                req.future.set_result(result)
+
+    def _run(self):
+        while True:
+            first = self.q.get()
+            if first is None:
+                return
+            batch = [first]
+            t_end = time.monotonic() + self.max_wait
+            while len(batch) < self.engine.max_batch:
+                try:
+                    nxt = self.q.get(timeout=max(0.0, t_end - time.monotonic()))
+                except queue.Empty:
+                    break
+                if nxt is None:
+                    self.q.put(None)
+                    break
+                batch.append(nxt)
+            live = []
+            for r in batch:
+                if r.cancelled():
+                    self.dropped += 1
+                    self._resolve(r, exc=TimeoutError("request cancelled before it was scheduled"))
+                else:
+                    live.append(r)
+            if not live:
+                continue
+            try:
+                outs = self.engine.generate([r.prompt for r in live], [r.cancelled for r in live])
+                if len(outs) != len(live):
+                    raise RuntimeError(f"engine returned {len(outs)} completions for {len(live)} prompts")
+                for r, o in zip(live, outs):
+                    self._resolve(r, result=o)
+            except BaseException as e:  # noqa: BLE001 - surfaced to every waiter as a 500
+                err = e if isinstance(e, RuntimeError) else RuntimeError(f"{type(e).__name__}: {e}")
+                for r in live:
+                    self._resolve(r, exc=err)
+
+
+#: names the ``model`` kwarg / OPENAI_MODEL may carry -> architecture key
+ARCH_ALIASES = {
+    "qwen2.5-0.5b": "qwen2.5-0.5b", "qwen/qwen2.5-0.5b": "qwen2.5-0.5b", "qwen2.5-0.5b-instruct": "qwen2.5-0.5b",
+    "llama-3.2-1b": "llama-3.2-1b", "meta-llama/llama-3.2-1b": "llama-3.2-1b",
+    "llama-3.1-8b": "llama-3.1-8b", "meta-llama/llama-3.1-8b": "llama-3.1-8b",
+}
+DEFAULT_ARCH = "qwen2.5-0.5b"
+
+
+def resolve_arch(model: Optional[str]) -> str:
+    key = (model or "").strip().lower()
+    if key in ARCH_ALIASES:
+        return ARCH_ALIASES[key]
+    logger.info("model %r is not a local architecture name; using %s", model, DEFAULT_ARCH)
+    return DEFAULT_ARCH
+
+
+class B200ChatModel(_LCRunnable):
+    """``ChatOpenAI``-compatible constructor, Runnable protocol, local generation."""
+
+    def __init__(self, temperature: float = 0, api_key: Optional[str] = None, model: Optional[str] = None,
+                 request_timeout: Optional[float] = None, base_url: Optional[str] = None, *,
+                 engine: Optional[Engine] = None, engine_factory: Optional[Callable[[str], Engine]] = None,
+                 max_wait_ms: float = 2.0, **ignored):
+        if temperature not in (0, 0.0, None):
+            raise ValueError("B200ChatModel decodes greedily; only temperature=0 is supported (app.py:109)")
+        self.temperature = 0
+        self.model_name = model
+        self.arch = resolve_arch(model)
+        self.request_timeout = request_timeout
+        self.base_url, self._api_key_ignored = base_url, api_key is not None
+        if engine is None:
+            if engine_factory is None:
+                from .engine import default_engine_factory  # the CUDA generator; raises if it cannot start
+                engine_factory = default_engine_factory
+            engine = engine_factory(self.arch)
+        self.engine = engine
+        self.frontend = BatchingFrontend(engine, max_wait_ms=max_wait_ms)
+
+    # ---- Runnable protocol -------------------------------------------------
+    def __or__(self, other):
+        if _HAVE_LANGCHAIN:
+            return super().__or__(other)
+        return _Sequence(self, other)
+
+    def __ror__(self, other):
+        if _HAVE_LANGCHAIN:
+            return super().__ror__(other)
+        return _Sequence(other, self)
+
+    def _request(self, value) -> _Request:
+        deadline = None if not self.request_timeout else time.monotonic() + float(self.request_timeout)
+        return _Request(prompt_to_text(value), deadline)
+
+    def _wrap(self, text: str):
+        return _make_message(text, {"model_name": self.arch, "finish_reason": "stop"})
+
+    def invoke(self, value, config=None, **kw):
+        req = self._request(value)
+        self.frontend.submit(req)
+        try:
+            return self._wrap(req.future.result(timeout=self.request_timeout or None))
+        except BaseException:
+            req.future.cancel()
+            raise
+
+    async def ainvoke(self, value, config=None, **kw):
+        req = self._request(value)
+        req.loop = asyncio.get_running_loop()
+        req.afuture = req.loop.create_future()
+        self.frontend.submit(req)
+        # CancelledError from asyncio.wait_for (app.py:183-186) cancels afuture, which
+        # the engine thread observes through req.cancelled().
+        return self._wrap(await req.afuture)
+
+    def batch(self, values, config=None, **kw):
+        reqs = [self._request(v) for v in values]
+        for r in reqs:
+            self.frontend.submit(r)
+        return [self._wrap(r.future.result(timeout=self.request_timeout or None)) for r in reqs]
+
+    async def abatch(self, values, config=None, **kw):
+        return list(await asyncio.gather(*(self.ainvoke(v, config) for v in values)))
+
+    def close(self):
+        self.frontend.close()
+
+    @property
+    def _llm_type(self) -> str:
+        return "b200-local"
+
+
+#: exported under the name the reference imports (app.py:11)
+ChatOpenAI = B200ChatModel

@@ -1,0 +1,27 @@
+// TEST INFRASTRUCTURE: runs the kernel's own per-string logic (csrc/k9_core.cuh,
+// written __host__ __device__) on the CPU so that logic errors are caught in the
+// CPU test suite before a GPU is involved.  Addressing mimics the kernel's
+// unstaged path (16-byte aligned word base + byte offset).
+#include <stdint.h>
+#include <string.h>
+#include <vector>
+#include "../../ai-agent-kubectl_b200/csrc/k9_core.cuh"
+
+extern "C" int k9_emul(const uint8_t *data, const int64_t *off, int64_t n, uint32_t flags, uint8_t *verdict,
+                       int64_t *hash, int32_t *span, uint8_t *san, int32_t *san_len) {
+    std::vector<uint32_t> buf;
+    for (int64_t s = 0; s < n; ++s) {
+        const int64_t len = off[s + 1] - off[s];
+        const int lead = (int)(s % 16);                       // exercise every misalignment
+        buf.assign((size_t)((lead + len + 15) / 16 * 4 + 4), 0xA5A5A5A5u);   // poison around the string
+        memcpy((uint8_t *)buf.data() + lead, data + off[s], (size_t)len);
+        k9::Result r = (flags & KX_FLAG_PARSE)
+            ? k9::process_string<true>(buf.data(), lead, lead + (int)len, hash != nullptr, san ? san + off[s] : nullptr)
+            : k9::process_string<false>(buf.data(), lead, lead + (int)len, hash != nullptr, san ? san + off[s] : nullptr);
+        if (hash) hash[s] = r.hash;
+        if (san_len) san_len[s] = r.san_len;
+        if (verdict) verdict[s] = (uint8_t)r.verdict;
+        if (span) { span[2 * s] = r.span_a; span[2 * s + 1] = r.span_b; }
+    }
+    return 0;
+}
