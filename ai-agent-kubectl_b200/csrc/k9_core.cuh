@@ -224,4 +224,141 @@ KX_HD Result process_string(const uint32_t *w, int lo, int hi, bool want_hash, u
     return r;
 }
 
+
+// --------------------------------------------------------------------------- //
+// Fast path: ASCII strings staged in (mutable) shared memory.
+//
+// The string is stripped by scanning ASCII whitespace inwards from both ends, the
+// "kubectl " prefix is compared on the raw bytes, and then ONE table-driven pass
+// over the stripped bytes advances a combined automaton
+//     state = quoting state (A,SQ,DQ,EA,ED) x previous byte class (other,&,|)
+// whose table entries also carry the sticky METACHAR / NON-ASCII flags, while the
+// sanitised form (whitespace runs -> one 0x20) is compacted IN PLACE at the front
+// of the string's own bytes (stores only happen once the output position differs
+// from the input position, i.e. never for an already-clean string).  SipHash-1-3
+// then runs over that compacted byte stream eight bytes per step, which keeps the
+// lanes of a warp in lockstep.  A string with any byte >= 0x80 (or, in PARSE mode,
+// starting with a back-tick) is reported back for the general code-point path.
+// --------------------------------------------------------------------------- //
+enum : uint32_t { F_STATE = 15u, F_META = 16u, F_NONASCII = 32u };
+
+struct FastTables {
+    uint8_t cls[256];     // byte -> class: 0 other 1 space 2 other-ws 3 meta 4 & 5 | 6 backslash 7 ' 8 " 9 >=0x80
+    uint8_t trans[256];   // (state << 4 | class) -> next state | flags
+};
+
+KX_HD constexpr FastTables make_fast_tables() {
+    FastTables t{};
+    for (int b = 0; b < 256; ++b) {
+        uint8_t c = 0;
+        if (b >= 0x80) c = 9;
+        else if (b == 0x20) c = 1;
+        else if ((b >= 0x09 && b <= 0x0D) || (b >= 0x1C && b <= 0x1F)) c = 2;
+        else if (b == ';' || b == '`' || b == '$' || b == '(' || b == ')' || b == '<' || b == '>') c = 3;
+        else if (b == '&') c = 4;
+        else if (b == '|') c = 5;
+        else if (b == '\\') c = 6;
+        else if (b == '\'') c = 7;
+        else if (b == '"') c = 8;
+        t.cls[b] = c;
+    }
+    const int dfa[5][4] = {{0, 3, 1, 2}, {1, 1, 0, 1}, {2, 4, 2, 0}, {0, 0, 0, 0}, {2, 2, 2, 2}};
+    for (int st = 0; st < 16; ++st) {
+        for (int c = 0; c < 16; ++c) {
+            uint8_t e = 0;
+            if (st < 15 && c < 10) {
+                const int q = st / 3, prev = st % 3;
+                const int qc = c == 6 ? 1 : c == 7 ? 2 : c == 8 ? 3 : 0;
+                const int nq = dfa[q][qc];
+                const int np = c == 4 ? 1 : c == 5 ? 2 : 0;
+                e = (uint8_t)(nq * 3 + np);
+                if (c == 3 || (c == 4 && prev == 1) || (c == 5 && prev == 2)) e |= F_META;
+                if (c == 9) e |= F_NONASCII;
+            }
+            t.trans[st * 16 + c] = e;
+        }
+    }
+    return t;
+}
+
+KX_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t shift_bits) {   // shift_bits in {0,8,16,24}
+#ifdef __CUDA_ARCH__
+    return __funnelshift_r(lo, hi, shift_bits);
+#else
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> shift_bits);
+#endif
+}
+
+// SipHash-1-3 (zero key) of the n bytes starting at byte offset `lo` of word buffer W.
+KX_HD int64_t sip_stream(const uint32_t *W, int lo, int n) {
+    if (n == 0) return 0;
+    Sip s;
+    s.init();
+    const uint32_t sh = (uint32_t)(lo & 3) * 8u;
+    int wi = lo >> 2;
+    uint32_t w0 = W[wi];
+    int left = n;
+    for (; left >= 8; left -= 8, wi += 2) {
+        const uint32_t w1 = W[wi + 1], w2 = W[wi + 2];
+        const uint64_t m = ((uint64_t)funnel_r(w1, w2, sh) << 32) | funnel_r(w0, w1, sh);
+        s.v3 ^= m; s.round(); s.v0 ^= m;
+        w0 = w2;
+    }
+    uint64_t m = 0;
+    if (left > 0) {
+        const uint32_t w1 = W[wi + 1];
+        const uint32_t w2 = left + (int)(sh >> 3) > 8 ? W[wi + 2] : 0u;
+        m = ((uint64_t)funnel_r(w1, w2, sh) << 32) | funnel_r(w0, w1, sh);
+        m &= ~0ULL >> (64 - 8 * left);
+    }
+    s.m = m;
+    s.nbytes = (uint32_t)n;
+    return s.finish();
+}
+
+// Returns true if the string must be redone by the general path; otherwise fills r.
+template <bool PARSE>
+KX_HD bool fast_string(uint32_t *W, int lo, int hi, const uint8_t *cls_lut, const uint8_t *trans,
+                       bool want_hash, uint8_t *san, Result &r) {
+    uint8_t *B = (uint8_t *)W;
+    int a = lo, b = hi;
+    while (a < hi && ws_ascii(B[a])) ++a;
+    while (b > a && ws_ascii(B[b - 1])) --b;
+    if (PARSE && a < b && B[a] == 0x60) return true;
+
+    bool pfx = false;
+    if (b - a >= 8) {
+        const uint32_t sh = (uint32_t)(a & 3) * 8u;
+        const int wi = a >> 2;
+        const uint32_t w0 = W[wi], w1 = W[wi + 1], w2 = W[wi + 2];
+        pfx = funnel_r(w0, w1, sh) == 0x6562756bu && funnel_r(w1, w2, sh) == 0x206c7463u;   // "kube" "ctl "
+    }
+
+    int o = lo;
+    uint32_t sf = 0;
+    bool prev_nonws = false;
+    uint32_t cur = a < b ? W[a >> 2] : 0u;
+    for (int p = a; p < b; ++p) {
+        const uint32_t x = kx_byte(cur, p & 3);
+        if ((p & 3) == 3 && p + 1 < b) cur = W[(p + 1) >> 2];
+        const uint32_t c = cls_lut[x];
+        sf = trans[((sf & F_STATE) << 4) | c] | (sf & (F_META | F_NONASCII));
+        const bool ws = (c - 1u) <= 1u;
+        const bool emit = !ws || prev_nonws;
+        const uint32_t val = ws ? 0x20u : x;
+        if (emit && (o != p || val != x)) B[o] = (uint8_t)val;
+        o += emit ? 1 : 0;
+        prev_nonws = !ws;
+    }
+    if (sf & F_NONASCII) return true;
+
+    r.verdict = !pfx ? KX_BAD_PREFIX : (sf & F_META) ? KX_METACHAR : (sf & F_STATE) >= 3u ? KX_BAD_QUOTING : KX_SAFE;
+    r.span_a = a - lo;
+    r.span_b = b - lo;
+    r.san_len = o - lo;
+    r.hash = want_hash ? sip_stream(W, lo, o - lo) : 0;
+    if (san) for (int i = 0; i < o - lo; ++i) san[i] = B[lo + i];
+    return false;
+}
+
 }  // namespace k9

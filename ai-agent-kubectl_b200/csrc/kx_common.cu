@@ -1,5 +1,8 @@
 #include "kx_common.cuh"
 #include <stdarg.h>
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace kx {
 static thread_local char t_err[512] = "";
@@ -11,8 +14,46 @@ void set_error(const char *fmt, ...) {
     vsnprintf(t_err, sizeof t_err, fmt, ap);
     va_end(ap);
 }
+
+namespace {
+struct Scratch { void *ptr = nullptr; size_t cap = 0; };
+std::mutex g_scratch_mu;
+std::map<std::pair<int, cudaStream_t>, Scratch> g_scratch;
+}  // namespace
+
+int stream_scratch(cudaStream_t stream, size_t bytes, void **out) {
+    int dev = 0;
+    KX_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    Scratch &s = g_scratch[{dev, stream}];
+    if (s.cap < bytes) {
+        if (s.ptr) {
+            KX_CUDA(cudaStreamSynchronize(stream));   // earlier work on this stream may still use it
+            KX_CUDA(cudaFree(s.ptr));
+            s.ptr = nullptr; s.cap = 0;
+        }
+        size_t cap = bytes + bytes / 4 + 256;
+        KX_CUDA(cudaMalloc(&s.ptr, cap));
+        s.cap = cap;
+    }
+    *out = s.ptr;
+    return KX_OK;
+}
+
+void release_scratch() {
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (auto &kv : g_scratch) {
+        cudaSetDevice(kv.first.first);
+        cudaFree(kv.second.ptr);
+    }
+    g_scratch.clear();
+    cudaSetDevice(prev);
+}
 }  // namespace kx
 
 extern "C" const char *kx_last_error(void) { return kx::t_err; }
 extern "C" int kx_version(void) { return 100; }
+extern "C" void kx_release_scratch(void) { kx::release_scratch(); }
 extern "C" int64_t kx_launch_count(void) { return kx::g_launches.load(); }

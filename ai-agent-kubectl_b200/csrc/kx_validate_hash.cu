@@ -7,14 +7,13 @@
 //
 // Layout: one CTA of 256 threads owns 256 consecutive strings.  The CTA's byte
 // range is contiguous in the CSR buffer, so it is staged into shared memory with
-// coalesced 16-byte loads (each HBM byte is read exactly once); then every thread
-// walks its own string out of shared memory, one code point at a time, carrying
-//   - the validator state (prefix match, metacharacter flag, 5-state quoting DFA),
-//     snapshotted at the last non-whitespace character so that strip() needs no
-//     backward scan,
-//   - the sanitiser (token/space state) feeding SipHash-1-3 eight bytes at a time
-//     in the buffer width (1/2/4 bytes per code point) CPython would have chosen.
-// A CTA whose byte range exceeds the staging buffer reads global memory directly.
+// coalesced 16-byte loads (each HBM byte is read exactly once).  Strings are
+// handed to threads sorted by length (a counting sort in shared memory) so the
+// lanes of a warp finish together.  Each thread then runs the table-driven ASCII
+// fast path of k9_core.cuh on its string; the few strings it hands back
+// (non-ASCII, fenced output in PARSE mode, CTAs whose byte range exceeds the staging
+// buffer) are appended to a queue in global scratch memory, and a second kernel runs
+// the general code-point path over that queue, packed densely over its threads.
 #include "kx_common.cuh"
 #include "k9_core.cuh"
 
@@ -22,47 +21,146 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kStageBytes = 32 * 1024;
+constexpr int kStageSlack = 16;           // sip_stream may read two words past the last string
+constexpr int kGeneralThreads = 128;
 
-template <bool PARSE>
-__global__ void __launch_bounds__(kThreads)
-k9_validate_hash(const uint8_t *__restrict__ data, const int64_t *__restrict__ off, int64_t n,
-                 uint8_t *__restrict__ verdict, int64_t *__restrict__ hash, int32_t *__restrict__ span,
-                 uint8_t *__restrict__ san, int32_t *__restrict__ san_len) {
-    extern __shared__ uint4 stage[];
-    const int64_t s0 = (int64_t)blockIdx.x * kThreads;
-    const int64_t s1 = min(n, s0 + kThreads);
-    const int64_t g_beg = off[s0], g_end = off[s1];
-    const uintptr_t addr = (uintptr_t)(data + g_beg);
-    const uint4 *abase = (const uint4 *)(addr & ~(uintptr_t)15);
-    const int lead = (int)(addr & 15);
-    const int64_t nbytes = lead + (g_end - g_beg);
-    const bool staged = nbytes <= kStageBytes;   // CTA-uniform
-    if (staged) {
-        const int nvec = (int)((nbytes + 15) >> 4);
-        for (int v = threadIdx.x; v < nvec; v += kThreads) stage[v] = __ldg(abase + v);
-        __syncthreads();
-    }
-    const int64_t s = s0 + threadIdx.x;
-    if (s >= s1) return;
-    const int64_t o0 = off[s], o1 = off[s + 1];
-    const uint32_t *w;
-    int lo, hi;
-    if (staged) {
-        w = (const uint32_t *)stage;
-        lo = (int)(o0 - g_beg) + lead;
-        hi = (int)(o1 - g_beg) + lead;
-    } else {
-        const uintptr_t sa = (uintptr_t)(data + o0);
-        w = (const uint32_t *)(sa & ~(uintptr_t)15);
-        lo = (int)(sa & 15);
-        hi = lo + (int)(o1 - o0);
-    }
+__device__ const k9::FastTables g_tables = k9::make_fast_tables();
 
-    const k9::Result r = k9::process_string<PARSE>(w, lo, hi, hash != nullptr, san ? san + o0 : nullptr);
+struct __align__(16) Shared {
+    k9::FastTables tab;
+    int32_t soff[kThreads + 1];           // string offsets relative to the staged base
+    int32_t hist[32];
+    int32_t perm[kThreads];
+    int32_t slowq[kThreads];
+    int32_t nslow;
+    uint32_t qbase;
+};
+
+__device__ __forceinline__ void store_result(const k9::Result &r, int64_t s, uint8_t *verdict, int64_t *hash,
+                                             int32_t *span, int32_t *san_len) {
     if (hash) hash[s] = r.hash;
     if (san_len) san_len[s] = r.san_len;
     if (verdict) verdict[s] = (uint8_t)r.verdict;
     if (span) { span[2 * s] = r.span_a; span[2 * s + 1] = r.span_b; }
+}
+
+// Pass 1: table-driven ASCII fast path out of shared memory.  Strings it cannot
+// finish are appended to `queue` (scratch: queue[0] is the element count, entries
+// start at queue[2]; entries are indices relative to this launch's first string).
+template <bool PARSE>
+__global__ void __launch_bounds__(kThreads)
+k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restrict__ off, int64_t n,
+                      uint8_t *__restrict__ verdict, int64_t *__restrict__ hash, int32_t *__restrict__ span,
+                      uint8_t *__restrict__ san, int32_t *__restrict__ san_len, uint32_t *__restrict__ queue) {
+    extern __shared__ uint4 stage[];                       // kStageBytes + slack, then Shared
+    Shared &sh = *reinterpret_cast<Shared *>(reinterpret_cast<uint8_t *>(stage) + kStageBytes + kStageSlack);
+    const int tid = threadIdx.x;
+    const int64_t s0 = (int64_t)blockIdx.x * kThreads;
+    const int cnt = (int)min((int64_t)kThreads, n - s0);
+    const int64_t g_beg = off[s0], g_end = off[s0 + cnt];
+    const uintptr_t addr = (uintptr_t)(data + g_beg);
+    const uint4 *abase = (const uint4 *)(addr & ~(uintptr_t)15);
+    const int lead = (int)(addr & 15);
+    const int64_t nbytes = lead + (g_end - g_beg);
+    const bool staged = nbytes <= kStageBytes;             // CTA-uniform
+
+    if (tid == 0) sh.nslow = 0;
+    if (staged) {
+        // ---- stage bytes (coalesced 16 B loads), tables and offsets ----
+        const int nvec = (int)((nbytes + 15) >> 4);
+        for (int v = tid; v < nvec; v += kThreads) stage[v] = __ldg(abase + v);
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&g_tables);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(&sh.tab);
+        for (int i = tid; i < (int)(sizeof(k9::FastTables) / 4); i += kThreads) dst[i] = src[i];
+        for (int i = tid; i <= cnt; i += kThreads) sh.soff[i] = (int32_t)(off[s0 + i] - g_beg) + lead;
+        if (tid < 32) sh.hist[tid] = 0;
+        __syncthreads();
+
+        // ---- give each warp strings of similar length (counting sort on len/8) ----
+        int bucket = 0, rank = 0;
+        if (tid < cnt) {
+            bucket = min((sh.soff[tid + 1] - sh.soff[tid]) >> 3, 31);
+            rank = atomicAdd(&sh.hist[bucket], 1);
+        }
+        __syncthreads();
+        if (tid < 32) {
+            const int c = sh.hist[tid];
+            int incl = c;
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (tid >= d) incl += t;
+            }
+            sh.hist[tid] = incl - c;                      // exclusive prefix
+        }
+        __syncthreads();
+        if (tid < cnt) sh.perm[sh.hist[bucket] + rank] = tid;
+        __syncthreads();
+
+        if (tid < cnt) {
+            const int i = sh.perm[tid];
+            k9::Result r;
+            const bool slow = k9::fast_string<PARSE>(reinterpret_cast<uint32_t *>(stage), sh.soff[i], sh.soff[i + 1],
+                                                     sh.tab.cls, sh.tab.trans, hash != nullptr,
+                                                     san ? san + g_beg + (sh.soff[i] - lead) : nullptr, r);
+            if (slow) sh.slowq[atomicAdd(&sh.nslow, 1)] = i;
+            else store_result(r, s0 + i, verdict, hash, span, san_len);
+        }
+    } else {
+        // strings too long to stage: the whole CTA goes to the general pass
+        __syncthreads();
+        if (tid < cnt) sh.slowq[atomicAdd(&sh.nslow, 1)] = tid;
+    }
+    __syncthreads();
+    const int nslow = sh.nslow;
+    if (nslow == 0) return;
+    if (tid == 0) sh.qbase = atomicAdd(queue, (uint32_t)nslow);
+    __syncthreads();
+    for (int q = tid; q < nslow; q += kThreads) queue[2 + sh.qbase + q] = (uint32_t)(s0 + sh.slowq[q]);
+}
+
+// Pass 2: general code-point path (k9::process_string) over the queued strings,
+// read from global memory, one string per thread with the queue packed densely.
+template <bool PARSE>
+__global__ void __launch_bounds__(kGeneralThreads)
+k9_validate_hash_general(const uint8_t *__restrict__ data, const int64_t *__restrict__ off,
+                         uint8_t *__restrict__ verdict, int64_t *__restrict__ hash, int32_t *__restrict__ span,
+                         uint8_t *__restrict__ san, int32_t *__restrict__ san_len,
+                         const uint32_t *__restrict__ queue) {
+    const uint32_t count = queue[0];
+    for (uint32_t q = blockIdx.x * kGeneralThreads + threadIdx.x; q < count; q += gridDim.x * kGeneralThreads) {
+        const int64_t s = queue[2 + q];
+        const int64_t o0 = off[s], o1 = off[s + 1];
+        const uintptr_t sa = (uintptr_t)(data + o0);
+        const uint32_t *w = (const uint32_t *)(sa & ~(uintptr_t)15);
+        const int lo = (int)(sa & 15), hi = lo + (int)(o1 - o0);
+        const k9::Result r = k9::process_string<PARSE>(w, lo, hi, hash != nullptr, san ? san + o0 : nullptr);
+        store_result(r, s, verdict, hash, span, san_len);
+    }
+}
+
+constexpr int kSmemBytes = kStageBytes + kStageSlack + (int)sizeof(Shared);
+constexpr int64_t kMaxStringsPerLaunch = 1ll << 31;   // queue entries are uint32 string indices
+
+// Both passes for n strings whose offsets start at `off`; `queue` holds 2 + n words.
+int launch_passes(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32_t flags, uint8_t *d_verdict,
+                  int64_t *d_hash, int32_t *d_span, uint8_t *d_san, int32_t *d_san_len, uint32_t *queue,
+                  cudaStream_t st) {
+    KX_CUDA(cudaMemsetAsync(queue, 0, 8, st));
+    const unsigned blocks = (unsigned)((n + kThreads - 1) / kThreads);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned gblocks = (unsigned)min((int64_t)sms * 8, (n + kGeneralThreads - 1) / kGeneralThreads);
+    if (flags & KX_FLAG_PARSE) {
+        k9_validate_hash_fast<true><<<blocks, kThreads, kSmemBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+        k9_validate_hash_general<true><<<gblocks, kGeneralThreads, 0, st>>>(d_data, d_off, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+    } else {
+        k9_validate_hash_fast<false><<<blocks, kThreads, kSmemBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+        k9_validate_hash_general<false><<<gblocks, kGeneralThreads, 0, st>>>(d_data, d_off, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+    }
+    kx::count_launch(2);
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
 }
 
 }  // namespace
@@ -74,14 +172,18 @@ extern "C" int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int
     KX_REQUIRE((flags & ~KX_FLAG_PARSE) == 0, KX_EINVAL, "kx_validate_hash: unknown flags 0x%x", flags);
     if (n == 0) return KX_OK;
     KX_REQUIRE(d_off != nullptr, KX_EINVAL, "kx_validate_hash: d_off is NULL");
-    const int64_t blocks = (n + kThreads - 1) / kThreads;
-    KX_REQUIRE(blocks <= 0x7fffffff, KX_ETOOBIG, "kx_validate_hash: n = %lld exceeds 2^31 * 256 strings", (long long)n);
     cudaStream_t st = (cudaStream_t)stream;
-    if (flags & KX_FLAG_PARSE)
-        k9_validate_hash<true><<<(unsigned)blocks, kThreads, kStageBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len);
-    else
-        k9_validate_hash<false><<<(unsigned)blocks, kThreads, kStageBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len);
-    kx::count_launch();
-    KX_CUDA(cudaGetLastError());
+    // Scratch: the queue of strings handed from pass 1 to pass 2 (4 bytes per string, worst case
+    // every string).  Owned by the library, cached per (device, stream), grown on demand.
+    for (int64_t r0 = 0; r0 < n; r0 += kMaxStringsPerLaunch) {
+        const int64_t rows = min(n - r0, kMaxStringsPerLaunch);
+        uint32_t *queue = nullptr;
+        int rc = kx::stream_scratch(st, sizeof(uint32_t) * (size_t)(rows + 2), (void **)&queue);
+        if (rc != KX_OK) return rc;
+        rc = launch_passes(d_data, d_off + r0, rows, flags, d_verdict ? d_verdict + r0 : nullptr,
+                           d_hash ? d_hash + r0 : nullptr, d_span ? d_span + 2 * r0 : nullptr, d_san,
+                           d_san_len ? d_san_len + r0 : nullptr, queue, st);
+        if (rc != KX_OK) return rc;
+    }
     return KX_OK;
 }

@@ -1,0 +1,36 @@
+"""Deterministic byte-level tokenizer (no tokenizer vocabulary exists offline).
+
+id 0..255 = the UTF-8 byte, 256 = BOS, 257 = EOS.  Random-init weights emit ids
+anywhere in [0, vocab); ids above 257 decode to the byte ``id & 0xFF`` so that every
+completion is a well-defined string for the parser/validator."""
+from __future__ import annotations
+
+from typing import List, Sequence
+
+BOS, EOS = 256, 257
+
+
+def encode(text: str, bos: bool = True) -> List[int]:
+    ids = list(text.encode("utf-8"))
+    return ([BOS] + ids) if bos else ids
+
+
+def decode(ids: Sequence[int]) -> str:
+    out = bytearray()
+    for i in ids:
+        i = int(i)
+        if i == EOS:
+            break
+        if i == BOS:
+            continue
+        out.append(i & 0xFF)
+    return out.decode("utf-8", errors="replace")
+
+
+def encode_fixed(text: str, length: int, pad: int = 32) -> List[int]:
+    """Prompt padded (left, with spaces) or truncated (keeping the tail, where the
+    query and the 'Kubectl Command:' cue are) to exactly ``length`` tokens."""
+    ids = encode(text, bos=False)
+    if len(ids) >= length - 1:
+        return [BOS] + ids[len(ids) - (length - 1):]
+    return [BOS] + [pad] * (length - 1 - len(ids)) + ids

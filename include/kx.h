@@ -65,6 +65,10 @@ int kx_version(void);
  * Any of the five output pointers may be NULL to skip that output.  Strings must
  * be shorter than 2^31-16 bytes.  Input that is not valid UTF-8 is processed by
  * a fixed, documented rule rather than rejected.
+ * Scratch: the first call on a (device, stream) pair with a larger n than before
+ * allocates 4 bytes per string of library-owned device memory (cudaMalloc, which
+ * synchronises); later calls reuse it.  Calls on one stream are ordered; calls on
+ * different streams use different scratch and may overlap.
  * The kernel reads d_data in aligned 16-byte units, so the bytes up to the next
  * 16-byte boundary after the last string must be readable (true of any CUDA
  * allocation).
@@ -86,6 +90,11 @@ int kx_validate_hash_host(const uint8_t *h_data, const int64_t *h_off, int64_t n
                           uint8_t *h_verdict, int64_t *h_hash, int32_t *h_span,
                           uint8_t *h_san, int32_t *h_san_len, int device);
 void kx_release_host_staging(void);
+
+/* frees the device scratch the library caches per (device, stream): the queue
+ * kx_validate_hash uses to hand strings from its fast pass to its general pass
+ * (4 bytes per string of the largest batch seen on that stream) */
+void kx_release_scratch(void);
 
 /* number of kernels this library has launched in this process (for bench.py) */
 int64_t kx_launch_count(void);

@@ -1,0 +1,116 @@
+"""TEST INFRASTRUCTURE ONLY -- plain-PyTorch fp32 CPU decoder (Llama / Qwen2 family)
+used as the oracle of the generator kernels and as the timed CPU baseline of the
+generation workloads.  The product path never imports it.
+
+Parity status: the reference repository contains no model code (its ``llm`` slot is
+the OpenAI service, app.py:108-117), so for generation **parity is unpinned by the
+reference**.  The pins are BASELINE.json's: first 32 greedy token ids equal, logits
+within 1e-2 relative of this model with the same (bf16-rounded) weights.  The
+architecture itself is pinned against ``transformers`` (Qwen2ForCausalLM /
+LlamaForCausalLM, version 5.5 in this image) in tests/test_cpu_model.py.
+
+Two numeric modes:
+  * ``emulate_bf16=False`` -- everything in fp32 (the reference the 1e-2 logits
+    bound is stated against).
+  * ``emulate_bf16=True``  -- same fp32 arithmetic, but activations are rounded to
+    bf16 exactly where the CUDA path stores bf16 (GEMM inputs, q/k/v, KV cache,
+    attention output, SwiGLU output).  Greedy ids are compared against this mode:
+    with random weights top-1 margins are tiny, and only a reference with the same
+    quantisation points makes "ids equal" a statement about the kernels rather
+    than about rounding luck.  DESIGN.md lists the rounding points.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+
+def _r(x: torch.Tensor, on: bool) -> torch.Tensor:
+    return x.to(torch.bfloat16).to(torch.float32) if on else x
+
+
+class RefModel:
+    def __init__(self, cfg, weights: Dict[str, torch.Tensor], rope: torch.Tensor, emulate_bf16: bool = False):
+        self.cfg, self.emu = cfg, emulate_bf16
+        self.w = {k: v.to(torch.float32) for k, v in weights.items()}
+        self.rope = rope  # [max_pos, hd/2, 2]
+
+    # -- pieces ---------------------------------------------------------------
+    def _norm(self, x, g):
+        var = x.pow(2).mean(-1, keepdim=True)
+        return x * torch.rsqrt(var + self.cfg.eps) * g
+
+    def _rope(self, x, pos):
+        # x [B,S,heads,hd], pos [B,S]; rotate-half pairs (i, i + hd/2)
+        half = self.cfg.head_dim // 2
+        cs = self.rope[pos]                      # [B,S,half,2]
+        cos, sin = cs[..., 0][:, :, None, :], cs[..., 1][:, :, None, :]
+        x1, x2 = x[..., :half], x[..., half:]
+        return torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], dim=-1)
+
+    def _layer(self, i, x, pos, cache, mask):
+        c, w, emu = self.cfg, self.w, self.emu
+        B, S, _ = x.shape
+        h = _r(self._norm(x, w[f"ln1.{i}"]), emu)
+        q, k, v = h @ w[f"wq.{i}"].T, h @ w[f"wk.{i}"].T, h @ w[f"wv.{i}"].T
+        if c.qkv_bias:
+            q, k, v = q + w[f"bq.{i}"], k + w[f"bk.{i}"], v + w[f"bv.{i}"]
+        q, k, v = _r(q, emu), _r(k, emu), _r(v, emu)
+        q = _r(self._rope(q.view(B, S, c.n_q, c.head_dim), pos), emu)
+        k = _r(self._rope(k.view(B, S, c.n_kv, c.head_dim), pos), emu)
+        v = v.view(B, S, c.n_kv, c.head_dim)
+        if cache is not None:
+            pk, pv = cache[i]
+            k = torch.cat([pk, k], dim=1) if pk is not None else k
+            v = torch.cat([pv, v], dim=1) if pv is not None else v
+            cache[i] = (k, v)
+        grp = c.n_q // c.n_kv
+        kk = k.repeat_interleave(grp, dim=2).permute(0, 2, 1, 3)      # [B,nq,T,hd]
+        vv = v.repeat_interleave(grp, dim=2).permute(0, 2, 1, 3)
+        s = (q.permute(0, 2, 1, 3) @ kk.transpose(-1, -2)) * (c.head_dim ** -0.5)
+        if mask is not None:
+            s = s + mask
+        p = torch.softmax(s, dim=-1)
+        a = _r((p @ vv).permute(0, 2, 1, 3).reshape(B, S, c.q_dim), emu)
+        x = x + a @ w[f"wo.{i}"].T
+        h = _r(self._norm(x, w[f"ln2.{i}"]), emu)
+        g, u = h @ w[f"wg.{i}"].T, h @ w[f"wu.{i}"].T
+        m = _r(torch.nn.functional.silu(g) * u, emu)
+        return x + m @ w[f"wd.{i}"].T
+
+    def forward(self, tokens: torch.Tensor, pos0: int = 0, cache: Optional[list] = None,
+                last_only: bool = True) -> torch.Tensor:
+        """tokens [B,S] int64 at positions pos0..pos0+S-1 -> logits [B,V] (last) or [B,S,V]."""
+        B, S = tokens.shape
+        x = self.w["embed"][tokens]
+        pos = torch.arange(pos0, pos0 + S)[None, :].expand(B, S)
+        T = pos0 + S
+        mask = None
+        if S > 1:
+            mask = torch.full((S, T), float("-inf")).triu(diagonal=pos0 + 1)[None, None]
+        for i in range(self.cfg.layers):
+            x = self._layer(i, x, pos, cache, mask)
+        if last_only:
+            x = x[:, -1:, :]
+        h = _r(self._norm(x, self.w["norm"]), self.emu)
+        head = self.w["embed"] if self.cfg.tied else self.w["lm_head"]
+        logits = h @ head.T
+        return logits[:, 0] if last_only else logits
+
+    @torch.no_grad()
+    def generate(self, tokens: torch.Tensor, n_new: int, return_logits: bool = False
+                 ) -> Tuple[torch.Tensor, List[torch.Tensor]]:
+        """Greedy decoding (temperature 0, app.py:109); ties -> lowest index like torch.argmax."""
+        cache = [(None, None) for _ in range(self.cfg.layers)]
+        S = tokens.shape[1]
+        logits = self.forward(tokens, 0, cache)
+        out, keep = [], []
+        for t in range(n_new):
+            nxt = logits.argmax(-1)
+            out.append(nxt)
+            if return_logits:
+                keep.append(logits.clone())
+            if t + 1 < n_new:
+                logits = self.forward(nxt[:, None], S + t, cache)
+        return torch.stack(out, dim=1), keep

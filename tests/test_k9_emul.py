@@ -21,15 +21,16 @@ def emul():
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(core)):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", src, "-o", so])
     L = ctypes.CDLL(so)
-    L.k9_emul.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint32] + [ctypes.c_void_p] * 5
+    L.k9_emul.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_uint32] + [ctypes.c_void_p] * 5 + [ctypes.c_int]
+    L.k9_emul.restype = ctypes.c_int64
 
-    def run(data, off, flags):
+    def run(data, off, flags, mode=0):
         n = off.size - 1
         out = {"verdict": np.empty(n, np.uint8), "hash": np.empty(n, np.int64), "span": np.empty((n, 2), np.int32),
                "san": np.zeros(max(1, data.size), np.uint8), "san_len": np.empty(n, np.int32)}
         data = np.ascontiguousarray(data)
-        L.k9_emul(data.ctypes.data if data.size else None, off.ctypes.data, n, flags, *(out[k].ctypes.data for k in
-                  ("verdict", "hash", "span", "san", "san_len")))
+        out["nslow"] = L.k9_emul(data.ctypes.data if data.size else None, off.ctypes.data, n, flags,
+                                 *(out[k].ctypes.data for k in ("verdict", "hash", "span", "san", "san_len")), mode)
         return out
     return run
 
@@ -58,7 +59,11 @@ def test_kernel_logic_on_synthetic_and_garbage(emul, flags):
     import kubectl_b200  # noqa: F401
     from kubectl_b200 import synth
     data, off = synth.command_csr(50_000, seed=2)
-    _same(emul(data, off, flags), c_oracle.validate_hash(data, off, flags, True, True), off)
+    ref = c_oracle.validate_hash(data, off, flags, True, True)
+    got = emul(data, off, flags)
+    _same(got, ref, off)
+    assert 0 < got["nslow"] < 0.1 * 50_000          # only the non-ASCII strings leave the fast path
+    _same(emul(data, off, flags, mode=1), ref, off)  # general path alone
     rng = random.Random(5)
     al = [0x20, 0x27, 0x22, 0x5C, 0x60, 0x6B, 0x80, 0xA0, 0xC2, 0xE2, 0xE3, 0xF0, 0xFF, 0x28, 0x85, 0x9F, 0x81, 0x00,
           0x40, 0xA8, 0xC1, 0x09]
