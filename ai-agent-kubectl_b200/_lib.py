@@ -27,6 +27,8 @@ _SIGNATURES = {
     "kx_validate_hash_host": (c_int, [c_void_p, c_void_p, c_int64, c_uint32] + [c_void_p] * 5 + [c_int]),
     "kx_release_host_staging": (None, []),
     "kx_release_scratch": (None, []),
+    "kx_gemm_bf16": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p,
+                             c_int64, c_void_p, c_int, c_void_p]),
 }
 
 

@@ -3,6 +3,7 @@
 #include <map>
 #include <mutex>
 #include <utility>
+#include <tuple>
 
 namespace kx {
 static thread_local char t_err[512] = "";
@@ -18,14 +19,14 @@ void set_error(const char *fmt, ...) {
 namespace {
 struct Scratch { void *ptr = nullptr; size_t cap = 0; };
 std::mutex g_scratch_mu;
-std::map<std::pair<int, cudaStream_t>, Scratch> g_scratch;
+std::map<std::tuple<int, cudaStream_t, int>, Scratch> g_scratch;
 }  // namespace
 
-int stream_scratch(cudaStream_t stream, size_t bytes, void **out) {
+int stream_scratch(cudaStream_t stream, int tag, size_t bytes, void **out, bool zero_on_alloc) {
     int dev = 0;
     KX_CUDA(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_scratch_mu);
-    Scratch &s = g_scratch[{dev, stream}];
+    Scratch &s = g_scratch[std::make_tuple(dev, stream, tag)];
     if (s.cap < bytes) {
         if (s.ptr) {
             KX_CUDA(cudaStreamSynchronize(stream));   // earlier work on this stream may still use it
@@ -35,6 +36,7 @@ int stream_scratch(cudaStream_t stream, size_t bytes, void **out) {
         size_t cap = bytes + bytes / 4 + 256;
         KX_CUDA(cudaMalloc(&s.ptr, cap));
         s.cap = cap;
+        if (zero_on_alloc) KX_CUDA(cudaMemsetAsync(s.ptr, 0, cap, stream));
     }
     *out = s.ptr;
     return KX_OK;
@@ -45,7 +47,7 @@ void release_scratch() {
     int prev = 0;
     cudaGetDevice(&prev);
     for (auto &kv : g_scratch) {
-        cudaSetDevice(kv.first.first);
+        cudaSetDevice(std::get<0>(kv.first));
         cudaFree(kv.second.ptr);
     }
     g_scratch.clear();

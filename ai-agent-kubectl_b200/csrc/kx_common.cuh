@@ -11,9 +11,10 @@ namespace kx {
 void set_error(const char *fmt, ...);
 extern std::atomic<int64_t> g_launches;
 
-// Library-owned device scratch, cached per (current device, stream) and grown on demand
+// Library-owned device scratch, cached per (current device, stream, purpose) and grown on demand
 // (cudaMalloc only when it has to grow).  Valid until the next call on the same stream.
-int stream_scratch(cudaStream_t stream, size_t bytes, void **out);
+enum ScratchTag { SCRATCH_K9_QUEUE = 0, SCRATCH_GEMM = 1, SCRATCH_TAGS = 2 };
+int stream_scratch(cudaStream_t stream, int tag, size_t bytes, void **out, bool zero_on_alloc = false);
 void release_scratch();
 
 inline void count_launch(int k = 1) { g_launches.fetch_add(k, std::memory_order_relaxed); }

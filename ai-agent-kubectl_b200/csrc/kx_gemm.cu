@@ -1,0 +1,388 @@
+// k1 / k3: bf16 GEMM on the 5th-generation tensor cores.
+//
+//     D[Ma, Nb] = A[Ma, K] * B[Nb, K]^T      A, B bf16 with K contiguous, fp32 accumulate
+//
+// One kernel serves prefill and decode:
+//   * prefill (swap = 0): A = activations [tokens, K], B = weights [features, K];
+//     the accumulator row is a token, the epilogue writes rows of `out`.
+//   * decode  (swap = 1): A = weights [features, K], B = activations [batch, K]
+//     ("swap-AB": the 128-row MMA operand is the weight tile, the batch is the MMA
+//     N), so every weight byte is streamed from HBM exactly once by a full-width
+//     tcgen05.mma even when the batch is 64; split-K over gridDim.z gives enough CTAs
+//     to pull HBM bandwidth when features/128 is small.
+//
+// Structure per CTA (192 threads): warp 0 = TMA producer (cp.async.bulk.tensor, 128 B
+// swizzle, mbarrier full/empty ring), warp 1 = TMEM allocator + single-thread
+// tcgen05.mma issuer (accumulator in TMEM, tcgen05.commit releases smem stages),
+// warps 2-5 = epilogue (tcgen05.ld 32x32b -> registers -> fused epilogue -> global).
+// Epilogues: bf16 (+bias) | fp32 residual accumulate | SwiGLU over interleaved
+// (gate, up) features -> bf16 | fp32 (logits).
+// Split-K: partial tiles are reduced with fp32 atomics into library scratch; the CTA
+// that takes the last ticket of a tile applies the epilogue and re-zeroes the scratch
+// (residual epilogue: atomics go straight into the residual stream, no scratch).
+#include <map>
+#include <mutex>
+#include <tuple>
+#include <cuda_bf16.h>
+#include "kx_common.cuh"
+#include "kx_sm100.cuh"
+#include "kx_gemm.cuh"
+
+namespace kx {
+
+using namespace sm100;
+
+namespace {
+
+constexpr int BM = 128, BK = 64;
+constexpr int kGemmThreads = 192;
+
+template <int BN> struct Cfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (96 * 1024) / STAGE_BYTES;          // two CTAs per SM
+    static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// Fused epilogue for 32 consecutive accumulator columns [c0, c0+32) of accumulator row `r`.
+template <int EPI, bool SWAP>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams &p, float (&v)[32], int arow, int bcol0, bool atomic_resid) {
+    if (!SWAP) {
+        // accumulator row = output row (token), columns = features
+        if (arow >= p.a_rows) return;
+        if (EPI == EPI_BF16) {
+            __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out) + (size_t)arow * p.ldo + bcol0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                if (bcol0 + j >= p.b_rows) break;
+                float b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                if (p.bias) {
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) b[t] = __ldg(p.bias + bcol0 + j + t);
+                }
+                uint4 q;
+                q.x = pack_bf16(v[j + 0] + b[0], v[j + 1] + b[1]);
+                q.y = pack_bf16(v[j + 2] + b[2], v[j + 3] + b[3]);
+                q.z = pack_bf16(v[j + 4] + b[4], v[j + 5] + b[5]);
+                q.w = pack_bf16(v[j + 6] + b[6], v[j + 7] + b[7]);
+                *reinterpret_cast<uint4 *>(o + j) = q;
+            }
+        } else if (EPI == EPI_RESID) {
+            float *o = reinterpret_cast<float *>(p.out) + (size_t)arow * p.ldo + bcol0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                if (bcol0 + j >= p.b_rows) break;
+                if (atomic_resid) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) atomicAdd(o + j + t, v[j + t]);
+                } else {
+                    float4 x = *reinterpret_cast<float4 *>(o + j);
+                    x.x += v[j]; x.y += v[j + 1]; x.z += v[j + 2]; x.w += v[j + 3];
+                    *reinterpret_cast<float4 *>(o + j) = x;
+                }
+            }
+        } else if (EPI == EPI_SWIGLU) {
+            __nv_bfloat16 *o = reinterpret_cast<__nv_bfloat16 *>(p.out) + (size_t)arow * p.ldo + (bcol0 >> 1);
+#pragma unroll
+            for (int j = 0; j < 32; j += 16) {
+                if (bcol0 + j >= p.b_rows) break;
+                uint4 q;
+                q.x = pack_bf16(silu(v[j + 0]) * v[j + 1], silu(v[j + 2]) * v[j + 3]);
+                q.y = pack_bf16(silu(v[j + 4]) * v[j + 5], silu(v[j + 6]) * v[j + 7]);
+                q.z = pack_bf16(silu(v[j + 8]) * v[j + 9], silu(v[j + 10]) * v[j + 11]);
+                q.w = pack_bf16(silu(v[j + 12]) * v[j + 13], silu(v[j + 14]) * v[j + 15]);
+                *reinterpret_cast<uint4 *>(o + (j >> 1)) = q;
+            }
+        } else {
+            float *o = reinterpret_cast<float *>(p.out) + (size_t)arow * p.ldo + bcol0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                if (bcol0 + j >= p.b_rows) break;
+                *reinterpret_cast<float4 *>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            }
+        }
+    } else {
+        // accumulator row = feature, columns = batch entries: out[b * ldo + feature]
+        const bool ok = arow < p.a_rows;
+        const float bias = (ok && p.bias) ? __ldg(p.bias + arow) : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int b = bcol0 + j;
+            if (b >= p.b_rows) break;                 // warp-uniform
+            if (EPI == EPI_SWIGLU) {
+                const float other = __shfl_xor_sync(0xffffffffu, v[j], 1);
+                if (ok && !(arow & 1))
+                    reinterpret_cast<__nv_bfloat16 *>(p.out)[(size_t)b * p.ldo + (arow >> 1)] = __float2bfloat16(silu(v[j]) * other);
+            } else if (!ok) {
+                continue;
+            } else if (EPI == EPI_BF16) {
+                reinterpret_cast<__nv_bfloat16 *>(p.out)[(size_t)b * p.ldo + arow] = __float2bfloat16(v[j] + bias);
+            } else if (EPI == EPI_RESID) {
+                float *o = reinterpret_cast<float *>(p.out) + (size_t)b * p.ldo + arow;
+                if (atomic_resid) atomicAdd(o, v[j]); else *o += v[j];
+            } else {
+                reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] = v[j];
+            }
+        }
+    }
+}
+
+template <int BN, int EPI, bool SWAP>
+__global__ void __launch_bounds__(kGemmThreads, 2)
+kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t *empty = full + C::STAGES;
+    uint64_t *tmem_full = empty + C::STAGES;
+    uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(tmem_full + 1);
+    uint32_t *flag = tmem_holder + 1;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+    const int total_kb = (p.k + BK - 1) / BK;
+    const int kb0 = blockIdx.z * p.kb_per_split;
+    const int nkb = min(total_kb - kb0, p.kb_per_split);
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_holder, C::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // weights are streamed once (evict-first); activations are re-read by other CTAs (evict-last)
+            const uint64_t pol_a = SWAP ? policy_evict_first() : policy_evict_last();
+            const uint64_t pol_b = SWAP ? policy_evict_last() : policy_evict_first();
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % C::STAGES;
+                const uint32_t ph = (i / C::STAGES) & 1;
+                mbar_wait(empty + s, ph ^ 1);
+                mbar_expect_tx(full + s, C::STAGE_BYTES);
+                uint8_t *sa = smem + s * C::STAGE_BYTES;
+                tma_load_2d_hint(sa, &tmA, full + s, (kb0 + i) * BK, m0, pol_a);
+                tma_load_2d_hint(sa + C::A_BYTES, &tmB, full + s, (kb0 + i) * BK, n0, pol_b);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_f32(BM, BN);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % C::STAGES;
+                const uint32_t ph = (i / C::STAGES) & 1;
+                mbar_wait(full + s, ph);
+                tc_fence_after();
+                const uint32_t sa = base + s * C::STAGE_BYTES;
+                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::A_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)   // +32 B per 16-element K step inside the swizzle atom
+                    umma_bf16(tmem, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+                umma_commit(empty + s);             // frees the smem stage once these MMAs retire
+            }
+            umma_commit(tmem_full);
+        }
+    } else {
+        // ---- epilogue warps: TMEM lane quarter = warp % 4 ----
+        const int q = warp & 3;
+        const int arow = m0 + q * 32 + lane;
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+        const int etid = threadIdx.x - 64;
+        mbar_wait(tmem_full, 0);
+        tc_fence_after();
+        const bool split = gridDim.z > 1;
+        if (!split || EPI == EPI_RESID) {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                tmem_ld_wait();
+                epilogue_chunk<EPI, SWAP>(p, v, arow, n0 + c, split);
+            }
+        } else {
+            // split-K: reduce into scratch laid out [tile][col][row] so a warp's atomics are contiguous
+            const size_t tile = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+            float *ws = p.ws + tile * (size_t)(BM * BN) + q * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (n0 + c + j < p.b_rows) atomicAdd(ws + (size_t)(c + j) * BM, v[j]);
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (etid == 0) *flag = atomicAdd(p.tickets + tile, 1u) == gridDim.z - 1 ? 1u : 0u;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (*flag) {
+                __threadfence();
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        v[j] = 0.f;
+                        if (n0 + c + j < p.b_rows) { v[j] = __ldcg(ws + (size_t)(c + j) * BM); __stcg(ws + (size_t)(c + j) * BM, 0.f); }
+                    }
+                    epilogue_chunk<EPI, SWAP>(p, v, arow, n0 + c, false);
+                }
+                if (etid == 0) p.tickets[tile] = 0;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+}
+
+// ---- host side ----------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    });
+    return fn;
+}
+
+template <int BN, int EPI, bool SWAP>
+int launch(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
+    auto kern = kx_gemm_bf16_kernel<BN, EPI, SWAP>;
+    static bool attr_set = false;   // per instantiation
+    if (!attr_set) {
+        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        attr_set = true;
+    }
+    kern<<<grid, kGemmThreads, Cfg<BN>::SMEM_BYTES, st>>>(ta, tb, p);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+template <int BN, bool SWAP>
+int launch_epi(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
+    switch (p.epilogue) {
+        case EPI_BF16: return launch<BN, EPI_BF16, SWAP>(ta, tb, p, grid, st);
+        case EPI_RESID: return launch<BN, EPI_RESID, SWAP>(ta, tb, p, grid, st);
+        case EPI_SWIGLU: return launch<BN, EPI_SWIGLU, SWAP>(ta, tb, p, grid, st);
+        case EPI_F32: return launch<BN, EPI_F32, SWAP>(ta, tb, p, grid, st);
+    }
+    set_error("kx_gemm: unknown epilogue %d", p.epilogue);
+    return KX_EINVAL;
+}
+
+}  // namespace
+
+int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    KX_REQUIRE(fn != nullptr, KX_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    KX_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 2) % 16 == 0, KX_EINVAL,
+               "GEMM operand must be 16-byte aligned with a row pitch that is a multiple of 16 bytes");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    KX_REQUIRE(r == CUDA_SUCCESS, KX_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return KX_OK;
+}
+
+int gemm_pick_bn(int swap, int64_t b_rows) {
+    if (!swap) return 128;
+    return b_rows <= 32 ? 32 : b_rows <= 64 ? 64 : 128;
+}
+
+size_t gemm_scratch_bytes(const GemmParams &p, int bn) {
+    if (p.splits <= 1 || p.epilogue == EPI_RESID) return 0;
+    const size_t tiles = (size_t)((p.a_rows + BM - 1) / BM) * (size_t)((p.b_rows + bn - 1) / bn);
+    return tiles * (size_t)(BM * bn) * sizeof(float) + tiles * sizeof(uint32_t);
+}
+
+int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int bn, void *scratch, cudaStream_t st) {
+    const int total_kb = (p.k + BK - 1) / BK;
+    int splits = p.splits < 1 ? 1 : p.splits;
+    if (splits > total_kb) splits = total_kb;
+    p.kb_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;      // no empty slice
+    p.splits = splits;
+    const size_t tiles = (size_t)((p.a_rows + BM - 1) / BM) * (size_t)((p.b_rows + bn - 1) / bn);
+    if (splits > 1 && p.epilogue != EPI_RESID) {
+        KX_REQUIRE(scratch != nullptr, KX_EINVAL, "kx_gemm: split-K needs scratch");
+        p.ws = reinterpret_cast<float *>(scratch);
+        p.tickets = reinterpret_cast<uint32_t *>(p.ws + tiles * (size_t)(BM * bn));
+    }
+    dim3 grid((unsigned)((p.b_rows + bn - 1) / bn), (unsigned)((p.a_rows + BM - 1) / BM), (unsigned)splits);
+    if (p.swap) {
+        switch (bn) {
+            case 32: return launch_epi<32, true>(ta, tb, p, grid, st);
+            case 64: return launch_epi<64, true>(ta, tb, p, grid, st);
+            case 128: return launch_epi<128, true>(ta, tb, p, grid, st);
+        }
+    } else if (bn == 128) {
+        return launch_epi<128, false>(ta, tb, p, grid, st);
+    }
+    set_error("kx_gemm: unsupported tile width %d (swap=%d)", bn, p.swap);
+    return KX_EINVAL;
+}
+
+}  // namespace kx
+
+// Stand-alone GEMM entry point (tests, and any caller that wants the op by itself).
+extern "C" int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, int64_t b_rows, int64_t ldb,
+                            int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
+                            void *stream) {
+    using namespace kx;
+    KX_REQUIRE(d_a && d_b && d_out, KX_EINVAL, "kx_gemm_bf16: NULL operand");
+    KX_REQUIRE(a_rows > 0 && b_rows > 0 && k > 0 && k % 8 == 0, KX_EINVAL, "kx_gemm_bf16: bad shape (k must be a multiple of 8)");
+    KX_REQUIRE(swap || b_rows % 8 == 0, KX_EINVAL, "kx_gemm_bf16: feature count must be a multiple of 8");
+    KX_REQUIRE(ldo % 8 == 0, KX_EINVAL, "kx_gemm_bf16: ldo must be a multiple of 8 elements");
+    KX_REQUIRE(epilogue != EPI_SWIGLU || (swap ? a_rows : b_rows) % 2 == 0, KX_EINVAL, "kx_gemm_bf16: SwiGLU needs (gate, up) pairs");
+    cudaStream_t st = (cudaStream_t)stream;
+    GemmParams p{};
+    p.a_rows = (int)a_rows; p.b_rows = (int)b_rows; p.k = k; p.out = d_out; p.ldo = (int)ldo; p.bias = d_bias;
+    p.swap = swap; p.epilogue = epilogue; p.splits = splits;
+    const int bn = gemm_pick_bn(swap, b_rows);
+    CUtensorMap ta, tb;
+    int rc = make_tmap_bf16_2d(&ta, d_a, a_rows, k, lda, BM);
+    if (rc != KX_OK) return rc;
+    rc = make_tmap_bf16_2d(&tb, d_b, b_rows, k, ldb, bn);
+    if (rc != KX_OK) return rc;
+    void *scratch = nullptr;
+    const size_t sb = gemm_scratch_bytes(p, bn);
+    if (sb) {
+        rc = stream_scratch(st, SCRATCH_GEMM, sb, &scratch, /*zero_on_alloc=*/true);
+        if (rc != KX_OK) return rc;
+    }
+    return gemm_launch(ta, tb, p, bn, scratch, st);
+}

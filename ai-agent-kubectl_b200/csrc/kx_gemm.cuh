@@ -1,0 +1,29 @@
+// Internal interface of the tcgen05 GEMM (kx_gemm.cu) used by the engine.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace kx {
+
+enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3 };
+
+struct GemmParams {
+    int a_rows, b_rows, k;   // D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T
+    void *out;
+    int ldo;                 // elements between consecutive output rows
+    const float *bias;       // per output feature, or NULL
+    int swap;                // 0: rows of A are output rows; 1: rows of A are features, out[b * ldo + feature]
+    int epilogue;
+    int splits;              // split-K factor requested (clamped to the number of 64-wide k blocks)
+    int kb_per_split;        // filled by gemm_launch
+    float *ws;               // split-K scratch, filled by gemm_launch
+    uint32_t *tickets;
+};
+
+int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+int gemm_pick_bn(int swap, int64_t b_rows);
+size_t gemm_scratch_bytes(const GemmParams &p, int bn);
+int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int bn, void *scratch, cudaStream_t st);
+
+}  // namespace kx

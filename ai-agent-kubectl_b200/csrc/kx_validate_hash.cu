@@ -178,7 +178,7 @@ extern "C" int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int
     for (int64_t r0 = 0; r0 < n; r0 += kMaxStringsPerLaunch) {
         const int64_t rows = min(n - r0, kMaxStringsPerLaunch);
         uint32_t *queue = nullptr;
-        int rc = kx::stream_scratch(st, sizeof(uint32_t) * (size_t)(rows + 2), (void **)&queue);
+        int rc = kx::stream_scratch(st, kx::SCRATCH_K9_QUEUE, sizeof(uint32_t) * (size_t)(rows + 2), (void **)&queue);
         if (rc != KX_OK) return rc;
         rc = launch_passes(d_data, d_off + r0, rows, flags, d_verdict ? d_verdict + r0 : nullptr,
                            d_hash ? d_hash + r0 : nullptr, d_span ? d_span + 2 * r0 : nullptr, d_san,

@@ -91,6 +91,33 @@ int kx_validate_hash_host(const uint8_t *h_data, const int64_t *h_off, int64_t n
                           uint8_t *h_san, int32_t *h_san_len, int device);
 void kx_release_host_staging(void);
 
+/* ------------------------------------------------------------------------- *
+ * Generator.  The reference has no code for these: its
+ * `llm` slot is ChatOpenAI (app.py:108-117), a remote service; BASELINE.json's
+ * north_star defines the kernels.  What they replace is that slot.
+ * ------------------------------------------------------------------------- */
+
+/* epilogues of kx_gemm_bf16 */
+#define KX_EPI_BF16      0   /* out bf16 = acc (+ bias[feature])                       */
+#define KX_EPI_RESID     1   /* out fp32 += acc   (residual stream)                    */
+#define KX_EPI_SWIGLU    2   /* features are (gate, up) pairs: out bf16[f/2] = silu(g)*u */
+#define KX_EPI_F32       3   /* out fp32 = acc    (logits)                             */
+
+/*
+ * kx_gemm_bf16 -- D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T on tcgen05 tensor
+ * cores (bf16 inputs with k contiguous, row pitches lda / ldb elements, fp32
+ * accumulation in TMEM), with a fused epilogue.
+ *   swap = 0 (prefill): A = activations, B = weights; out[i * ldo + j], feature = j.
+ *   swap = 1 (decode) : A = weights, B = activations (batch <= any); out[j * ldo + i],
+ *                       feature = i.  Every weight byte is read once.
+ * bias (fp32, per feature) may be NULL.  splits > 1 cuts k across CTAs (decode, few
+ * feature tiles); partial sums are reduced in library scratch (see kx_release_scratch).
+ * k % 8 == 0, ldo % 8 == 0, operands 16-byte aligned.
+ */
+int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, int64_t b_rows, int64_t ldb,
+                 int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
+                 void *stream);
+
 /* frees the device scratch the library caches per (device, stream): the queue
  * kx_validate_hash uses to hand strings from its fast pass to its general pass
  * (4 bytes per string of the largest batch seen on that stream) */
