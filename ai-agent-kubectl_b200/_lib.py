@@ -24,6 +24,7 @@ _SIGNATURES = {
     "kx_version": (c_int, []),
     "kx_launch_count": (c_int64, []),
     "kx_validate_hash": (c_int, [c_void_p, c_void_p, c_int64, c_uint32] + [c_void_p] * 6),
+    "kx_validate_hash_noalloc": (c_int, [c_void_p, c_void_p, c_int64, c_uint32] + [c_void_p] * 6),
     "kx_validate_hash_host": (c_int, [c_void_p, c_void_p, c_int64, c_uint32] + [c_void_p] * 5 + [c_int]),
     "kx_release_host_staging": (None, []),
     "kx_release_scratch": (None, []),

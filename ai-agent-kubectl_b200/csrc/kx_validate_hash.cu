@@ -14,6 +14,7 @@
 // (non-ASCII, fenced output in PARSE mode, CTAs whose byte range exceeds the staging
 // buffer) are appended to a queue in global scratch memory, and a second kernel runs
 // the general code-point path over that queue, packed densely over its threads.
+#include <atomic>
 #include "kx_common.cuh"
 #include "k9_core.cuh"
 
@@ -186,4 +187,59 @@ extern "C" int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int
         if (rc != KX_OK) return rc;
     }
     return KX_OK;
+}
+
+// ---------------------------------------------------------------------------
+// kx_validate_hash_noalloc: the same two passes, with the hand-over queue in a
+// fixed array that is part of the loaded module instead of cudaMalloc'ed scratch.
+//
+// Who needs this: a host process that cannot (or must not) allocate device memory
+// at call time.  Two cases we know of: a serving process whose framework allocator
+// has already reserved all of HBM for weights and KV cache, where a cudaMalloc from
+// a plugin simply fails; and a request loop with a latency budget, where
+// cudaMalloc's device-wide synchronisation would stall every other stream on the
+// GPU.  Such a caller passes inputs and outputs as usual and this entry point
+// touches no allocator at all (no cudaMalloc / cudaFree, no library pool).
+//
+// The price is a fixed capacity (KX_NOALLOC_MAX_STRINGS strings per call, about
+// 4 MB of device memory that every GPU loading the library holds until exit) and a
+// single shared array: two calls that overlap on one GPU (different streams or
+// threads) would race on it, so callers must serialise them.  The array keeps the
+// previous call's contents; the only part that has to start from zero, the queue's
+// element counter, is cleared on the stream at the start of every call.
+//
+// In host code `g_noalloc_queue` names a host-side shadow of the symbol, not device
+// memory, so the device address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and that pointer is what the
+// kernels receive.  The lookup happens in the first call on each device; make that
+// first call before any stream capture begins.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) uint32_t g_noalloc_queue[2 + KX_NOALLOC_MAX_STRINGS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<uint32_t *> g_noalloc_ptr[kMaxDevices];
+}  // namespace
+
+extern "C" int kx_validate_hash_noalloc(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32_t flags,
+                                        uint8_t *d_verdict, int64_t *d_hash, int32_t *d_span,
+                                        uint8_t *d_san, int32_t *d_san_len, void *stream) {
+    KX_REQUIRE(n >= 0, KX_EINVAL, "kx_validate_hash_noalloc: n = %lld is negative", (long long)n);
+    KX_REQUIRE((flags & ~KX_FLAG_PARSE) == 0, KX_EINVAL, "kx_validate_hash_noalloc: unknown flags 0x%x", flags);
+    KX_REQUIRE(n <= KX_NOALLOC_MAX_STRINGS, KX_ETOOBIG,
+               "kx_validate_hash_noalloc: n = %lld exceeds the %d strings its fixed scratch holds; "
+               "split the batch or call kx_validate_hash", (long long)n, KX_NOALLOC_MAX_STRINGS);
+    if (n == 0) return KX_OK;
+    KX_REQUIRE(d_off != nullptr, KX_EINVAL, "kx_validate_hash_noalloc: d_off is NULL");
+    int dev = 0;
+    KX_CUDA(cudaGetDevice(&dev));
+    KX_REQUIRE(dev >= 0 && dev < kMaxDevices, KX_EINVAL, "kx_validate_hash_noalloc: device ordinal %d not supported", dev);
+    uint32_t *queue = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (queue == nullptr) {
+        // once per device, with that device current: the symbol's address in device memory
+        KX_CUDA(cudaGetSymbolAddress((void **)&queue, g_noalloc_queue));
+        g_noalloc_ptr[dev].store(queue, std::memory_order_release);
+    }
+    return launch_passes(d_data, d_off, n, flags, d_verdict, d_hash, d_span, d_san, d_san_len, queue,
+                         (cudaStream_t)stream);
 }

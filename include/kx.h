@@ -78,6 +78,24 @@ int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int64_t n, uin
                      uint8_t *d_san, int32_t *d_san_len, void *stream);
 
 /*
+ * kx_validate_hash_noalloc -- kx_validate_hash for callers that cannot allocate device
+ * memory when they call (no counterpart in the reference; it exists for hosts whose
+ * allocator already owns all of HBM, or whose request loop cannot afford the device-wide
+ * synchronisation of cudaMalloc).  Same arguments and results as kx_validate_hash, but
+ * the scratch queue is a fixed array inside the library, so:
+ *   - n may be at most KX_NOALLOC_MAX_STRINGS per call (KX_ETOOBIG otherwise);
+ *   - the array (about 4 MB) is resident on every GPU that loads the library;
+ *   - all calls share it: calls that overlap on one GPU race, so serialise them;
+ *   - no cudaMalloc, cudaFree or pool allocation happens in this call;
+ *   - the first call on each device looks up the array's device address; make that
+ *     call before any stream capture starts.
+ */
+#define KX_NOALLOC_MAX_STRINGS (1 << 20)
+int kx_validate_hash_noalloc(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32_t flags,
+                             uint8_t *d_verdict, int64_t *d_hash, int32_t *d_span,
+                             uint8_t *d_san, int32_t *d_san_len, void *stream);
+
+/*
  * kx_validate_hash_host -- same contract with HOST buffers: copies the batch to
  * `device` in chunks over two streams (copy of chunk k+1 overlaps the kernel on
  * chunk k), runs kx_validate_hash and copies the requested outputs back.
