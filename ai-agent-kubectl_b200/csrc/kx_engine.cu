@@ -1,0 +1,349 @@
+// Generation engine: orchestrates the kernels of kx_gemm.cu / kx_ops.cu for a
+// decoder-only transformer with a paged KV cache.  What it replaces in the reference
+// is the remote call behind `llm` (app.py:117, awaited at app.py:183-186); the model
+// math is defined by BASELINE.json's north_star, not by reference code.
+//
+// One engine = one model replica on one GPU.  Prefill runs over whole sequences in
+// chunks of at most `prefill_chunk` tokens; every decode step is the same sequence of
+// launches, so after the first (eager) step the rest are replayed as one CUDA graph
+// with the positions and the step counter advanced on the device.
+#include <vector>
+#include <cuda_bf16.h>
+#include "kx_common.cuh"
+#include "kx_gemm.cuh"
+#include "kx_ops.cuh"
+
+using namespace kx;
+
+struct LayerPlan {
+    kx_layer_weights w;
+    // weight maps in both roles: A operand (decode, 128-row box) and B operand (prefill, 128-row box)
+    CUtensorMap wqkv, wo, wgu, wd;
+    void *kv_pages;
+};
+
+struct kx_engine {
+    kx_model_desc d;
+    int qkv_dim, q_dim, max_pages, num_pages, max_tokens;
+    std::vector<LayerPlan> layers;
+    const void *embed, *lm_head, *norm;
+    const float *rope;
+    CUtensorMap lm_head_map;
+    // activations
+    float *resid = nullptr, *logits = nullptr;
+    __nv_bfloat16 *xn = nullptr, *qkv = nullptr, *attn = nullptr, *mlp = nullptr;
+    CUtensorMap xn_a, attn_a, mlp_a;               // as A operand (prefill)
+    CUtensorMap xn_b[3], attn_b[3], mlp_b[3];      // as B operand (decode), box rows 32 / 64 / 128
+    int *tokens = nullptr, *pos = nullptr, *seq = nullptr, *last_rows = nullptr, *next_tok = nullptr;
+    int *out_ids = nullptr, *block_table = nullptr, *step = nullptr;
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
+    cudaStream_t stream = nullptr;                 // the engine's own stream (the decode loop is captured on it)
+    int64_t device_bytes = 0;
+    std::vector<void *> owned;
+};
+
+namespace {
+
+int dev_alloc(kx_engine *e, void **p, size_t bytes) {
+    KX_CUDA(cudaMalloc(p, bytes));
+    e->owned.push_back(*p);
+    e->device_bytes += (int64_t)bytes;
+    return KX_OK;
+}
+
+#define KX_TRY(x) do { int rc__ = (x); if (rc__ != KX_OK) return rc__; } while (0)
+
+int bn_index(int bn) { return bn == 32 ? 0 : bn == 64 ? 1 : 2; }
+
+// decode split-K factor: enough CTAs to keep every SM streaming weights
+int pick_splits(int features, int k, int b_tiles) {
+    const int tiles = ((features + 127) / 128) * b_tiles;
+    const int kb = (k + 63) / 64;
+    int s = (296 + tiles - 1) / tiles;
+    if (s > kb) s = kb;
+    if (s < 1) s = 1;
+    return s;
+}
+
+__global__ void advance_step_kernel(int *pos, int *step, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) pos[i] += 1;
+    if (i == 0) *step += 1;
+}
+
+__global__ void store_token_kernel(const int *next_tok, int *out_ids, const int *step, int B, int n_new) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) out_ids[(size_t)b * n_new + *step] = next_tok[b];
+}
+
+struct GemmCall {
+    const CUtensorMap *a, *b;
+    int a_rows, b_rows, k, epi, swap, splits, bn;
+    void *out; int ldo; const float *bias;
+};
+
+int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
+    GemmParams p{};
+    p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
+    p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits;
+    KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
+    return gemm_launch(*c.a, *c.b, p, c.bn, e->scratch, st);
+}
+
+// One transformer layer over M token rows.  decode: rows are one token per sequence.
+int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    LayerPlan &L = e->layers[li];
+    const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
+    const int b_tiles = (M + bn - 1) / bn;
+    KX_TRY(op_rmsnorm(e->resid, L.w.ln1, e->xn, M, d.hidden, d.eps, nullptr, st));
+    if (decode)
+        KX_TRY(run_gemm(e, {&L.wqkv, &e->xn_b[bi], e->qkv_dim, M, d.hidden, EPI_BF16, 1,
+                            pick_splits(e->qkv_dim, d.hidden, b_tiles), bn, e->qkv, e->qkv_dim, L.w.bqkv}, st));
+    else
+        KX_TRY(run_gemm(e, {&e->xn_a, &L.wqkv, M, e->qkv_dim, d.hidden, EPI_BF16, 0, 1, 128, e->qkv, e->qkv_dim, L.w.bqkv}, st));
+    KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
+                          d.n_q, d.n_kv, d.head_dim, st));
+    if (decode)
+        KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos, M,
+                              max_T, d.n_q, d.n_kv, d.head_dim, st));
+    else
+        KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
+                               e->max_pages, nb, S, 0, d.n_q, d.n_kv, d.head_dim, st));
+    if (decode) {
+        KX_TRY(run_gemm(e, {&L.wo, &e->attn_b[bi], d.hidden, M, e->q_dim, EPI_RESID, 1,
+                            pick_splits(d.hidden, e->q_dim, b_tiles), bn, e->resid, d.hidden, nullptr}, st));
+        KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
+        KX_TRY(run_gemm(e, {&L.wgu, &e->xn_b[bi], 2 * d.inter, M, d.hidden, EPI_SWIGLU, 1,
+                            pick_splits(2 * d.inter, d.hidden, b_tiles), bn, e->mlp, d.inter, nullptr}, st));
+        KX_TRY(run_gemm(e, {&L.wd, &e->mlp_b[bi], d.hidden, M, d.inter, EPI_RESID, 1,
+                            pick_splits(d.hidden, d.inter, b_tiles), bn, e->resid, d.hidden, nullptr}, st));
+    } else {
+        KX_TRY(run_gemm(e, {&e->attn_a, &L.wo, M, d.hidden, e->q_dim, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr}, st));
+        KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
+        KX_TRY(run_gemm(e, {&e->xn_a, &L.wgu, M, 2 * d.inter, d.hidden, EPI_SWIGLU, 0, 1, 128, e->mlp, d.inter, nullptr}, st));
+        KX_TRY(run_gemm(e, {&e->mlp_a, &L.wd, M, d.hidden, d.inter, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr}, st));
+    }
+    return KX_OK;
+}
+
+// final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
+int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    const int bn = gemm_pick_bn(1, B), bi = bn_index(bn);
+    KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, B, d.hidden, d.eps, row_map, st));
+    KX_TRY(run_gemm(e, {&e->lm_head_map, &e->xn_b[bi], d.vocab, B, d.hidden, EPI_F32, 1, 1, bn, e->logits, d.vocab, nullptr}, st));
+    if (d_logits_step)
+        KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
+    KX_TRY(op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st));
+    store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+}  // namespace
+
+extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weights *w, kx_engine **out) {
+    KX_REQUIRE(desc && w && out, KX_EINVAL, "kx_engine_create: NULL argument");
+    const kx_model_desc &d = *desc;
+    KX_REQUIRE(d.head_dim == 64 || d.head_dim == 128, KX_EINVAL, "kx_engine_create: head_dim must be 64 or 128");
+    KX_REQUIRE(d.hidden % 128 == 0 && d.inter % 8 == 0 && d.vocab % 8 == 0, KX_EINVAL,
+               "kx_engine_create: hidden must be a multiple of 128, inter and vocab of 8");
+    KX_REQUIRE(d.n_q % d.n_kv == 0, KX_EINVAL, "kx_engine_create: n_q must be a multiple of n_kv");
+    KX_REQUIRE(d.max_seq <= d.max_pos, KX_EINVAL, "kx_engine_create: max_seq exceeds the rope table");
+    kx_engine *e = new kx_engine();
+    e->d = d;
+    if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
+    e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
+    e->q_dim = d.n_q * d.head_dim;
+    e->max_pages = (d.max_seq + KX_KV_PAGE - 1) / KX_KV_PAGE;
+    e->num_pages = e->max_pages * d.max_batch;
+    if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { delete e; set_error("kx_engine_create: cannot create a stream"); return KX_ECUDA; }
+    e->embed = w->embed; e->lm_head = w->lm_head; e->norm = w->norm; e->rope = w->rope;
+    // prefill works on whole sequences, so the token buffers hold at least one chunk or one full batch of prompts
+    e->max_tokens = e->d.prefill_chunk > d.max_batch ? e->d.prefill_chunk : d.max_batch;
+    if (e->max_tokens < d.max_seq) e->max_tokens = d.max_seq;
+    const size_t Mx = (size_t)e->max_tokens;
+    int rc = KX_OK;
+    auto fail = [&](int code) { kx_engine_destroy(e); return code; };
+#define KX_E(x) do { rc = (x); if (rc != KX_OK) return fail(rc); } while (0)
+    KX_E(dev_alloc(e, (void **)&e->resid, Mx * d.hidden * 4));
+    KX_E(dev_alloc(e, (void **)&e->xn, Mx * d.hidden * 2));
+    KX_E(dev_alloc(e, (void **)&e->qkv, Mx * e->qkv_dim * 2));
+    KX_E(dev_alloc(e, (void **)&e->attn, Mx * e->q_dim * 2));
+    KX_E(dev_alloc(e, (void **)&e->mlp, Mx * d.inter * 2));
+    KX_E(dev_alloc(e, (void **)&e->logits, (size_t)d.max_batch * d.vocab * 4));
+    KX_E(dev_alloc(e, (void **)&e->tokens, Mx * 4));
+    KX_E(dev_alloc(e, (void **)&e->pos, Mx * 4));
+    KX_E(dev_alloc(e, (void **)&e->seq, Mx * 4));
+    KX_E(dev_alloc(e, (void **)&e->last_rows, (size_t)d.max_batch * 4));
+    KX_E(dev_alloc(e, (void **)&e->next_tok, (size_t)d.max_batch * 4));
+    KX_E(dev_alloc(e, (void **)&e->out_ids, (size_t)d.max_batch * d.max_seq * 4));
+    KX_E(dev_alloc(e, (void **)&e->block_table, (size_t)d.max_batch * e->max_pages * 4));
+    KX_E(dev_alloc(e, (void **)&e->step, 4));
+    // split-K scratch for the largest decode GEMM: tiles * 128 * bn floats + tickets
+    {
+        size_t best = 0;
+        const int feats[3] = {e->qkv_dim, d.hidden, 2 * d.inter};   // lm_head never splits
+        for (int f : feats) {
+            const size_t tiles = (size_t)((f + 127) / 128) * (size_t)((d.max_batch + 127) / 128 + 1);
+            const size_t b = tiles * 128 * 128 * 4 + tiles * 4;
+            if (b > best) best = b;
+        }
+        e->scratch_bytes = best;
+        KX_E(dev_alloc(e, &e->scratch, best));
+        if (cudaMemset(e->scratch, 0, best) != cudaSuccess) return fail(KX_ECUDA);
+    }
+    // static block table: sequence b owns pages [b * max_pages, (b+1) * max_pages)
+    {
+        std::vector<int> bt((size_t)d.max_batch * e->max_pages);
+        for (size_t i = 0; i < bt.size(); ++i) bt[i] = (int)i;
+        if (cudaMemcpy(e->block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) return fail(KX_ECUDA);
+    }
+    const size_t page_bytes = (size_t)2 * d.n_kv * KX_KV_PAGE * d.head_dim * 2;
+    e->layers.resize(d.layers);
+    for (int i = 0; i < d.layers; ++i) {
+        LayerPlan &L = e->layers[i];
+        L.w = w->layers[i];
+        KX_E(dev_alloc(e, &L.kv_pages, page_bytes * e->num_pages));
+        KX_E(make_tmap_bf16_2d(&L.wqkv, L.w.wqkv, e->qkv_dim, d.hidden, d.hidden, 128));
+        KX_E(make_tmap_bf16_2d(&L.wo, L.w.wo, d.hidden, e->q_dim, e->q_dim, 128));
+        KX_E(make_tmap_bf16_2d(&L.wgu, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, 128));
+        KX_E(make_tmap_bf16_2d(&L.wd, L.w.wd, d.hidden, d.inter, d.inter, 128));
+    }
+    KX_E(make_tmap_bf16_2d(&e->lm_head_map, e->lm_head, d.vocab, d.hidden, d.hidden, 128));
+    KX_E(make_tmap_bf16_2d(&e->xn_a, e->xn, Mx, d.hidden, d.hidden, 128));
+    KX_E(make_tmap_bf16_2d(&e->attn_a, e->attn, Mx, e->q_dim, e->q_dim, 128));
+    KX_E(make_tmap_bf16_2d(&e->mlp_a, e->mlp, Mx, d.inter, d.inter, 128));
+    const int bns[3] = {32, 64, 128};
+    for (int j = 0; j < 3; ++j) {
+        KX_E(make_tmap_bf16_2d(&e->xn_b[j], e->xn, Mx, d.hidden, d.hidden, bns[j]));
+        KX_E(make_tmap_bf16_2d(&e->attn_b[j], e->attn, Mx, e->q_dim, e->q_dim, bns[j]));
+        KX_E(make_tmap_bf16_2d(&e->mlp_b[j], e->mlp, Mx, d.inter, d.inter, bns[j]));
+    }
+#undef KX_E
+    *out = e;
+    return KX_OK;
+}
+
+extern "C" void kx_engine_destroy(kx_engine *e) {
+    if (!e) return;
+    for (void *p : e->owned) cudaFree(p);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+extern "C" int64_t kx_engine_device_bytes(const kx_engine *e) { return e ? e->device_bytes : 0; }
+
+extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t B, int32_t S, int32_t n_new,
+                                  int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream) {
+    KX_REQUIRE(e && h_tokens && h_out, KX_EINVAL, "kx_engine_generate: NULL argument");
+    const kx_model_desc &d = e->d;
+    KX_REQUIRE(B >= 1 && B <= d.max_batch, KX_ETOOBIG, "kx_engine_generate: batch %d exceeds max_batch %d", B, d.max_batch);
+    KX_REQUIRE(S >= 1 && n_new >= 1 && S + n_new <= d.max_seq, KX_ETOOBIG,
+               "kx_engine_generate: %d prompt + %d new tokens exceed max_seq %d", S, n_new, d.max_seq);
+    // Work runs on the engine's own stream (a legacy default stream cannot be captured into a
+    // graph); it is ordered after whatever the caller already enqueued on `stream`.
+    cudaStream_t st = e->stream;
+    const int64_t launches0 = kx_launch_count();
+    cudaEvent_t ev0, ev1, ev2;
+    KX_CUDA(cudaEventCreate(&ev0)); KX_CUDA(cudaEventCreate(&ev1)); KX_CUDA(cudaEventCreate(&ev2));
+    KX_CUDA(cudaEventRecord(ev0, (cudaStream_t)stream));
+    KX_CUDA(cudaStreamWaitEvent(st, ev0, 0));
+    KX_CUDA(cudaMemsetAsync(e->step, 0, 4, st));
+    KX_CUDA(cudaEventRecord(ev0, st));
+
+    // ---- prefill, whole sequences per chunk ----
+    int seqs_per_chunk = d.prefill_chunk / S;
+    if (seqs_per_chunk < 1) seqs_per_chunk = 1;
+    KX_REQUIRE((int64_t)seqs_per_chunk * S <= e->max_tokens || S <= e->max_tokens, KX_ETOOBIG, "kx_engine_generate: prompt too long");
+    if ((int64_t)seqs_per_chunk * S > e->max_tokens) seqs_per_chunk = e->max_tokens / S;
+    std::vector<int> hpos, hseq;
+    for (int b0 = 0; b0 < B; b0 += seqs_per_chunk) {
+        const int nb = (B - b0 < seqs_per_chunk) ? B - b0 : seqs_per_chunk;
+        const int M = nb * S;
+        hpos.resize(M); hseq.resize(M);
+        for (int b = 0; b < nb; ++b)
+            for (int t = 0; t < S; ++t) { hpos[b * S + t] = t; hseq[b * S + t] = b0 + b; }
+        KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens + (size_t)b0 * S, (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaStreamSynchronize(st));          // hpos/hseq are reused by the next chunk
+        KX_TRY(op_embed(e->tokens, e->embed, e->resid, M, d.hidden, st));
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, b0, 0, st));
+        // first token of this chunk's sequences: final norm on each last prompt row
+        std::vector<int> rows(nb);
+        for (int b = 0; b < nb; ++b) rows[b] = b * S + S - 1;
+        KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaStreamSynchronize(st));
+        {
+            const int bn = gemm_pick_bn(1, nb), bi = bn_index(bn);
+            KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, nb, d.hidden, d.eps, e->last_rows, st));
+            KX_TRY(run_gemm(e, {&e->lm_head_map, &e->xn_b[bi], d.vocab, nb, d.hidden, EPI_F32, 1, 1, bn,
+                                e->logits + (size_t)b0 * d.vocab, d.vocab, nullptr}, st));
+        }
+    }
+    if (d_logits) KX_CUDA(cudaMemcpyAsync(d_logits, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
+    KX_TRY(op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st));
+    store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
+    count_launch();
+    KX_CUDA(cudaEventRecord(ev1, st));
+
+    // ---- decode: positions S, S+1, ... one token per sequence ----
+    {
+        std::vector<int> p0(B, S - 1), sq(B);          // advance_step_kernel moves to S before the first use
+        for (int b = 0; b < B; ++b) sq[b] = b;
+        KX_CUDA(cudaMemcpyAsync(e->pos, p0.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaMemcpyAsync(e->seq, sq.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaStreamSynchronize(st));
+    }
+    const int max_T = S + n_new;
+    auto step_once = [&](float *logits_dst) -> int {
+        // pos[b] currently holds the previous token's position
+        advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);
+        count_launch();
+        KX_TRY(op_embed(e->next_tok, e->embed, e->resid, B, d.hidden, st));
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, max_T, st));
+        KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st));
+        return KX_OK;
+    };
+    int steps_done = 0;
+    if (n_new > 1) {
+        KX_TRY(step_once(d_logits ? d_logits + (size_t)1 * B * d.vocab : nullptr));   // eager: also sets kernel attributes
+        steps_done = 1;
+    }
+    if (n_new > 2) {
+        if (d_logits) {
+            for (int t = 2; t < n_new; ++t) KX_TRY(step_once(d_logits + (size_t)t * B * d.vocab));
+        } else {
+            cudaGraph_t graph = nullptr;
+            cudaGraphExec_t exec = nullptr;
+            const int64_t l0 = kx_launch_count();
+            KX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            int rc = step_once(nullptr);
+            cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (rc != KX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+            KX_CUDA(ce);
+            const int64_t per_step = kx_launch_count() - l0;
+            KX_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+            for (int t = 2; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(exec, st));
+            count_launch((int)(per_step * (n_new - 3)));      // the capture itself was counted once
+            cudaGraphExecDestroy(exec);
+            cudaGraphDestroy(graph);
+        }
+        steps_done = n_new - 1;
+    }
+    KX_CUDA(cudaEventRecord(ev2, st));
+    KX_CUDA(cudaMemcpyAsync(h_out, e->out_ids, (size_t)B * n_new * 4, cudaMemcpyDeviceToHost, st));
+    KX_CUDA(cudaStreamSynchronize(st));
+    if (stats) {
+        cudaEventElapsedTime(&stats->prefill_ms, ev0, ev1);
+        cudaEventElapsedTime(&stats->decode_ms, ev1, ev2);
+        stats->decode_steps = steps_done;
+        stats->launches = (int32_t)(kx_launch_count() - launches0);
+    }
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
+    return KX_OK;
+}

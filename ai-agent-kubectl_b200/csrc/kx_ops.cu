@@ -126,7 +126,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
     float *qs = sm;                                   // [G][HD]
     float *sc = qs + G * HD;                          // [G][Tpad]
     const int Tpad = (T + 31) & ~31;
-    float *red = sc + G * Tpad;                       // [G][4] + [G][HD][2] scratch
+    float *red = sc + G * Tpad;                       // [G] 1/sum, then [KG][G][HD] partial outputs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     for (int i = tid; i < G * HD; i += 128) {
@@ -180,7 +180,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
 
     // output: thread = (key parity group, dim pair); V rows are read as contiguous 2*HD bytes
     constexpr int DP = HD / 2;                       // dim pairs
-    constexpr int KG = 128 / DP;                     // key groups (2 for HD 64, 1... for HD 128 -> 2)
+    constexpr int KG = 128 / DP;                     // key groups: 4 for HD 64, 2 for HD 128
     const int dp = tid % DP, kg = tid / DP;
     float o[G][2];
 #pragma unroll
@@ -420,7 +420,11 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
 #define KX_DEC(GV)                                                                                          \
     case GV: {                                                                                              \
         auto k = attn_decode_kernel<HD, GV>;                                                                \
-        if (smem > 48 * 1024) KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        static size_t granted = 48 * 1024;   /* raised outside any stream capture by the first, eager call */  \
+        if (smem > granted) {                                                                               \
+            KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+            granted = smem;                                                                                 \
+        }                                                                                                   \
         k<<<grid, 128, smem, st>>>(qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, n_q, n_kv, scale);   \
         break;                                                                                              \
     }
@@ -463,7 +467,8 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, const voi
                    int max_pages, const int *pos, int B, int max_T, int n_q, int n_kv, int hd, cudaStream_t st) {
     const int G = n_q / n_kv;
     const int Tpad = (max_T + 31) & ~31;
-    const size_t smem = sizeof(float) * ((size_t)G * hd + (size_t)G * Tpad + G + 2 * (size_t)G * hd + 8);
+    const int KG = 128 / (hd / 2);                                  // key groups of the PV pass
+    const size_t smem = sizeof(float) * ((size_t)G * hd + (size_t)G * Tpad + G + (size_t)KG * G * hd + 8);
     KX_REQUIRE(smem <= 200 * 1024, KX_ETOOBIG, "attention: context of %d tokens exceeds the decode kernel's shared memory", max_T);
     const float scale = 1.0f / sqrtf((float)hd);
     dim3 grid(n_kv, B);
@@ -493,7 +498,8 @@ int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const vo
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else if (hd == 128) {
         auto k = attn_prefill_kernel<128>;
-        KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 64 * 128 * 2));
+        static bool granted = false;
+        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 64 * 128 * 2)); granted = true; }
         k<<<grid, 128, 3 * 64 * 128 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else {

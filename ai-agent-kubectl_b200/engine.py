@@ -1,6 +1,148 @@
-"""Generation engine behind ``B200ChatModel`` (placeholder until generator lands)."""
+"""Generation engine behind ``B200ChatModel``: random-init weights of a named
+architecture packed for the CUDA kernels, and ``generate`` over the C ABI
+(``kx_engine_create`` / ``kx_engine_generate`` in include/kx.h).
+
+torch is used for device memory only (weights live in torch tensors; the library
+receives raw pointers).  There is no CPU path: creating an engine without a CUDA
+device raises.
+"""
 from __future__ import annotations
 
+import ctypes
+from typing import Dict, List, Optional, Sequence
 
-def default_engine_factory(arch: str):
-    raise RuntimeError("the CUDA generator engine is not available in this build")
+import numpy as np
+
+from . import _lib, tokenizer, weights as weights_mod
+from .chat_model import Engine
+from .model_config import ModelConfig, get_config
+
+c_int32, c_float, c_void_p = ctypes.c_int32, ctypes.c_float, ctypes.c_void_p
+
+
+class KxModelDesc(ctypes.Structure):
+    _fields_ = [(n, c_int32) for n in ("hidden", "layers", "n_q", "n_kv", "head_dim", "inter", "vocab", "max_pos")] + \
+               [("eps", c_float), ("max_batch", c_int32), ("max_seq", c_int32), ("prefill_chunk", c_int32)]
+
+
+class KxLayerWeights(ctypes.Structure):
+    _fields_ = [(n, c_void_p) for n in ("ln1", "wqkv", "bqkv", "wo", "ln2", "wgu", "wd")]
+
+
+class KxModelWeights(ctypes.Structure):
+    _fields_ = [("embed", c_void_p), ("lm_head", c_void_p), ("norm", c_void_p), ("rope", c_void_p),
+                ("layers", ctypes.POINTER(KxLayerWeights))]
+
+
+class KxGenStats(ctypes.Structure):
+    _fields_ = [("prefill_ms", c_float), ("decode_ms", c_float), ("decode_steps", c_int32), ("launches", c_int32)]
+
+
+_lib.declare("kx_engine_create", ctypes.c_int, [ctypes.POINTER(KxModelDesc), ctypes.POINTER(KxModelWeights),
+                                                 ctypes.POINTER(c_void_p)])
+_lib.declare("kx_engine_destroy", None, [c_void_p])
+_lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
+_lib.declare("kx_engine_generate", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p,
+                                                   ctypes.POINTER(KxGenStats), c_void_p])
+
+
+def pack_weights(cfg: ModelConfig, w: Dict, device) -> Dict:
+    """Logical tensors (weights.make_weights) -> the layouts of include/kx.h on `device`."""
+    import torch
+    out = {"embed": w["embed"].to(device), "norm": w["norm"].to(device), "layers": []}
+    out["lm_head"] = out["embed"] if cfg.tied else w["lm_head"].to(device)
+    for i in range(cfg.layers):
+        wgu = torch.stack([w[f"wg.{i}"], w[f"wu.{i}"]], dim=1).reshape(2 * cfg.inter, cfg.hidden)   # rows g0,u0,g1,u1,...
+        layer = {
+            "ln1": w[f"ln1.{i}"].to(device), "ln2": w[f"ln2.{i}"].to(device),
+            "wqkv": torch.cat([w[f"wq.{i}"], w[f"wk.{i}"], w[f"wv.{i}"]], dim=0).contiguous().to(device),
+            "bqkv": (torch.cat([w[f"bq.{i}"], w[f"bk.{i}"], w[f"bv.{i}"]]).float().to(device) if cfg.qkv_bias else None),
+            "wo": w[f"wo.{i}"].contiguous().to(device), "wgu": wgu.contiguous().to(device),
+            "wd": w[f"wd.{i}"].contiguous().to(device),
+        }
+        out["layers"].append(layer)
+    return out
+
+
+class Generator:
+    """One model replica on one GPU."""
+
+    def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, max_seq: int = 320, device: int = 0,
+                 weights: Optional[Dict] = None, prefill_chunk: int = 32768):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("the generator needs a CUDA device; there is no CPU fallback")
+        self.cfg = get_config(arch)
+        self.device = torch.device("cuda", device)
+        self.max_batch, self.max_seq = max_batch, max_seq
+        self.logical = weights if weights is not None else weights_mod.make_weights(self.cfg, seed)
+        with torch.cuda.device(self.device):
+            self.packed = pack_weights(self.cfg, self.logical, self.device)
+            self.rope = weights_mod.rope_table(self.cfg, self.cfg.max_pos).to(self.device)
+            c = self.cfg
+            desc = KxModelDesc(c.hidden, c.layers, c.n_q, c.n_kv, c.head_dim, c.inter, c.vocab, c.max_pos, c.eps,
+                               max_batch, max_seq, prefill_chunk)
+            arr = (KxLayerWeights * c.layers)()
+            for i, l in enumerate(self.packed["layers"]):
+                arr[i] = KxLayerWeights(l["ln1"].data_ptr(), l["wqkv"].data_ptr(),
+                                        l["bqkv"].data_ptr() if l["bqkv"] is not None else None, l["wo"].data_ptr(),
+                                        l["ln2"].data_ptr(), l["wgu"].data_ptr(), l["wd"].data_ptr())
+            self._layer_array = arr
+            mw = KxModelWeights(self.packed["embed"].data_ptr(), self.packed["lm_head"].data_ptr(),
+                                self.packed["norm"].data_ptr(), self.rope.data_ptr(), arr)
+            h = c_void_p()
+            _lib.check(_lib.lib().kx_engine_create(ctypes.byref(desc), ctypes.byref(mw), ctypes.byref(h)))
+            self._h = h
+        self.last_stats: Optional[KxGenStats] = None
+
+    def device_bytes(self) -> int:
+        return int(_lib.lib().kx_engine_device_bytes(self._h))
+
+    def generate_ids(self, tokens: np.ndarray, n_new: int, want_logits: bool = False):
+        """tokens int32 [B, S] -> (ids int32 [B, n_new], logits torch fp32 [n_new, B, V] or None)."""
+        import torch
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        B, S = tokens.shape
+        out = np.empty((B, n_new), np.int32)
+        stats = KxGenStats()
+        with torch.cuda.device(self.device):
+            logits = torch.empty((n_new, B, self.cfg.vocab), dtype=torch.float32, device=self.device) if want_logits else None
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(_lib.lib().kx_engine_generate(self._h, tokens.ctypes.data, B, S, n_new, out.ctypes.data,
+                                                     logits.data_ptr() if want_logits else None, ctypes.byref(stats), st))
+        self.last_stats = stats
+        return out, logits
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.lib().kx_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class B200Engine(Engine):
+    """``chat_model.Engine`` over a ``Generator``: prompts are byte-tokenised and padded /
+    truncated to ``prompt_len`` tokens (BASELINE configs 3-4 use exactly 256), ``max_new``
+    tokens are decoded greedily and the ids are mapped back to text."""
+
+    def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
+                 device: int = 0):
+        self.gen = Generator(arch, seed=seed, max_batch=max_batch, max_seq=prompt_len + max_new, device=device)
+        self.max_batch, self.prompt_len, self.max_new = max_batch, prompt_len, max_new
+
+    def generate(self, prompts: Sequence[str], cancelled=None) -> List[str]:
+        toks = np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
+        ids, _ = self.gen.generate_ids(toks, self.max_new)
+        return [tokenizer.decode(row) for row in ids]
+
+    def close(self):
+        self.gen.close()
+
+
+def default_engine_factory(arch: str) -> Engine:
+    return B200Engine(arch)

@@ -136,6 +136,63 @@ int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, 
                  int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
                  void *stream);
 
+/*
+ * Generation engine: a decoder-only transformer (Llama / Qwen2 family) with a paged
+ * bf16 KV cache, greedy decoding (temperature 0, app.py:109).  This is what
+ * B200ChatModel (the occupant of the reference's `llm` slot, app.py:117-118) drives.
+ * All weight pointers are device pointers owned by the caller and must outlive the
+ * engine; layouts:
+ *   embed   bf16 [vocab, hidden]         lm_head bf16 [vocab, hidden] (= embed when tied)
+ *   norm    bf16 [hidden]                rope    fp32 [max_pos, head_dim/2, 2] (cos, sin)
+ *   per layer: ln1, ln2 bf16 [hidden]; wqkv bf16 [(n_q + 2 n_kv) head_dim, hidden]
+ *   (q heads, then k heads, then v heads); bqkv fp32 [same rows] or NULL;
+ *   wo bf16 [hidden, n_q head_dim]; wgu bf16 [2 inter, hidden] with rows interleaved
+ *   (gate_0, up_0, gate_1, up_1, ...); wd bf16 [hidden, inter].
+ */
+typedef struct kx_model_desc {
+    int32_t hidden, layers, n_q, n_kv, head_dim, inter, vocab;
+    int32_t max_pos;        /* rows of the rope table                                  */
+    float   eps;
+    int32_t max_batch;      /* sequences resident at once                              */
+    int32_t max_seq;        /* prompt + generated tokens per sequence                  */
+    int32_t prefill_chunk;  /* max tokens per prefill pass (0 = default 32768)         */
+} kx_model_desc;
+
+typedef struct kx_layer_weights {
+    const void *ln1, *wqkv;
+    const float *bqkv;
+    const void *wo, *ln2, *wgu, *wd;
+} kx_layer_weights;
+
+typedef struct kx_model_weights {
+    const void *embed, *lm_head, *norm;
+    const float *rope;
+    const kx_layer_weights *layers;   /* host array of `layers` entries */
+} kx_model_weights;
+
+typedef struct kx_gen_stats {
+    float prefill_ms;      /* enqueue -> first token of every sequence (device time)  */
+    float decode_ms;       /* all remaining steps                                      */
+    int32_t decode_steps;
+    int32_t launches;      /* kernels launched by this call (graph replays counted)    */
+} kx_gen_stats;
+
+typedef struct kx_engine kx_engine;
+
+int kx_engine_create(const kx_model_desc *desc, const kx_model_weights *weights, kx_engine **out);
+void kx_engine_destroy(kx_engine *e);
+int64_t kx_engine_device_bytes(const kx_engine *e);
+
+/*
+ * kx_engine_generate -- prefill `batch` prompts of `prompt_len` tokens each (host int32
+ * [batch, prompt_len]) and decode `n_new` tokens greedily; h_out receives int32
+ * [batch, n_new].  d_logits (device fp32 [n_new, batch, vocab]) may be NULL; when given,
+ * the logits that produced every token are kept (for the parity tests) and the decode
+ * loop is launched kernel by kernel instead of as a CUDA graph.  Blocks until done.
+ */
+int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t batch, int32_t prompt_len, int32_t n_new,
+                       int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream);
+
 /* frees the device scratch the library caches per (device, stream): the queue
  * kx_validate_hash uses to hand strings from its fast pass to its general pass
  * (4 bytes per string of the largest batch seen on that stream) */

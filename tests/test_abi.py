@@ -7,7 +7,7 @@ import re
 from conftest import ROOT
 
 import kubectl_b200  # noqa: F401
-from kubectl_b200 import _lib, build
+from kubectl_b200 import _lib, build, engine  # noqa: F401  (engine registers its entry points)
 
 
 def declared_symbols():
