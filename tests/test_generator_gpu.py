@@ -1,6 +1,6 @@
 """Generator parity (BASELINE.json's three checks) on small architectures:
-  1. greedy token ids equal to the CPU oracle's (bf16-emulating mode; any differing
-     position must be a near-tie of the oracle's top two logits),
+  1. greedy token ids equal to the CPU oracle's (bf16-emulating mode); a position may
+     differ only where the oracle's top-2 margin is below twice the measured bf16 noise,
   2. logits within 1e-2 (relative to the largest logit) of the pure-fp32 CPU oracle
      evaluated on the same token history,
 through the C ABI (kx_engine_create / kx_engine_generate)."""
@@ -41,24 +41,38 @@ def _check(arch, B, S, n_new, seed=3):
         err = (logits[t] - full[:, t]).abs().max().item() / full[:, t].abs().max().item()
         worst = max(worst, err)
     assert worst <= 1e-2, f"logits off by {worst:.3e} relative"
-    # (1) greedy ids vs the bf16-emulating oracle
-    mism = 0
-    for b in range(B):
-        for t in range(n_new):
+    # (1) greedy ids vs the bf16-emulating oracle.  bf16 GEMM inputs put a noise floor on the logits
+    # (measured here, per step, as the largest |gpu - oracle| logit difference over sequences whose
+    # histories are still identical; it must itself stay within the 1e-2 bound).  Ids must be equal
+    # wherever the oracle's top-2 margin exceeds that noise; a flip is only accepted below 2x the noise.
+    alive = np.ones(B, bool)
+    mism, min_margin = 0, float("inf")
+    for t in range(n_new):
+        if not alive.any():
+            break
+        wl = want_logits[t]
+        noise = (logits[t][alive] - wl[alive]).abs().max().item()
+        scale = wl.abs().max().item()
+        assert noise <= 1e-2 * scale, f"step {t}: logits differ from the emulating oracle by {noise / scale:.2e}"
+        top2 = wl.topk(2, dim=-1).values
+        margin = (top2[:, 0] - top2[:, 1]).numpy()
+        min_margin = min(min_margin, float(margin[alive].min()))
+        for b in np.flatnonzero(alive):
             if ids[b, t] != want_ids[b, t]:
-                top2 = want_logits[t][b].topk(2).values
-                margin = (top2[0] - top2[1]).item() / want_logits[t][b].abs().max().item()
-                assert margin < 2e-3, f"seq {b} step {t}: ids differ with oracle margin {margin:.2e}"
+                assert margin[b] <= 2 * noise, \
+                    f"seq {b} step {t}: ids differ although the oracle margin {margin[b]:.3e} exceeds the noise {noise:.3e}"
+                alive[b] = False
                 mism += 1
-                break                                                            # histories diverge after this
-    assert mism <= max(1, B // 16), f"{mism} of {B} sequences hit a near-tie"
+    print(f"{arch}: {B - mism}/{B} sequences identical for {n_new} tokens, min top-2 margin {min_margin:.2e}, "
+          f"worst logit error vs fp32 {worst:.2e}")
     gen.close()
     return worst, mism
 
 
 @pytest.mark.parametrize("arch", ["tiny-qwen2", "tiny-llama", "tiny-llama-hd128"])
 def test_small_batch_ragged_block_sizes(arch):
-    _check(arch, B=5, S=70, n_new=8)
+    _, mism = _check(arch, B=5, S=70, n_new=8)
+    assert mism == 0
 
 
 def test_config3_shape_on_tiny_model():
@@ -68,3 +82,10 @@ def test_config3_shape_on_tiny_model():
 def test_batch_above_one_tile_and_chunked_prefill():
     import kubectl_b200  # noqa: F401
     _check("tiny-llama", B=150, S=64, n_new=6)
+
+
+def test_qwen25_05b_full_architecture():
+    """BASELINE configs[2] architecture at full size (151,936-token vocabulary, 24 layers, GQA 14/2,
+    q/k/v biases), 256-token prompts, 32 greedy tokens, on a subset of the batch the CPU oracle
+    can finish in seconds."""
+    _check("qwen2.5-0.5b", B=4, S=256, n_new=32, seed=3)
