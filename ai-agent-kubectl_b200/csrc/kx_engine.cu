@@ -19,6 +19,7 @@ struct LayerPlan {
     kx_layer_weights w;
     // weight maps in both roles: A operand (decode, 128-row box) and B operand (prefill, 128-row box)
     CUtensorMap wqkv, wo, wgu, wd;
+    CUtensorMap wqkv_h, wo_h, wgu_h, wd_h;         // half-tile boxes for the CTA-pair prefill kernel
     void *kv_pages;
 };
 
@@ -81,12 +82,17 @@ struct GemmCall {
     const CUtensorMap *a, *b;
     int a_rows, b_rows, k, epi, swap, splits, bn;
     void *out; int ldo; const float *bias;
+    const CUtensorMap *b_half = nullptr;           // prefill only: weight map with a half-tile box
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     GemmParams p{};
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
     p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits;
+    if (!c.swap && c.b_half) {
+        const int pbn = gemm_pair_bn(c.a_rows, c.b_rows);
+        if (pbn) return gemm_launch_pair(*c.a, *c.b_half, p, pbn, st);
+    }
     KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
     return gemm_launch(*c.a, *c.b, p, c.bn, e->scratch, st);
 }
@@ -102,7 +108,7 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(run_gemm(e, {&L.wqkv, &e->xn_b[bi], e->qkv_dim, M, d.hidden, EPI_BF16, 1,
                             pick_splits(e->qkv_dim, d.hidden, b_tiles), bn, e->qkv, e->qkv_dim, L.w.bqkv}, st));
     else
-        KX_TRY(run_gemm(e, {&e->xn_a, &L.wqkv, M, e->qkv_dim, d.hidden, EPI_BF16, 0, 1, 128, e->qkv, e->qkv_dim, L.w.bqkv}, st));
+        KX_TRY(run_gemm(e, {&e->xn_a, &L.wqkv, M, e->qkv_dim, d.hidden, EPI_BF16, 0, 1, 128, e->qkv, e->qkv_dim, L.w.bqkv, &L.wqkv_h}, st));
     KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
                           d.n_q, d.n_kv, d.head_dim, st));
     if (decode)
@@ -120,10 +126,10 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(run_gemm(e, {&L.wd, &e->mlp_b[bi], d.hidden, M, d.inter, EPI_RESID, 1,
                             pick_splits(d.hidden, d.inter, b_tiles), bn, e->resid, d.hidden, nullptr}, st));
     } else {
-        KX_TRY(run_gemm(e, {&e->attn_a, &L.wo, M, d.hidden, e->q_dim, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr}, st));
+        KX_TRY(run_gemm(e, {&e->attn_a, &L.wo, M, d.hidden, e->q_dim, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr, &L.wo_h}, st));
         KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
-        KX_TRY(run_gemm(e, {&e->xn_a, &L.wgu, M, 2 * d.inter, d.hidden, EPI_SWIGLU, 0, 1, 128, e->mlp, d.inter, nullptr}, st));
-        KX_TRY(run_gemm(e, {&e->mlp_a, &L.wd, M, d.hidden, d.inter, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr}, st));
+        KX_TRY(run_gemm(e, {&e->xn_a, &L.wgu, M, 2 * d.inter, d.hidden, EPI_SWIGLU, 0, 1, 128, e->mlp, d.inter, nullptr, &L.wgu_h}, st));
+        KX_TRY(run_gemm(e, {&e->mlp_a, &L.wd, M, d.hidden, d.inter, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr, &L.wd_h}, st));
     }
     return KX_OK;
 }
@@ -212,6 +218,11 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&L.wo, L.w.wo, d.hidden, e->q_dim, e->q_dim, 128));
         KX_E(make_tmap_bf16_2d(&L.wgu, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, 128));
         KX_E(make_tmap_bf16_2d(&L.wd, L.w.wd, d.hidden, d.inter, d.inter, 128));
+        // pair kernel: box = half of its tile width for that feature count (row count only affects the 256-row gate)
+        KX_E(make_tmap_bf16_2d(&L.wqkv_h, L.w.wqkv, e->qkv_dim, d.hidden, d.hidden, gemm_pair_bn(256, e->qkv_dim) / 2));
+        KX_E(make_tmap_bf16_2d(&L.wo_h, L.w.wo, d.hidden, e->q_dim, e->q_dim, gemm_pair_bn(256, d.hidden) / 2));
+        KX_E(make_tmap_bf16_2d(&L.wgu_h, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, gemm_pair_bn(256, 2 * d.inter) / 2));
+        KX_E(make_tmap_bf16_2d(&L.wd_h, L.w.wd, d.hidden, d.inter, d.inter, gemm_pair_bn(256, d.hidden) / 2));
     }
     KX_E(make_tmap_bf16_2d(&e->lm_head_map, e->lm_head, d.vocab, d.hidden, d.hidden, 128));
     KX_E(make_tmap_bf16_2d(&e->xn_a, e->xn, Mx, d.hidden, d.hidden, 128));

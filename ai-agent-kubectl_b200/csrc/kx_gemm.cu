@@ -256,6 +256,167 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
 }
 
+
+// ---------------------------------------------------------------------------------
+// Prefill GEMM, second generation: persistent, CTA pairs with TMA multicast.
+//
+// The 128x128 kernel above is L2-bandwidth bound: it pulls 32 KB of operands per
+// 128x128x64 MMA block (128 B/cycle/SM at full tensor rate) while the L2 feeds about
+// 45 B/cycle/SM.  Here a cluster of two CTAs computes a 256 x BN output tile: each CTA
+// owns 128 rows (its own A tile) and the pair shares the B tile -- each CTA fetches half
+// of it and TMA multicasts that half into both CTAs' shared memory.  Operand traffic
+// per CTA drops to 16 KB (A) + BN/2 x 128 B per k-block.  The kernel is persistent (one
+// cluster per SM pair walks the tile list) and the accumulator is double buffered in
+// TMEM (2 x BN columns), so the epilogue of tile i overlaps the MMAs of tile i+1.
+// ---------------------------------------------------------------------------------
+template <int BN> struct Cfg2 {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (192 * 1024) / STAGE_BYTES;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <int BN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBhalf,
+                         const GemmParams p, int m_pairs, int n_tiles) {
+    using C = Cfg2<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t *empty = full + C::STAGES;
+    uint64_t *tmem_full = empty + C::STAGES;      // [2]
+    uint64_t *tmem_empty = tmem_full + 2;         // [2]
+    uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    const int total_kb = (p.k + BK - 1) / BK;
+    const int n_work = m_pairs * n_tiles;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmBhalf);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 2); }   // empty: both CTAs' MMAs
+        for (int b = 0; b < 2; ++b) { mbar_init(tmem_full + b, 1); mbar_init(tmem_empty + b, 4); }  // 4 epilogue warps
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_holder, C::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                            // the peer's barriers exist before anything targets them
+    tc_fence_after();
+    const uint32_t tmem = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint64_t pol_act = policy_evict_last(), pol_w = policy_evict_last();
+            int it = 0;
+            for (int wk = cluster_id; wk < n_work; wk += n_clusters) {
+                const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
+                const int m0 = (2 * mp + (int)rank) * BM, n0 = nt * BN + (int)rank * (BN / 2);
+                for (int i = 0; i < total_kb; ++i, ++it) {
+                    const int s = it % C::STAGES;
+                    const uint32_t ph = (it / C::STAGES) & 1;
+                    mbar_wait(empty + s, ph ^ 1);                       // both CTAs are done with this stage
+                    mbar_expect_tx(full + s, C::STAGE_BYTES);
+                    uint8_t *sa = smem + s * C::STAGE_BYTES;
+                    tma_load_2d_hint(sa, &tmA, full + s, i * BK, m0, pol_act);
+                    tma_load_2d_mcast(sa + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + s, i * BK, n0, (uint16_t)3, pol_w);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_f32(BM, BN);
+            int it = 0, tile_it = 0;
+            for (int wk = cluster_id; wk < n_work; wk += n_clusters, ++tile_it) {
+                const int ab = tile_it & 1;
+                mbar_wait(tmem_empty + ab, ((tile_it >> 1) & 1) ^ 1);   // epilogue drained this accumulator
+                tc_fence_after();
+                const uint32_t acc = tmem + (uint32_t)(ab * BN);
+                for (int i = 0; i < total_kb; ++i, ++it) {
+                    const int s = it % C::STAGES;
+                    const uint32_t ph = (it / C::STAGES) & 1;
+                    mbar_wait(full + s, ph);
+                    tc_fence_after();
+                    const uint32_t sa = base + s * C::STAGE_BYTES;
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) umma_bf16(acc, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+                    umma_commit_mcast(empty + s, (uint16_t)3);          // stage free in both CTAs once these retire
+                }
+                umma_commit(tmem_full + ab);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        int tile_it = 0;
+        for (int wk = cluster_id; wk < n_work; wk += n_clusters, ++tile_it) {
+            const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
+            const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
+            const int ab = tile_it & 1;
+            mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                tmem_ld_wait();
+                if (c + 32 >= BN) {                                     // last read of this accumulator: hand it back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tmem_empty + ab);
+                }
+                epilogue_chunk<EPI, false>(p, v, arow, n0 + c, false);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                            // nobody leaves while the peer can still reach its smem
+    if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+}
+
+template <int BN, int EPI>
+int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams &p, cudaStream_t st) {
+    auto kern = kx_gemm_bf16_pair_kernel<BN, EPI>;
+    static bool attr_set = false;
+    static int sms = 0;
+    if (!attr_set) {
+        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
+        int dev = 0;
+        KX_CUDA(cudaGetDevice(&dev));
+        KX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        attr_set = true;
+    }
+    const int m_pairs = (p.a_rows + 2 * BM - 1) / (2 * BM), n_tiles = (p.b_rows + BN - 1) / BN;
+    int clusters = sms / 2;
+    if (clusters > m_pairs * n_tiles) clusters = m_pairs * n_tiles;
+    kern<<<2 * clusters, kGemmThreads, Cfg2<BN>::SMEM_BYTES, st>>>(ta, tbh, p, m_pairs, n_tiles);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+template <int BN>
+int launch_pair_epi(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams &p, cudaStream_t st) {
+    switch (p.epilogue) {
+        case EPI_BF16: return launch_pair<BN, EPI_BF16>(ta, tbh, p, st);
+        case EPI_RESID: return launch_pair<BN, EPI_RESID>(ta, tbh, p, st);
+        case EPI_SWIGLU: return launch_pair<BN, EPI_SWIGLU>(ta, tbh, p, st);
+        case EPI_F32: return launch_pair<BN, EPI_F32>(ta, tbh, p, st);
+    }
+    set_error("kx_gemm: unknown epilogue %d", p.epilogue);
+    return KX_EINVAL;
+}
+
 // ---- host side ----------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -318,6 +479,19 @@ int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t c
     return KX_OK;
 }
 
+// Prefill tile width: 256-wide pair tiles when the feature count fills them, else 128-wide.
+int gemm_pair_bn(int64_t a_rows, int64_t b_rows) {
+    if (a_rows < 256) return 0;                       // too few rows for a CTA pair: single-CTA kernel
+    return (b_rows % 256 == 0 || b_rows >= 2048) ? 256 : 128;
+}
+
+int gemm_launch_pair(const CUtensorMap &ta, const CUtensorMap &tb_half, const GemmParams &p, int bn, cudaStream_t st) {
+    if (bn == 256) return launch_pair_epi<256>(ta, tb_half, p, st);
+    if (bn == 128) return launch_pair_epi<128>(ta, tb_half, p, st);
+    set_error("kx_gemm: unsupported pair tile width %d", bn);
+    return KX_EINVAL;
+}
+
 int gemm_pick_bn(int swap, int64_t b_rows) {
     if (!swap) return 128;
     return b_rows <= 32 ? 32 : b_rows <= 64 ? 64 : 128;
@@ -372,10 +546,16 @@ extern "C" int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const 
     GemmParams p{};
     p.a_rows = (int)a_rows; p.b_rows = (int)b_rows; p.k = k; p.out = d_out; p.ldo = (int)ldo; p.bias = d_bias;
     p.swap = swap; p.epilogue = epilogue; p.splits = splits;
-    const int bn = gemm_pick_bn(swap, b_rows);
     CUtensorMap ta, tb;
     int rc = make_tmap_bf16_2d(&ta, d_a, a_rows, k, lda, BM);
     if (rc != KX_OK) return rc;
+    const int pbn = swap ? 0 : gemm_pair_bn(a_rows, b_rows);
+    if (pbn) {                                        // prefill: persistent CTA-pair kernel
+        rc = make_tmap_bf16_2d(&tb, d_b, b_rows, k, ldb, pbn / 2);
+        if (rc != KX_OK) return rc;
+        return gemm_launch_pair(ta, tb, p, pbn, st);
+    }
+    const int bn = gemm_pick_bn(swap, b_rows);
     rc = make_tmap_bf16_2d(&tb, d_b, b_rows, k, ldb, bn);
     if (rc != KX_OK) return rc;
     void *scratch = nullptr;

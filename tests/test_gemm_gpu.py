@@ -29,7 +29,8 @@ def _ref(a, b):
     return a.float() @ b.float().T
 
 
-SHAPES = [(128, 128, 64), (300, 256, 192), (1000, 1152, 896), (257, 144, 4864)]
+SHAPES = [(128, 128, 64), (300, 256, 192), (1000, 1152, 896), (257, 144, 4864), (4096, 2048, 896), (2049, 896, 512),
+          (640, 9728, 896)]
 
 
 @pytest.mark.parametrize("m,n,k", SHAPES)
