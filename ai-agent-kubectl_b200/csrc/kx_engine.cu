@@ -29,7 +29,7 @@ struct kx_engine {
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
     const float *rope;
-    CUtensorMap lm_head_map;
+    CUtensorMap lm_head_map, lm_head_h;
     // activations
     float *resid = nullptr, *logits = nullptr;
     __nv_bfloat16 *xn = nullptr, *qkv = nullptr, *attn = nullptr, *mlp = nullptr;
@@ -97,49 +97,64 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     return gemm_launch(*c.a, *c.b, p, c.bn, e->scratch, st);
 }
 
+// A linear layer y = x W^T over M token rows with a fused epilogue.  Chooses the kernel:
+//   * token-major CTA-pair kernel when the output has enough 256-row x BN tiles to fill the GPU
+//     (prefill, and the widest layers of a large decode batch);
+//   * otherwise the swap-AB weight-streaming kernel, split-K inside a cluster.
+struct Linear {
+    const CUtensorMap *w_full, *w_half;            // weight maps: 128-row box, half-pair-tile box
+    const CUtensorMap *x_a;                        // activation as A operand (128-row box)
+    const CUtensorMap *x_b;                        // activation as B operand, indexed by bn_index
+    int features, k;
+};
+
+int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st) {
+    const int pbn = gemm_pair_bn(M, l.features);
+    const int pair_tiles = pbn ? ((M + 255) / 256) * ((l.features + pbn - 1) / pbn) : 0;
+    if (pair_tiles >= 64)
+        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half}, st);
+    if (M > 512) {
+        // tall but narrow: the single-CTA token-major kernel (128 x 128 tiles)
+        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, nullptr}, st);
+    }
+    const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
+    const int b_tiles = (M + bn - 1) / bn;
+    return run_gemm(e, {l.w_full, l.x_b + bi, l.features, M, l.k, epi, 1, pick_splits(l.features, l.k, b_tiles), bn,
+                        out, ldo, bias}, st);
+}
+
 // One transformer layer over M token rows.  decode: rows are one token per sequence.
 int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
-    const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
-    const int b_tiles = (M + bn - 1) / bn;
+    const Linear qkv{&L.wqkv, &L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden};
+    const Linear wo{&L.wo, &L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim};
+    const Linear wgu{&L.wgu, &L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
+    const Linear wd{&L.wd, &L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
     KX_TRY(op_rmsnorm(e->resid, L.w.ln1, e->xn, M, d.hidden, d.eps, nullptr, st));
-    if (decode)
-        KX_TRY(run_gemm(e, {&L.wqkv, &e->xn_b[bi], e->qkv_dim, M, d.hidden, EPI_BF16, 1,
-                            pick_splits(e->qkv_dim, d.hidden, b_tiles), bn, e->qkv, e->qkv_dim, L.w.bqkv}, st));
-    else
-        KX_TRY(run_gemm(e, {&e->xn_a, &L.wqkv, M, e->qkv_dim, d.hidden, EPI_BF16, 0, 1, 128, e->qkv, e->qkv_dim, L.w.bqkv, &L.wqkv_h}, st));
-    KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
-                          d.n_q, d.n_kv, d.head_dim, st));
-    if (decode)
-        KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos, M,
-                              max_T, d.n_q, d.n_kv, d.head_dim, st));
-    else
+    KX_TRY(linear(e, qkv, M, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, st));
+    if (decode) {
+        KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos,
+                              e->rope, M, max_T, d.n_q, d.n_kv, d.head_dim, st));
+    } else {
+        KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
+                              d.n_q, d.n_kv, d.head_dim, st));
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, 0, d.n_q, d.n_kv, d.head_dim, st));
-    if (decode) {
-        KX_TRY(run_gemm(e, {&L.wo, &e->attn_b[bi], d.hidden, M, e->q_dim, EPI_RESID, 1,
-                            pick_splits(d.hidden, e->q_dim, b_tiles), bn, e->resid, d.hidden, nullptr}, st));
-        KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
-        KX_TRY(run_gemm(e, {&L.wgu, &e->xn_b[bi], 2 * d.inter, M, d.hidden, EPI_SWIGLU, 1,
-                            pick_splits(2 * d.inter, d.hidden, b_tiles), bn, e->mlp, d.inter, nullptr}, st));
-        KX_TRY(run_gemm(e, {&L.wd, &e->mlp_b[bi], d.hidden, M, d.inter, EPI_RESID, 1,
-                            pick_splits(d.hidden, d.inter, b_tiles), bn, e->resid, d.hidden, nullptr}, st));
-    } else {
-        KX_TRY(run_gemm(e, {&e->attn_a, &L.wo, M, d.hidden, e->q_dim, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr, &L.wo_h}, st));
-        KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
-        KX_TRY(run_gemm(e, {&e->xn_a, &L.wgu, M, 2 * d.inter, d.hidden, EPI_SWIGLU, 0, 1, 128, e->mlp, d.inter, nullptr, &L.wgu_h}, st));
-        KX_TRY(run_gemm(e, {&e->mlp_a, &L.wd, M, d.hidden, d.inter, EPI_RESID, 0, 1, 128, e->resid, d.hidden, nullptr, &L.wd_h}, st));
     }
+    KX_TRY(linear(e, wo, M, EPI_RESID, e->resid, d.hidden, nullptr, st));
+    KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
+    KX_TRY(linear(e, wgu, M, EPI_SWIGLU, e->mlp, d.inter, nullptr, st));
+    KX_TRY(linear(e, wd, M, EPI_RESID, e->resid, d.hidden, nullptr, st));
     return KX_OK;
 }
 
 // final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
 int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
     const kx_model_desc &d = e->d;
-    const int bn = gemm_pick_bn(1, B), bi = bn_index(bn);
     KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, B, d.hidden, d.eps, row_map, st));
-    KX_TRY(run_gemm(e, {&e->lm_head_map, &e->xn_b[bi], d.vocab, B, d.hidden, EPI_F32, 1, 1, bn, e->logits, d.vocab, nullptr}, st));
+    const Linear head{&e->lm_head_map, &e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+    KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
     KX_TRY(op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st));
@@ -225,6 +240,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&L.wd_h, L.w.wd, d.hidden, d.inter, d.inter, gemm_pair_bn(256, d.hidden) / 2));
     }
     KX_E(make_tmap_bf16_2d(&e->lm_head_map, e->lm_head, d.vocab, d.hidden, d.hidden, 128));
+    KX_E(make_tmap_bf16_2d(&e->lm_head_h, e->lm_head, d.vocab, d.hidden, d.hidden, gemm_pair_bn(256, d.vocab) / 2));
     KX_E(make_tmap_bf16_2d(&e->xn_a, e->xn, Mx, d.hidden, d.hidden, 128));
     KX_E(make_tmap_bf16_2d(&e->attn_a, e->attn, Mx, e->q_dim, e->q_dim, 128));
     KX_E(make_tmap_bf16_2d(&e->mlp_a, e->mlp, Mx, d.inter, d.inter, 128));
@@ -290,10 +306,9 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaStreamSynchronize(st));
         {
-            const int bn = gemm_pick_bn(1, nb), bi = bn_index(bn);
+            const Linear head{&e->lm_head_map, &e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
             KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, nb, d.hidden, d.eps, e->last_rows, st));
-            KX_TRY(run_gemm(e, {&e->lm_head_map, &e->xn_b[bi], d.vocab, nb, d.hidden, EPI_F32, 1, 1, bn,
-                                e->logits + (size_t)b0 * d.vocab, d.vocab, nullptr}, st));
+            KX_TRY(linear(e, head, nb, EPI_F32, e->logits + (size_t)b0 * d.vocab, d.vocab, nullptr, st));
         }
     }
     if (d_logits) KX_CUDA(cudaMemcpyAsync(d_logits, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));

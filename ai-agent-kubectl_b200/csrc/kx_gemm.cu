@@ -417,6 +417,174 @@ int launch_pair_epi(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmPar
     return KX_EINVAL;
 }
 
+
+// ---------------------------------------------------------------------------------
+// Decode GEMM with split-K inside a thread-block cluster (swap-AB orientation).
+//
+// gridDim.z CTAs form one cluster per output tile; CTA z streams its slice of K (its
+// share of the weight tile) through the same TMA -> tcgen05 pipeline, parks its fp32
+// partial tile in its own shared memory, and after a cluster barrier every CTA reduces
+// a slice of the tile's batch columns by reading all partials over distributed shared
+// memory, in a fixed order (so the result is deterministic), and applies the epilogue.
+// No global scratch, no atomics.
+// ---------------------------------------------------------------------------------
+template <int EPI>
+__device__ __forceinline__ void epilogue_swap_elem(const GemmParams &p, float v, int arow, int b, bool ok, float bias) {
+    if (EPI == EPI_SWIGLU) {
+        const float other = __shfl_xor_sync(0xffffffffu, v, 1);
+        if (ok && !(arow & 1))
+            reinterpret_cast<__nv_bfloat16 *>(p.out)[(size_t)b * p.ldo + (arow >> 1)] = __float2bfloat16(silu(v) * other);
+    } else if (!ok) {
+        return;
+    } else if (EPI == EPI_BF16) {
+        reinterpret_cast<__nv_bfloat16 *>(p.out)[(size_t)b * p.ldo + arow] = __float2bfloat16(v + bias);
+    } else if (EPI == EPI_RESID) {
+        reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] += v;
+    } else {
+        reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] = v;
+    }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 2)
+kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t *empty = full + C::STAGES;
+    uint64_t *tmem_full = empty + C::STAGES;
+    uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(tmem_full + 1);
+    float *partial = reinterpret_cast<float *>(smem);          // [BN][128] fp32, reuses the drained stage ring
+    static_assert(BN * BM * 4 <= C::STAGES * C::STAGE_BYTES, "partial tile must fit in the stage ring");
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+    const int S = gridDim.z, z = blockIdx.z;                  // cluster = the z column; rank == z
+    const int total_kb = (p.k + BK - 1) / BK;
+    const int kb0 = z * p.kb_per_split;
+    const int nkb = min(total_kb - kb0, p.kb_per_split);
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+        mbar_init(tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_holder, C::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_holder;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint64_t pol_w = policy_evict_first(), pol_x = policy_evict_last();
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % C::STAGES;
+                mbar_wait(empty + s, ((i / C::STAGES) & 1) ^ 1);
+                mbar_expect_tx(full + s, C::STAGE_BYTES);
+                uint8_t *sa = smem + s * C::STAGE_BYTES;
+                tma_load_2d_hint(sa, &tmA, full + s, (kb0 + i) * BK, m0, pol_w);
+                tma_load_2d_hint(sa + C::A_BYTES, &tmB, full + s, (kb0 + i) * BK, n0, pol_x);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16_f32(BM, BN);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % C::STAGES;
+                mbar_wait(full + s, (i / C::STAGES) & 1);
+                tc_fence_after();
+                const uint32_t sa = base + s * C::STAGE_BYTES;
+                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::A_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) umma_bf16(tmem, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+                umma_commit(empty + s);
+            }
+            umma_commit(tmem_full);
+        }
+    } else {
+        const int q = warp & 3, r = q * 32 + lane;
+        mbar_wait(tmem_full, 0);                               // all MMAs retired: the stage ring is free
+        tc_fence_after();
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            float v[32];
+            tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) partial[(c + j) * BM + r] = v[j];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                                        // every partial of the cluster is in place
+
+    if (warp >= 2) {
+        const int r = (warp & 3) * 32 + lane, arow = m0 + r;
+        const bool ok = arow < p.a_rows;
+        const float bias = (ok && p.bias) ? __ldg(p.bias + arow) : 0.0f;
+        const int cols_per = (BN + S - 1) / S;
+        const int j0 = z * cols_per, j1 = min(BN, j0 + cols_per);
+        const uint32_t local = smem_u32(partial);
+        uint32_t peer[8];
+#pragma unroll
+        for (int src = 0; src < 8; ++src) peer[src] = dsmem_addr(local, (uint32_t)(src < S ? src : 0));
+        for (int j = j0; j < j1; ++j) {
+            if (n0 + j >= p.b_rows) break;                     // warp-uniform
+            float part[8];
+#pragma unroll
+            for (int src = 0; src < 8; ++src)                  // all remote loads in flight together
+                part[src] = src < S ? dsmem_ld_f32(peer[src] + (uint32_t)((j * BM + r) * 4)) : 0.f;
+            float v = 0.f;
+#pragma unroll
+            for (int src = 0; src < 8; ++src) v += part[src];  // fixed order: deterministic sum
+            epilogue_swap_elem<EPI>(p, v, arow, n0 + j, ok, bias);
+        }
+    }
+    cluster_sync_all();                                        // peers may still be reading this CTA's partial
+    if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+}
+
+template <int BN, int EPI>
+int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
+    auto kern = kx_gemm_bf16_ksplit_kernel<BN, EPI>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg<BN>::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+    count_launch();
+    return KX_OK;
+}
+
+template <int BN>
+int launch_ksplit_epi(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
+    switch (p.epilogue) {
+        case EPI_BF16: return launch_ksplit<BN, EPI_BF16>(ta, tb, p, grid, st);
+        case EPI_RESID: return launch_ksplit<BN, EPI_RESID>(ta, tb, p, grid, st);
+        case EPI_SWIGLU: return launch_ksplit<BN, EPI_SWIGLU>(ta, tb, p, grid, st);
+        case EPI_F32: return launch_ksplit<BN, EPI_F32>(ta, tb, p, grid, st);
+    }
+    set_error("kx_gemm: unknown epilogue %d", p.epilogue);
+    return KX_EINVAL;
+}
+
 // ---- host side ----------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -498,7 +666,7 @@ int gemm_pick_bn(int swap, int64_t b_rows) {
 }
 
 size_t gemm_scratch_bytes(const GemmParams &p, int bn) {
-    if (p.splits <= 1 || p.epilogue == EPI_RESID) return 0;
+    if (p.splits <= 1 || p.epilogue == EPI_RESID || p.swap) return 0;   // swap-AB splits reduce over DSMEM
     const size_t tiles = (size_t)((p.a_rows + BM - 1) / BM) * (size_t)((p.b_rows + bn - 1) / bn);
     return tiles * (size_t)(BM * bn) * sizeof(float) + tiles * sizeof(uint32_t);
 }
@@ -510,6 +678,19 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;      // no empty slice
     p.splits = splits;
+    if (p.swap && splits > 1) {
+        // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory
+        if (splits > 8) splits = 8;
+        p.kb_per_split = (total_kb + splits - 1) / splits;
+        splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+        p.splits = splits;
+        dim3 cgrid((unsigned)((p.b_rows + bn - 1) / bn), (unsigned)((p.a_rows + BM - 1) / BM), (unsigned)splits);
+        switch (bn) {
+            case 32: return launch_ksplit_epi<32>(ta, tb, p, cgrid, st);
+            case 64: return launch_ksplit_epi<64>(ta, tb, p, cgrid, st);
+            case 128: return launch_ksplit_epi<128>(ta, tb, p, cgrid, st);
+        }
+    }
     const size_t tiles = (size_t)((p.a_rows + BM - 1) / BM) * (size_t)((p.b_rows + bn - 1) / bn);
     if (splits > 1 && p.epilogue != EPI_RESID) {
         KX_REQUIRE(scratch != nullptr, KX_EINVAL, "kx_gemm: split-K needs scratch");

@@ -113,57 +113,100 @@ __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, 
 }
 
 // ---- decode attention: one query token per sequence over its paged KV ----------
-// grid (n_kv, B), 128 threads.  All G = n_q / n_kv query heads that share the kv head
-// are served by one pass over K and one pass over V (each cache byte read once).
+// grid (n_kv, B), 256 threads.  The CTA first applies RoPE to the new token's q heads of
+// its GQA group and to its k head, appends k and v to the cache (so no separate launch),
+// then serves all G = n_q / n_kv query heads from ONE pass over K and ONE pass over V.
+// Lanes are split (key, 8-dim chunk): a warp load covers whole 128 B / 256 B cache rows,
+// 16 bytes per lane, four independent loads in flight per lane (the kernel is latency
+// bound otherwise); dot products are finished with log2(HD/8) shuffles.
+constexpr int kDecThreads = 256, kDecWarps = 8, kDecUnroll = 4;
+
 template <int HD, int G>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(kDecThreads)
 attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
-                   const __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
-                   const int *__restrict__ pos, int n_q, int n_kv, float scale) {
+                   __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
+                   const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale) {
     extern __shared__ float sm[];
+    constexpr int LPK = HD / 8;                       // lanes per key
+    constexpr int KPW = 32 / LPK;                     // keys per warp iteration
+    constexpr int HALF = HD / 2;
     const int kvh = blockIdx.x, b = blockIdx.y;
-    const int T = pos[b] + 1;                         // keys 0 .. pos
+    const int p = pos[b], T = p + 1;                  // keys 0 .. p (p = the new token)
+    const int Tpad = (T + 31) & ~31;
     float *qs = sm;                                   // [G][HD]
     float *sc = qs + G * HD;                          // [G][Tpad]
-    const int Tpad = (T + 31) & ~31;
-    float *red = sc + G * Tpad;                       // [G] 1/sum, then [KG][G][HD] partial outputs
+    float *red = sc + G * Tpad;                       // [G] 1/sum, then [kDecWarps][G][HD] partial outputs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int *bt = block_table + (size_t)b * max_pages;
+    const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
 
-    for (int i = tid; i < G * HD; i += 128) {
-        const int g = i / HD, d = i - g * HD;
-        qs[i] = __bfloat162float(qkv[(size_t)b * qkv_ld + (size_t)(kvh * G + g) * HD + d]);
+    // RoPE on q (-> smem, rounded to bf16 like the stored q of the prefill path) and on k (-> cache); v -> cache
+    {
+        const float2 *cs = rope + (size_t)p * HALF;
+        __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
+        __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
+        for (int i = tid; i < (G + 1) * HALF; i += kDecThreads) {
+            const int h = i / HALF, d = i - h * HALF;
+            const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
+            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
+            const float2 c = cs[d];
+            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
+            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            if (h < G) { qs[h * HD + d] = __bfloat162float(o1); qs[h * HD + d + HALF] = __bfloat162float(o2); }
+            else { kdst[d] = o1; kdst[d + HALF] = o2; }
+        }
+        const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
+        for (int i = tid; i < HD; i += kDecThreads) vdst[i] = vsrc[i];
     }
     __syncthreads();
 
-    // scores: thread = key
-    const int *bt = block_table + (size_t)b * max_pages;
-    for (int t = tid; t < Tpad; t += 128) {
-        float acc[G];
+    const int kq = lane / LPK, dc = lane % LPK;
+    float qr[G][8];
 #pragma unroll
-        for (int g = 0; g < G; ++g) acc[g] = 0.f;
-        if (t < T) {
-            const __nv_bfloat16 *k = pages + (((size_t)bt[t / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD;
+    for (int g = 0; g < G; ++g)
 #pragma unroll
-            for (int c = 0; c < HD; c += 8) {
-                const uint4 kq = *reinterpret_cast<const uint4 *>(k + c);
-                const __nv_bfloat162 *kh = reinterpret_cast<const __nv_bfloat162 *>(&kq);
-                float kf[8];
+        for (int u = 0; u < 8; ++u) qr[g][u] = qs[g * HD + dc * 8 + u];
+
+    auto row_ptr = [&](int t, int which) -> const __nv_bfloat16 * {
+        return pages + (((size_t)bt[t / kPage] * 2 + which) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD + dc * 8;
+    };
+    constexpr int STEP = kDecWarps * KPW;             // keys covered by the CTA per unrolled slot
+
+    // scores
+    for (int t0 = warp * KPW; t0 < Tpad; t0 += STEP * kDecUnroll) {
+        uint4 kraw[kDecUnroll];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) { kf[2 * u] = __low2float(kh[u]); kf[2 * u + 1] = __high2float(kh[u]); }
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) acc[g] = fmaf(qs[g * HD + c + u], kf[u], acc[g]);
-                }
-            }
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const int t = t0 + u * STEP + kq;
+            kraw[u] = make_uint4(0, 0, 0, 0);
+            if (t < T) kraw[u] = *reinterpret_cast<const uint4 *>(row_ptr(t, 0));
         }
 #pragma unroll
-        for (int g = 0; g < G; ++g) sc[g * Tpad + t] = t < T ? acc[g] * scale : -INFINITY;
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const int t = t0 + u * STEP + kq;
+            const __nv_bfloat162 *kh = reinterpret_cast<const __nv_bfloat162 *>(&kraw[u]);
+            float kf[8];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { kf[2 * e] = __low2float(kh[e]); kf[2 * e + 1] = __high2float(kh[e]); }
+            float acc[G];
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                acc[g] = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[g] = fmaf(qr[g][e], kf[e], acc[g]);
+#pragma unroll
+                for (int o = LPK / 2; o > 0; o >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], o);
+            }
+            if (dc == 0 && t < Tpad) {
+#pragma unroll
+                for (int g = 0; g < G; ++g) sc[g * Tpad + t] = t < T ? acc[g] * scale : -INFINITY;
+            }
+        }
     }
     __syncthreads();
 
-    // softmax per query head (warp w handles heads w, w+4, ...)
-    for (int g = warp; g < G; g += 4) {
+    // softmax per query head (warp w handles heads w, w + kDecWarps, ...)
+    for (int g = warp; g < G; g += kDecWarps) {
         float mx = -INFINITY;
         for (int t = lane; t < Tpad; t += 32) mx = fmaxf(mx, sc[g * Tpad + t]);
         mx = warp_max(mx);
@@ -178,36 +221,57 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
     }
     __syncthreads();
 
-    // output: thread = (key parity group, dim pair); V rows are read as contiguous 2*HD bytes
-    constexpr int DP = HD / 2;                       // dim pairs
-    constexpr int KG = 128 / DP;                     // key groups: 4 for HD 64, 2 for HD 128
-    const int dp = tid % DP, kg = tid / DP;
-    float o[G][2];
+    // O = P V with the same (key, dim chunk) lane split
+    float o[G][8];
 #pragma unroll
-    for (int g = 0; g < G; ++g) { o[g][0] = 0.f; o[g][1] = 0.f; }
-    for (int t = kg; t < T; t += KG) {
-        const __nv_bfloat16 *v = pages + (((size_t)bt[t / kPage] * 2 + 1) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD;
-        const __nv_bfloat162 vv = *reinterpret_cast<const __nv_bfloat162 *>(v + 2 * dp);
-        const float v0 = __low2float(vv), v1 = __high2float(vv);
+    for (int g = 0; g < G; ++g)
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
-            const float p = sc[g * Tpad + t];
-            o[g][0] = fmaf(p, v0, o[g][0]);
-            o[g][1] = fmaf(p, v1, o[g][1]);
+        for (int u = 0; u < 8; ++u) o[g][u] = 0.f;
+    for (int t0 = warp * KPW; t0 < T; t0 += STEP * kDecUnroll) {
+        uint4 vraw[kDecUnroll];
+#pragma unroll
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const int t = t0 + u * STEP + kq;
+            vraw[u] = make_uint4(0, 0, 0, 0);
+            if (t < T) vraw[u] = *reinterpret_cast<const uint4 *>(row_ptr(t, 1));
+        }
+#pragma unroll
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const int t = t0 + u * STEP + kq;
+            if (t < T) {
+                const __nv_bfloat162 *vh = reinterpret_cast<const __nv_bfloat162 *>(&vraw[u]);
+                float vf[8];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { vf[2 * e] = __low2float(vh[e]); vf[2 * e + 1] = __high2float(vh[e]); }
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    const float pg = sc[g * Tpad + t];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pg, vf[e], o[g][e]);
+                }
+            }
         }
     }
-    float *part = red + G;                            // [KG][G][HD]
+    // reduce over the KPW key slots of the warp, then over the warps
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-        part[(kg * G + g) * HD + 2 * dp] = o[g][0];
-        part[(kg * G + g) * HD + 2 * dp + 1] = o[g][1];
+    for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int ofs = LPK; ofs < 32; ofs <<= 1) o[g][u] += __shfl_xor_sync(0xffffffffu, o[g][u], ofs);
+    float *part = red + G;                            // [kDecWarps][G][HD]
+    if (kq == 0) {
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+            for (int u = 0; u < 8; ++u) part[(warp * G + g) * HD + dc * 8 + u] = o[g][u];
     }
     __syncthreads();
-    for (int i = tid; i < G * HD; i += 128) {
+    for (int i = tid; i < G * HD; i += kDecThreads) {
         const int g = i / HD, d = i - g * HD;
         float s = 0.f;
 #pragma unroll
-        for (int k = 0; k < KG; ++k) s += part[(k * G + g) * HD + d];
+        for (int w = 0; w < kDecWarps; ++w) s += part[(w * G + g) * HD + d];
         out[(size_t)b * out_ld + (size_t)(kvh * G + g) * HD + d] = __float2bfloat16(s * red[g]);
     }
 }
@@ -415,8 +479,8 @@ __global__ void advance_kernel(int *pos, int n) {
 
 template <int HD>
 int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_bfloat16 *qkv, int qkv_ld,
-                    __nv_bfloat16 *out, int out_ld, const __nv_bfloat16 *pages, const int *bt, int max_pages,
-                    const int *pos, int n_q, int n_kv, float scale) {
+                    __nv_bfloat16 *out, int out_ld, __nv_bfloat16 *pages, const int *bt, int max_pages,
+                    const int *pos, const float2 *rope, int n_q, int n_kv, float scale) {
 #define KX_DEC(GV)                                                                                          \
     case GV: {                                                                                              \
         auto k = attn_decode_kernel<HD, GV>;                                                                \
@@ -425,7 +489,7 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
             granted = smem;                                                                                 \
         }                                                                                                   \
-        k<<<grid, 128, smem, st>>>(qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, n_q, n_kv, scale);   \
+        k<<<grid, kDecThreads, smem, st>>>(qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale); \
         break;                                                                                              \
     }
     switch (G) {
@@ -463,22 +527,22 @@ int op_rope_append(void *qkv, int qkv_ld, const int *pos, const int *seq, const 
     return KX_OK;
 }
 
-int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
-                   int max_pages, const int *pos, int B, int max_T, int n_q, int n_kv, int hd, cudaStream_t st) {
+int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pages, const int *block_table,
+                   int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
+                   cudaStream_t st) {
     const int G = n_q / n_kv;
     const int Tpad = (max_T + 31) & ~31;
-    const int KG = 128 / (hd / 2);                                  // key groups of the PV pass
-    const size_t smem = sizeof(float) * ((size_t)G * hd + (size_t)G * Tpad + G + (size_t)KG * G * hd + 8);
+    const size_t smem = sizeof(float) * ((size_t)G * hd + (size_t)G * Tpad + G + (size_t)kDecWarps * G * hd + 8);
     KX_REQUIRE(smem <= 200 * 1024, KX_ETOOBIG, "attention: context of %d tokens exceeds the decode kernel's shared memory", max_T);
     const float scale = 1.0f / sqrtf((float)hd);
     dim3 grid(n_kv, B);
     int rc;
     if (hd == 64)
         rc = launch_decode_g<64>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                 (const __nv_bfloat16 *)pages, block_table, max_pages, pos, n_q, n_kv, scale);
+                                 (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale);
     else if (hd == 128)
         rc = launch_decode_g<128>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                  (const __nv_bfloat16 *)pages, block_table, max_pages, pos, n_q, n_kv, scale);
+                                  (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale);
     else {
         set_error("attention: head_dim %d not supported (64 or 128)", hd);
         return KX_EINVAL;

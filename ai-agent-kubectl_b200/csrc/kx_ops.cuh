@@ -11,8 +11,10 @@ int op_embed(const int *tokens, const void *table, float *x, int M, int H, cudaS
 int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st);
 int op_rope_append(void *qkv, int qkv_ld, const int *pos, const int *seq, const float *rope, void *pages,
                    const int *block_table, int max_pages, int M, int n_q, int n_kv, int hd, cudaStream_t st);
-int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
-                   int max_pages, const int *pos, int B, int max_T, int n_q, int n_kv, int hd, cudaStream_t st);
+// decode attention also applies RoPE to the new token's q/k and appends its k, v to the cache
+int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pages, const int *block_table,
+                   int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
+                   cudaStream_t st);
 int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
                     int max_pages, int B, int S, int pos0, int n_q, int n_kv, int hd, cudaStream_t st);
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st);

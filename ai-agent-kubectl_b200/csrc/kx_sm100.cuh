@@ -88,6 +88,18 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// distributed shared memory: address of the same smem offset in cluster CTA `rank`
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ float dsmem_ld_f32(uint32_t cluster_addr) {
+    float v;
+    asm("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr));   // not volatile: loads may be batched
+    return v;
+}
+
 // ---- tcgen05 ------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t *smem_holder, uint32_t ncols) {   // one full warp
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_holder)), "r"(ncols) : "memory");
