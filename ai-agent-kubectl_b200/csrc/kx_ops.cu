@@ -11,6 +11,7 @@
 #include <cuda_bf16.h>
 #include "kx_common.cuh"
 #include "kx_ops.cuh"
+#include "kx_sm100.cuh"
 
 namespace kx {
 
@@ -113,34 +114,60 @@ __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, 
 }
 
 // ---- decode attention: one query token per sequence over its paged KV ----------
-// grid (n_kv, B), 256 threads.  The CTA first applies RoPE to the new token's q heads of
-// its GQA group and to its k head, appends k and v to the cache (so no separate launch),
-// then serves all G = n_q / n_kv query heads from ONE pass over K and ONE pass over V.
-// Lanes are split (key, 8-dim chunk): a warp load covers whole 128 B / 256 B cache rows,
-// 16 bytes per lane, four independent loads in flight per lane (the kernel is latency
-// bound otherwise); dot products are finished with log2(HD/8) shuffles.
-constexpr int kDecThreads = 256, kDecWarps = 8, kDecUnroll = 4;
+// grid (n_kv, B), 256 threads.  Latency, not arithmetic, decides this kernel, so the CTA
+// first puts its whole K and V working set in flight: one warp issues a 1-D bulk copy
+// (cp.async.bulk -> mbarrier) per cache page into shared memory, up to 32 KB of K and
+// 32 KB of V per chunk, while the other warps apply RoPE to the new token's q heads (of
+// this GQA group) and k head and append k, v to the cache (no separate launch).  All
+// G = n_q / n_kv query heads are then served from that one copy of K and V: lanes are split
+// (key, 8-dim chunk) so every shared-memory access is a conflict-free 16-byte load, dot
+// products finish with log2(HD/8) shuffles, softmax is online across chunks.
+constexpr int kDecThreads = 256, kDecWarps = 8;
 
 template <int HD, int G>
-__global__ void __launch_bounds__(kDecThreads)
+__global__ void __launch_bounds__(kDecThreads, (G <= 4 ? 3 : 1))
 attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
                    __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
                    const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(128) uint8_t dsm[];
     constexpr int LPK = HD / 8;                       // lanes per key
     constexpr int KPW = 32 / LPK;                     // keys per warp iteration
     constexpr int HALF = HD / 2;
+    constexpr int CH = 32768 / (HD * 2);              // tokens per chunk (32 KB of K, 32 KB of V)
+    constexpr int PAGE_BYTES = kPage * HD * 2;
+    uint64_t *bar = reinterpret_cast<uint64_t *>(dsm);
+    __nv_bfloat16 *Ks = reinterpret_cast<__nv_bfloat16 *>(dsm + 128);
+    __nv_bfloat16 *Vs = Ks + CH * HD;
+    float *qs = reinterpret_cast<float *>(Vs + CH * HD);   // [G][HD]
+    float *sc = qs + G * HD;                               // [G][CH]
+    float *ml = sc + G * CH;                               // [G] running max, [G] running sum, [G] rescale
+    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(ml + ((3 * G + 3) & ~3));   // [HD] new k, [HD] new v (16 B aligned)
+    __nv_bfloat16 *vnew = knew + HD;
+    float *part = reinterpret_cast<float *>(Ks);           // [kDecWarps][G][HD], aliases K/V after the last chunk
+
     const int kvh = blockIdx.x, b = blockIdx.y;
     const int p = pos[b], T = p + 1;                  // keys 0 .. p (p = the new token)
-    const int Tpad = (T + 31) & ~31;
-    float *qs = sm;                                   // [G][HD]
-    float *sc = qs + G * HD;                          // [G][Tpad]
-    float *red = sc + G * Tpad;                       // [G] 1/sum, then [kDecWarps][G][HD] partial outputs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int *bt = block_table + (size_t)b * max_pages;
     const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
 
-    // RoPE on q (-> smem, rounded to bf16 like the stored q of the prefill path) and on k (-> cache); v -> cache
+    if (tid == 0) { sm100::mbar_init(bar, 1); sm100::fence_barrier_init(); }
+    if (tid < 3 * G) ml[tid] = tid < G ? -INFINITY : 0.f;
+    __syncthreads();
+
+    auto issue_chunk = [&](int c0) {                  // warp 0: one bulk copy per page for K and for V
+        const int npages = (min(T, c0 + CH) - c0 + kPage - 1) / kPage;
+        if (lane == 0) sm100::mbar_expect_tx(bar, (uint32_t)(2 * npages * PAGE_BYTES));
+        __syncwarp();
+        for (int i = lane; i < 2 * npages; i += 32) {
+            const int pg = i >> 1, which = i & 1;
+            const __nv_bfloat16 *src = pages + (((size_t)bt[c0 / kPage + pg] * 2 + which) * n_kv + kvh) * kPage * HD;
+            sm100::bulk_load((which ? Vs : Ks) + (size_t)pg * kPage * HD, src, PAGE_BYTES, bar);
+        }
+    };
+    if (warp == 0) issue_chunk(0);
+
+    // RoPE on q (-> smem, rounded to bf16 like the stored q of the prefill path) and on k; append k, v
     {
         const float2 *cs = rope + (size_t)p * HALF;
         __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
@@ -153,105 +180,111 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
             const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
             const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
             if (h < G) { qs[h * HD + d] = __bfloat162float(o1); qs[h * HD + d + HALF] = __bfloat162float(o2); }
-            else { kdst[d] = o1; kdst[d + HALF] = o2; }
+            else { kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2; }
         }
         const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
-        for (int i = tid; i < HD; i += kDecThreads) vdst[i] = vsrc[i];
+        for (int i = tid; i < HD; i += kDecThreads) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
     }
     __syncthreads();
 
     const int kq = lane / LPK, dc = lane % LPK;
-    float qr[G][8];
+    float qr[G][8], o[G][8];
 #pragma unroll
     for (int g = 0; g < G; ++g)
 #pragma unroll
-        for (int u = 0; u < 8; ++u) qr[g][u] = qs[g * HD + dc * 8 + u];
+        for (int u = 0; u < 8; ++u) { qr[g][u] = qs[g * HD + dc * 8 + u]; o[g][u] = 0.f; }
 
-    auto row_ptr = [&](int t, int which) -> const __nv_bfloat16 * {
-        return pages + (((size_t)bt[t / kPage] * 2 + which) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD + dc * 8;
-    };
-    constexpr int STEP = kDecWarps * KPW;             // keys covered by the CTA per unrolled slot
-
-    // scores
-    for (int t0 = warp * KPW; t0 < Tpad; t0 += STEP * kDecUnroll) {
-        uint4 kraw[kDecUnroll];
-#pragma unroll
-        for (int u = 0; u < kDecUnroll; ++u) {
-            const int t = t0 + u * STEP + kq;
-            kraw[u] = make_uint4(0, 0, 0, 0);
-            if (t < T) kraw[u] = *reinterpret_cast<const uint4 *>(row_ptr(t, 0));
+    uint32_t phase = 0;
+    for (int c0 = 0; c0 < T; c0 += CH) {
+        const int n = min(T, c0 + CH) - c0;           // valid keys in this chunk
+        const int npad = (n + 31) & ~31;
+        sm100::mbar_wait(bar, phase);
+        phase ^= 1;
+        // the new token's row comes from this CTA, not from the copy (which raced with the append)
+        if (p >= c0 && p < c0 + CH && tid < HD / 8) {
+            reinterpret_cast<uint4 *>(Ks + (size_t)(p - c0) * HD)[tid] = reinterpret_cast<const uint4 *>(knew)[tid];
+            reinterpret_cast<uint4 *>(Vs + (size_t)(p - c0) * HD)[tid] = reinterpret_cast<const uint4 *>(vnew)[tid];
         }
-#pragma unroll
-        for (int u = 0; u < kDecUnroll; ++u) {
-            const int t = t0 + u * STEP + kq;
-            const __nv_bfloat162 *kh = reinterpret_cast<const __nv_bfloat162 *>(&kraw[u]);
-            float kf[8];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { kf[2 * e] = __low2float(kh[e]); kf[2 * e + 1] = __high2float(kh[e]); }
+        __syncthreads();
+
+        // scores
+        for (int t0 = warp * KPW; t0 < npad; t0 += kDecWarps * KPW) {
+            const int t = t0 + kq;
             float acc[G];
 #pragma unroll
+            for (int g = 0; g < G; ++g) acc[g] = 0.f;
+            if (t < n) {
+                const uint4 kq4 = *reinterpret_cast<const uint4 *>(Ks + (size_t)t * HD + dc * 8);
+                const __nv_bfloat162 *kh = reinterpret_cast<const __nv_bfloat162 *>(&kq4);
+                float kf[8];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { kf[2 * e] = __low2float(kh[e]); kf[2 * e + 1] = __high2float(kh[e]); }
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) acc[g] = fmaf(qr[g][e], kf[e], acc[g]);
+            }
+#pragma unroll
             for (int g = 0; g < G; ++g) {
-                acc[g] = 0.f;
 #pragma unroll
-                for (int e = 0; e < 8; ++e) acc[g] = fmaf(qr[g][e], kf[e], acc[g]);
-#pragma unroll
-                for (int o = LPK / 2; o > 0; o >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], o);
+                for (int ofs = LPK / 2; ofs > 0; ofs >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], ofs);
             }
-            if (dc == 0 && t < Tpad) {
+            if (dc == 0) {
 #pragma unroll
-                for (int g = 0; g < G; ++g) sc[g * Tpad + t] = t < T ? acc[g] * scale : -INFINITY;
+                for (int g = 0; g < G; ++g) sc[g * CH + t] = t < n ? acc[g] * scale : -INFINITY;
             }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // softmax per query head (warp w handles heads w, w + kDecWarps, ...)
-    for (int g = warp; g < G; g += kDecWarps) {
-        float mx = -INFINITY;
-        for (int t = lane; t < Tpad; t += 32) mx = fmaxf(mx, sc[g * Tpad + t]);
-        mx = warp_max(mx);
-        float sum = 0.f;
-        for (int t = lane; t < Tpad; t += 32) {
-            const float e = __expf(sc[g * Tpad + t] - mx);
-            sc[g * Tpad + t] = e;
-            sum += e;
+        // online softmax bookkeeping per query head (warp w handles heads w, w + kDecWarps, ...)
+        for (int g = warp; g < G; g += kDecWarps) {
+            float mx = -INFINITY;
+            for (int t = lane; t < npad; t += 32) mx = fmaxf(mx, sc[g * CH + t]);
+            mx = warp_max(mx);
+            const float m_old = ml[g], m_new = fmaxf(m_old, mx);
+            float sum = 0.f;
+            for (int t = lane; t < npad; t += 32) {
+                const float e = __expf(sc[g * CH + t] - m_new);
+                sc[g * CH + t] = e;
+                sum += e;
+            }
+            sum = warp_sum(sum);
+            if (lane == 0) {
+                const float f = __expf(m_old - m_new);       // 0 on the first chunk (m_old = -inf)
+                ml[g] = m_new;
+                ml[G + g] = ml[G + g] * f + sum;
+                ml[2 * G + g] = f;
+            }
         }
-        sum = warp_sum(sum);
-        if (lane == 0) red[g] = 1.0f / sum;
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // O = P V with the same (key, dim chunk) lane split
-    float o[G][8];
+        // O = O * f + P V
 #pragma unroll
-    for (int g = 0; g < G; ++g)
+        for (int g = 0; g < G; ++g) {
+            const float f = ml[2 * G + g];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) o[g][u] = 0.f;
-    for (int t0 = warp * KPW; t0 < T; t0 += STEP * kDecUnroll) {
-        uint4 vraw[kDecUnroll];
-#pragma unroll
-        for (int u = 0; u < kDecUnroll; ++u) {
-            const int t = t0 + u * STEP + kq;
-            vraw[u] = make_uint4(0, 0, 0, 0);
-            if (t < T) vraw[u] = *reinterpret_cast<const uint4 *>(row_ptr(t, 1));
+            for (int u = 0; u < 8; ++u) o[g][u] *= f;
         }
-#pragma unroll
-        for (int u = 0; u < kDecUnroll; ++u) {
-            const int t = t0 + u * STEP + kq;
-            if (t < T) {
-                const __nv_bfloat162 *vh = reinterpret_cast<const __nv_bfloat162 *>(&vraw[u]);
+        for (int t0 = warp * KPW; t0 < n; t0 += kDecWarps * KPW) {
+            const int t = t0 + kq;
+            if (t < n) {
+                const uint4 vq4 = *reinterpret_cast<const uint4 *>(Vs + (size_t)t * HD + dc * 8);
+                const __nv_bfloat162 *vh = reinterpret_cast<const __nv_bfloat162 *>(&vq4);
                 float vf[8];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) { vf[2 * e] = __low2float(vh[e]); vf[2 * e + 1] = __high2float(vh[e]); }
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    const float pg = sc[g * Tpad + t];
+                    const float pg = sc[g * CH + t];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pg, vf[e], o[g][e]);
                 }
             }
         }
+        __syncthreads();                              // K/V/sc of this chunk fully consumed
+        if (c0 + CH < T && warp == 0) issue_chunk(c0 + CH);
     }
+
     // reduce over the KPW key slots of the warp, then over the warps
 #pragma unroll
     for (int g = 0; g < G; ++g)
@@ -259,7 +292,6 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         for (int u = 0; u < 8; ++u)
 #pragma unroll
             for (int ofs = LPK; ofs < 32; ofs <<= 1) o[g][u] += __shfl_xor_sync(0xffffffffu, o[g][u], ofs);
-    float *part = red + G;                            // [kDecWarps][G][HD]
     if (kq == 0) {
 #pragma unroll
         for (int g = 0; g < G; ++g)
@@ -272,7 +304,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < kDecWarps; ++w) s += part[(w * G + g) * HD + d];
-        out[(size_t)b * out_ld + (size_t)(kvh * G + g) * HD + d] = __float2bfloat16(s * red[g]);
+        out[(size_t)b * out_ld + (size_t)(kvh * G + g) * HD + d] = __float2bfloat16(s / ml[G + g]);
     }
 }
 
@@ -531,9 +563,9 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
                    int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
                    cudaStream_t st) {
     const int G = n_q / n_kv;
-    const int Tpad = (max_T + 31) & ~31;
-    const size_t smem = sizeof(float) * ((size_t)G * hd + (size_t)G * Tpad + G + (size_t)kDecWarps * G * hd + 8);
-    KX_REQUIRE(smem <= 200 * 1024, KX_ETOOBIG, "attention: context of %d tokens exceeds the decode kernel's shared memory", max_T);
+    (void)max_T;                                      // any context length: K/V are consumed in 32 KB chunks
+    const int ch = 32768 / (hd * 2);
+    const size_t smem = 128 + (size_t)2 * ch * hd * 2 + sizeof(float) * ((size_t)G * hd + (size_t)G * ch + 3 * G) + 4 * hd + 64;
     const float scale = 1.0f / sqrtf((float)hd);
     dim3 grid(n_kv, B);
     int rc;

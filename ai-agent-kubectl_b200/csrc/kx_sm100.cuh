@@ -77,6 +77,12 @@ __device__ __forceinline__ void tma_load_2d_mcast(void *smem_dst, const CUtensor
         ::"r"(smem_u32(smem_dst)), "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask), "l"(policy) : "memory");
 }
 
+// 1-D bulk copy global -> shared (size multiple of 16 B, both addresses 16 B aligned)
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // ---- clusters -------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
