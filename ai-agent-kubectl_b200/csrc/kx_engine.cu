@@ -19,7 +19,8 @@ struct LayerPlan {
     kx_layer_weights w;
     // weight maps in both roles: A operand (decode, 128-row box) and B operand (prefill, 128-row box)
     CUtensorMap wqkv, wo, wgu, wd;
-    CUtensorMap wqkv_h, wo_h, wgu_h, wd_h;         // half-tile boxes for the CTA-pair prefill kernel
+    // half-tile boxes for the CTA-pair kernel: [0] = 64 rows (128-wide tiles), [1] = 128 rows (256-wide tiles)
+    CUtensorMap wqkv_h[2], wo_h[2], wgu_h[2], wd_h[2];
     void *kv_pages;
 };
 
@@ -29,7 +30,7 @@ struct kx_engine {
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
     const float *rope;
-    CUtensorMap lm_head_map, lm_head_h;
+    CUtensorMap lm_head_map, lm_head_h[2];
     // activations
     float *resid = nullptr, *logits = nullptr;
     __nv_bfloat16 *xn = nullptr, *qkv = nullptr, *attn = nullptr, *mlp = nullptr;
@@ -61,7 +62,8 @@ int bn_index(int bn) { return bn == 32 ? 0 : bn == 64 ? 1 : 2; }
 int pick_splits(int features, int k, int b_tiles) {
     const int tiles = ((features + 127) / 128) * b_tiles;
     const int kb = (k + 63) / 64;
-    int s = (296 + tiles - 1) / tiles;
+    int s = 296 / tiles;                            // at most one wave of 2 CTAs per SM
+    if (s > 8) s = 8;                               // portable cluster size
     if (s > kb) s = kb;
     if (s < 1) s = 1;
     return s;
@@ -82,17 +84,15 @@ struct GemmCall {
     const CUtensorMap *a, *b;
     int a_rows, b_rows, k, epi, swap, splits, bn;
     void *out; int ldo; const float *bias;
-    const CUtensorMap *b_half = nullptr;           // prefill only: weight map with a half-tile box
+    const CUtensorMap *b_half = nullptr;           // token-major pair kernel: weight map with a half-tile box
+    int pair_bn = 0;                               // ... and its tile width (128 or 256)
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     GemmParams p{};
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
     p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits;
-    if (!c.swap && c.b_half) {
-        const int pbn = gemm_pair_bn(c.a_rows, c.b_rows);
-        if (pbn) return gemm_launch_pair(*c.a, *c.b_half, p, pbn, st);
-    }
+    if (!c.swap && c.b_half) return gemm_launch_pair(*c.a, *c.b_half, p, c.pair_bn, st);
     KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
     return gemm_launch(*c.a, *c.b, p, c.bn, e->scratch, st);
 }
@@ -102,21 +102,24 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
 //     (prefill, and the widest layers of a large decode batch);
 //   * otherwise the swap-AB weight-streaming kernel, split-K inside a cluster.
 struct Linear {
-    const CUtensorMap *w_full, *w_half;            // weight maps: 128-row box, half-pair-tile box
+    const CUtensorMap *w_full, *w_half;            // weight maps: 128-row box; half-pair-tile boxes [64 rows, 128 rows]
     const CUtensorMap *x_a;                        // activation as A operand (128-row box)
     const CUtensorMap *x_b;                        // activation as B operand, indexed by bn_index
     int features, k;
 };
 
 int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st) {
-    const int pbn = gemm_pair_bn(M, l.features);
-    const int pair_tiles = pbn ? ((M + 255) / 256) * ((l.features + pbn - 1) / pbn) : 0;
-    if (pair_tiles >= 64)
-        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half}, st);
-    if (M > 512) {
-        // tall but narrow: the single-CTA token-major kernel (128 x 128 tiles)
-        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, nullptr}, st);
+    if (M >= 256) {
+        const int m_pairs = (M + 255) / 256;
+        const int t256 = m_pairs * ((l.features + 255) / 256), t128 = m_pairs * ((l.features + 127) / 128);
+        const bool wide_ok = l.features % 256 == 0 || l.features >= 2048;
+        if (wide_ok && t256 >= 64)
+            return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + 1, 256}, st);
+        if (t128 >= 24)
+            return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + 0, 128}, st);
     }
+    if (M > 512)   // tall but very narrow: the single-CTA token-major kernel (128 x 128 tiles)
+        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias}, st);
     const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
     const int b_tiles = (M + bn - 1) / bn;
     return run_gemm(e, {l.w_full, l.x_b + bi, l.features, M, l.k, epi, 1, pick_splits(l.features, l.k, b_tiles), bn,
@@ -127,10 +130,10 @@ int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, co
 int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
-    const Linear qkv{&L.wqkv, &L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden};
-    const Linear wo{&L.wo, &L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim};
-    const Linear wgu{&L.wgu, &L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
-    const Linear wd{&L.wd, &L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
+    const Linear qkv{&L.wqkv, L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden};
+    const Linear wo{&L.wo, L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim};
+    const Linear wgu{&L.wgu, L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
+    const Linear wd{&L.wd, L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
     KX_TRY(op_rmsnorm(e->resid, L.w.ln1, e->xn, M, d.hidden, d.eps, nullptr, st));
     KX_TRY(linear(e, qkv, M, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, st));
     if (decode) {
@@ -153,7 +156,7 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
 int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, B, d.hidden, d.eps, row_map, st));
-    const Linear head{&e->lm_head_map, &e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+    const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
     KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
@@ -233,14 +236,17 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&L.wo, L.w.wo, d.hidden, e->q_dim, e->q_dim, 128));
         KX_E(make_tmap_bf16_2d(&L.wgu, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, 128));
         KX_E(make_tmap_bf16_2d(&L.wd, L.w.wd, d.hidden, d.inter, d.inter, 128));
-        // pair kernel: box = half of its tile width for that feature count (row count only affects the 256-row gate)
-        KX_E(make_tmap_bf16_2d(&L.wqkv_h, L.w.wqkv, e->qkv_dim, d.hidden, d.hidden, gemm_pair_bn(256, e->qkv_dim) / 2));
-        KX_E(make_tmap_bf16_2d(&L.wo_h, L.w.wo, d.hidden, e->q_dim, e->q_dim, gemm_pair_bn(256, d.hidden) / 2));
-        KX_E(make_tmap_bf16_2d(&L.wgu_h, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, gemm_pair_bn(256, 2 * d.inter) / 2));
-        KX_E(make_tmap_bf16_2d(&L.wd_h, L.w.wd, d.hidden, d.inter, d.inter, gemm_pair_bn(256, d.hidden) / 2));
+        for (int j = 0; j < 2; ++j) {              // pair kernel: box = half of its tile width
+            const int box = j ? 128 : 64;
+            KX_E(make_tmap_bf16_2d(&L.wqkv_h[j], L.w.wqkv, e->qkv_dim, d.hidden, d.hidden, box));
+            KX_E(make_tmap_bf16_2d(&L.wo_h[j], L.w.wo, d.hidden, e->q_dim, e->q_dim, box));
+            KX_E(make_tmap_bf16_2d(&L.wgu_h[j], L.w.wgu, 2 * d.inter, d.hidden, d.hidden, box));
+            KX_E(make_tmap_bf16_2d(&L.wd_h[j], L.w.wd, d.hidden, d.inter, d.inter, box));
+        }
     }
     KX_E(make_tmap_bf16_2d(&e->lm_head_map, e->lm_head, d.vocab, d.hidden, d.hidden, 128));
-    KX_E(make_tmap_bf16_2d(&e->lm_head_h, e->lm_head, d.vocab, d.hidden, d.hidden, gemm_pair_bn(256, d.vocab) / 2));
+    KX_E(make_tmap_bf16_2d(&e->lm_head_h[0], e->lm_head, d.vocab, d.hidden, d.hidden, 64));
+    KX_E(make_tmap_bf16_2d(&e->lm_head_h[1], e->lm_head, d.vocab, d.hidden, d.hidden, 128));
     KX_E(make_tmap_bf16_2d(&e->xn_a, e->xn, Mx, d.hidden, d.hidden, 128));
     KX_E(make_tmap_bf16_2d(&e->attn_a, e->attn, Mx, e->q_dim, e->q_dim, 128));
     KX_E(make_tmap_bf16_2d(&e->mlp_a, e->mlp, Mx, d.inter, d.inter, 128));
@@ -306,7 +312,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaStreamSynchronize(st));
         {
-            const Linear head{&e->lm_head_map, &e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+            const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
             KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, nb, d.hidden, d.eps, e->last_rows, st));
             KX_TRY(linear(e, head, nb, EPI_F32, e->logits + (size_t)b0 * d.vocab, d.vocab, nullptr, st));
         }

@@ -113,201 +113,6 @@ __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, 
     }
 }
 
-// ---- decode attention: one query token per sequence over its paged KV ----------
-// grid (n_kv, B), 256 threads.  Latency, not arithmetic, decides this kernel, so the CTA
-// first puts its whole K and V working set in flight: one warp issues a 1-D bulk copy
-// (cp.async.bulk -> mbarrier) per cache page into shared memory, up to 32 KB of K and
-// 32 KB of V per chunk, while the other warps apply RoPE to the new token's q heads (of
-// this GQA group) and k head and append k, v to the cache (no separate launch).  All
-// G = n_q / n_kv query heads are then served from that one copy of K and V: lanes are split
-// (key, 8-dim chunk) so every shared-memory access is a conflict-free 16-byte load, dot
-// products finish with log2(HD/8) shuffles, softmax is online across chunks.
-constexpr int kDecThreads = 256, kDecWarps = 8;
-
-template <int HD, int G>
-__global__ void __launch_bounds__(kDecThreads, (G <= 4 ? 3 : 1))
-attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
-                   __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
-                   const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale) {
-    extern __shared__ __align__(128) uint8_t dsm[];
-    constexpr int LPK = HD / 8;                       // lanes per key
-    constexpr int KPW = 32 / LPK;                     // keys per warp iteration
-    constexpr int HALF = HD / 2;
-    constexpr int CH = 32768 / (HD * 2);              // tokens per chunk (32 KB of K, 32 KB of V)
-    constexpr int PAGE_BYTES = kPage * HD * 2;
-    uint64_t *bar = reinterpret_cast<uint64_t *>(dsm);
-    __nv_bfloat16 *Ks = reinterpret_cast<__nv_bfloat16 *>(dsm + 128);
-    __nv_bfloat16 *Vs = Ks + CH * HD;
-    float *qs = reinterpret_cast<float *>(Vs + CH * HD);   // [G][HD]
-    float *sc = qs + G * HD;                               // [G][CH]
-    float *ml = sc + G * CH;                               // [G] running max, [G] running sum, [G] rescale
-    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(ml + ((3 * G + 3) & ~3));   // [HD] new k, [HD] new v (16 B aligned)
-    __nv_bfloat16 *vnew = knew + HD;
-    float *part = reinterpret_cast<float *>(Ks);           // [kDecWarps][G][HD], aliases K/V after the last chunk
-
-    const int kvh = blockIdx.x, b = blockIdx.y;
-    const int p = pos[b], T = p + 1;                  // keys 0 .. p (p = the new token)
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int *bt = block_table + (size_t)b * max_pages;
-    const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
-
-    if (tid == 0) { sm100::mbar_init(bar, 1); sm100::fence_barrier_init(); }
-    if (tid < 3 * G) ml[tid] = tid < G ? -INFINITY : 0.f;
-    __syncthreads();
-
-    auto issue_chunk = [&](int c0) {                  // warp 0: one bulk copy per page for K and for V
-        const int npages = (min(T, c0 + CH) - c0 + kPage - 1) / kPage;
-        if (lane == 0) sm100::mbar_expect_tx(bar, (uint32_t)(2 * npages * PAGE_BYTES));
-        __syncwarp();
-        for (int i = lane; i < 2 * npages; i += 32) {
-            const int pg = i >> 1, which = i & 1;
-            const __nv_bfloat16 *src = pages + (((size_t)bt[c0 / kPage + pg] * 2 + which) * n_kv + kvh) * kPage * HD;
-            sm100::bulk_load((which ? Vs : Ks) + (size_t)pg * kPage * HD, src, PAGE_BYTES, bar);
-        }
-    };
-    if (warp == 0) issue_chunk(0);
-
-    // RoPE on q (-> smem, rounded to bf16 like the stored q of the prefill path) and on k; append k, v
-    {
-        const float2 *cs = rope + (size_t)p * HALF;
-        __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
-        __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
-        for (int i = tid; i < (G + 1) * HALF; i += kDecThreads) {
-            const int h = i / HALF, d = i - h * HALF;
-            const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
-            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
-            const float2 c = cs[d];
-            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
-            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
-            if (h < G) { qs[h * HD + d] = __bfloat162float(o1); qs[h * HD + d + HALF] = __bfloat162float(o2); }
-            else { kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2; }
-        }
-        const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
-        for (int i = tid; i < HD; i += kDecThreads) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
-    }
-    __syncthreads();
-
-    const int kq = lane / LPK, dc = lane % LPK;
-    float qr[G][8], o[G][8];
-#pragma unroll
-    for (int g = 0; g < G; ++g)
-#pragma unroll
-        for (int u = 0; u < 8; ++u) { qr[g][u] = qs[g * HD + dc * 8 + u]; o[g][u] = 0.f; }
-
-    uint32_t phase = 0;
-    for (int c0 = 0; c0 < T; c0 += CH) {
-        const int n = min(T, c0 + CH) - c0;           // valid keys in this chunk
-        const int npad = (n + 31) & ~31;
-        sm100::mbar_wait(bar, phase);
-        phase ^= 1;
-        // the new token's row comes from this CTA, not from the copy (which raced with the append)
-        if (p >= c0 && p < c0 + CH && tid < HD / 8) {
-            reinterpret_cast<uint4 *>(Ks + (size_t)(p - c0) * HD)[tid] = reinterpret_cast<const uint4 *>(knew)[tid];
-            reinterpret_cast<uint4 *>(Vs + (size_t)(p - c0) * HD)[tid] = reinterpret_cast<const uint4 *>(vnew)[tid];
-        }
-        __syncthreads();
-
-        // scores
-        for (int t0 = warp * KPW; t0 < npad; t0 += kDecWarps * KPW) {
-            const int t = t0 + kq;
-            float acc[G];
-#pragma unroll
-            for (int g = 0; g < G; ++g) acc[g] = 0.f;
-            if (t < n) {
-                const uint4 kq4 = *reinterpret_cast<const uint4 *>(Ks + (size_t)t * HD + dc * 8);
-                const __nv_bfloat162 *kh = reinterpret_cast<const __nv_bfloat162 *>(&kq4);
-                float kf[8];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) { kf[2 * e] = __low2float(kh[e]); kf[2 * e + 1] = __high2float(kh[e]); }
-#pragma unroll
-                for (int g = 0; g < G; ++g)
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) acc[g] = fmaf(qr[g][e], kf[e], acc[g]);
-            }
-#pragma unroll
-            for (int g = 0; g < G; ++g) {
-#pragma unroll
-                for (int ofs = LPK / 2; ofs > 0; ofs >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], ofs);
-            }
-            if (dc == 0) {
-#pragma unroll
-                for (int g = 0; g < G; ++g) sc[g * CH + t] = t < n ? acc[g] * scale : -INFINITY;
-            }
-        }
-        __syncthreads();
-
-        // online softmax bookkeeping per query head (warp w handles heads w, w + kDecWarps, ...)
-        for (int g = warp; g < G; g += kDecWarps) {
-            float mx = -INFINITY;
-            for (int t = lane; t < npad; t += 32) mx = fmaxf(mx, sc[g * CH + t]);
-            mx = warp_max(mx);
-            const float m_old = ml[g], m_new = fmaxf(m_old, mx);
-            float sum = 0.f;
-            for (int t = lane; t < npad; t += 32) {
-                const float e = __expf(sc[g * CH + t] - m_new);
-                sc[g * CH + t] = e;
-                sum += e;
-            }
-            sum = warp_sum(sum);
-            if (lane == 0) {
-                const float f = __expf(m_old - m_new);       // 0 on the first chunk (m_old = -inf)
-                ml[g] = m_new;
-                ml[G + g] = ml[G + g] * f + sum;
-                ml[2 * G + g] = f;
-            }
-        }
-        __syncthreads();
-
-        // O = O * f + P V
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            const float f = ml[2 * G + g];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) o[g][u] *= f;
-        }
-        for (int t0 = warp * KPW; t0 < n; t0 += kDecWarps * KPW) {
-            const int t = t0 + kq;
-            if (t < n) {
-                const uint4 vq4 = *reinterpret_cast<const uint4 *>(Vs + (size_t)t * HD + dc * 8);
-                const __nv_bfloat162 *vh = reinterpret_cast<const __nv_bfloat162 *>(&vq4);
-                float vf[8];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) { vf[2 * e] = __low2float(vh[e]); vf[2 * e + 1] = __high2float(vh[e]); }
-#pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    const float pg = sc[g * CH + t];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pg, vf[e], o[g][e]);
-                }
-            }
-        }
-        __syncthreads();                              // K/V/sc of this chunk fully consumed
-        if (c0 + CH < T && warp == 0) issue_chunk(c0 + CH);
-    }
-
-    // reduce over the KPW key slots of the warp, then over the warps
-#pragma unroll
-    for (int g = 0; g < G; ++g)
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-#pragma unroll
-            for (int ofs = LPK; ofs < 32; ofs <<= 1) o[g][u] += __shfl_xor_sync(0xffffffffu, o[g][u], ofs);
-    if (kq == 0) {
-#pragma unroll
-        for (int g = 0; g < G; ++g)
-#pragma unroll
-            for (int u = 0; u < 8; ++u) part[(warp * G + g) * HD + dc * 8 + u] = o[g][u];
-    }
-    __syncthreads();
-    for (int i = tid; i < G * HD; i += kDecThreads) {
-        const int g = i / HD, d = i - g * HD;
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < kDecWarps; ++w) s += part[(w * G + g) * HD + d];
-        out[(size_t)b * out_ld + (size_t)(kvh * G + g) * HD + d] = __float2bfloat16(s / ml[G + g]);
-    }
-}
-
 // ---- prefill attention: causal flash attention, GQA, K/V from the paged cache ----
 // grid (ceil(S/64), n_q, B), 128 threads; warp w owns query rows 16w .. 16w+15 of the
 // 64-row block.  QK^T and PV run on tensor cores (mma.sync m16n8k16 bf16, fp32 acc) with
@@ -471,6 +276,210 @@ attn_prefill_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bflo
     }
 }
 
+// ---- decode attention: one query token per sequence over its paged KV ----------
+// grid (n_kv, B), 128 threads.  The CTA applies RoPE to the new token's q heads (of this
+// GQA group) and k head and appends k, v to the cache (no separate launch); the G query
+// heads become the rows of one 16-row MMA tile, so QK^T and PV for all heads of the group
+// run on tensor cores (mma.sync m16n8k16 bf16) from ONE copy of K and V.  K/V rows are
+// staged with 16-byte cp.async into XOR-swizzled shared memory (conflict-free ldmatrix),
+// 256 keys per round; each warp owns a 64-key block of the round with its own online
+// softmax state and the four partial results are merged at the end (flash decoding
+// inside the CTA).
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+constexpr int kDecThreads = 128;
+
+template <int HD, int G>
+__global__ void __launch_bounds__(kDecThreads)
+attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
+                   __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
+                   const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2) {
+    extern __shared__ __align__(128) uint8_t smem_dec[];
+    constexpr int CH = HD / 8;                        // 16 B chunks per row
+    constexpr int HALF = HD / 2;
+    constexpr int ROUND = 256;                        // keys staged per round (4 warps x 64)
+    constexpr int QT = 16 * HD * 2, KT = ROUND * HD * 2;
+    uint8_t *Qs = smem_dec, *Ks = Qs + QT, *Vs = Ks + KT;
+    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Vs + KT), *vnew = knew + HD;
+    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ks_u = qs_u + QT, vs_u = ks_u + KT;
+    float *comb_m = reinterpret_cast<float *>(Ks);    // after the last round: [4][16] max, [4][16] sum, [4][G][HD] O
+    float *comb_l = comb_m + 64;
+    float *comb_o = comb_l + 64;
+
+    const int kvh = blockIdx.x, b = blockIdx.y;
+    const int p = pos[b], T = p + 1;                  // keys 0 .. p (p = the new token)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int *bt = block_table + (size_t)b * max_pages;
+    const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
+
+    // RoPE: q heads -> Q tile rows 0..G-1 (bf16, like the q the prefill path stores), k -> cache; v -> cache
+    {
+        const float2 *cs = rope + (size_t)p * HALF;
+        __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
+        __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
+        for (int i = tid; i < (G + 1) * HALF; i += kDecThreads) {
+            const int h = i / HALF, d = i - h * HALF;
+            const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
+            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
+            const float2 c = cs[d];
+            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
+            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            if (h < G) {
+                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, d >> 3) + (d & 7) * 2) = o1;
+                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+            } else {
+                kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2;
+            }
+        }
+        const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
+        for (int i = tid; i < HD; i += kDecThreads) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
+        for (int i = tid; i < (16 - G) * CH; i += kDecThreads)          // padding rows of the Q tile
+            *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    uint32_t qf[HD / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], qs_u + swz<HD>(lane & 15, 2 * ks + (lane >> 4)));
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+    const int g = lane >> 2, tq = lane & 3;
+
+    for (int c0 = 0; c0 < T; c0 += ROUND) {
+        const int n = min(T, c0 + ROUND) - c0;        // valid keys this round
+        const int nfill = (n + 63) & ~63;             // whole 64-key blocks are read by ldmatrix
+        for (int i = tid; i < nfill * CH; i += kDecThreads) {
+            const int r = i / CH, c = i - r * CH;
+            if (r < n) {
+                const int t = c0 + r;
+                const __nv_bfloat16 *kp = pages + (((size_t)bt[t / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD + c * 8;
+                cp_async16(ks_u + swz<HD>(r, c), kp);
+                cp_async16(vs_u + swz<HD>(r, c), kp + (size_t)n_kv * kPage * HD);
+            } else {
+                *reinterpret_cast<uint4 *>(Ks + swz<HD>(r, c)) = make_uint4(0, 0, 0, 0);
+                *reinterpret_cast<uint4 *>(Vs + swz<HD>(r, c)) = make_uint4(0, 0, 0, 0);
+            }
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        // the new token's row comes from this CTA, not from the copy (which raced with the append)
+        if (p >= c0 && p < c0 + ROUND && tid < CH) {
+            *reinterpret_cast<uint4 *>(Ks + swz<HD>(p - c0, tid)) = reinterpret_cast<const uint4 *>(knew)[tid];
+            *reinterpret_cast<uint4 *>(Vs + swz<HD>(p - c0, tid)) = reinterpret_cast<const uint4 *>(vnew)[tid];
+        }
+        __syncthreads();
+
+        const int k0 = warp * 64;                     // this warp's 64-key block inside the round
+        if (k0 < n) {
+            float s[8][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+#pragma unroll
+            for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+                for (int jp = 0; jp < 4; ++jp) {
+                    uint32_t kf[4];
+                    ldsm_x4(kf, ks_u + swz<HD>(k0 + jp * 16 + (lane & 7) + ((lane >> 4) << 3), 2 * ks + ((lane >> 3) & 1)));
+                    mma_bf16(s[2 * jp], qf[ks], kf[0], kf[1]);
+                    mma_bf16(s[2 * jp + 1], qf[ks], kf[2], kf[3]);
+                }
+            }
+            float mx[2] = {mrow[0], mrow[1]};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (k0 + j * 8 + 2 * tq + (e & 1) >= n) s[j][e] = -INFINITY;
+                    mx[e >> 1] = fmaxf(mx[e >> 1], s[j][e]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+                mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+            }
+            float corr[2], msc[2];
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                corr[r] = exp2f((mrow[r] - mx[r]) * scale_log2);
+                mrow[r] = mx[r];
+                msc[r] = mx[r] * scale_log2;
+                lrow[r] *= corr[r];
+            }
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) { o[j][0] *= corr[0]; o[j][1] *= corr[0]; o[j][2] *= corr[1]; o[j][3] *= corr[1]; }
+            uint32_t pf[4][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float p0 = exp2f(s[j][0] * scale_log2 - msc[0]), p1 = exp2f(s[j][1] * scale_log2 - msc[0]);
+                const float p2 = exp2f(s[j][2] * scale_log2 - msc[1]), p3 = exp2f(s[j][3] * scale_log2 - msc[1]);
+                lrow[0] += p0 + p1;
+                lrow[1] += p2 + p3;
+                pf[j >> 1][(j & 1) * 2] = pack2(p0, p1);
+                pf[j >> 1][(j & 1) * 2 + 1] = pack2(p2, p3);
+            }
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+                for (int dp = 0; dp < HD / 16; ++dp) {
+                    uint32_t vf[4];
+                    ldsm_x4_t(vf, vs_u + swz<HD>(k0 + kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), 2 * dp + (lane >> 4)));
+                    mma_bf16(o[2 * dp], pf[kk], vf[0], vf[1]);
+                    mma_bf16(o[2 * dp + 1], pf[kk], vf[2], vf[3]);
+                }
+            }
+        }
+        __syncthreads();                              // K/V of this round fully consumed
+    }
+
+    // merge the four warps' (max, sum, O) -- only rows < G are real query heads
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 2);
+    }
+    if (tq == 0) {
+        comb_m[warp * 16 + g] = mrow[0]; comb_m[warp * 16 + g + 8] = mrow[1];
+        comb_l[warp * 16 + g] = lrow[0]; comb_l[warp * 16 + g + 8] = lrow[1];
+    }
+    if (g < G) {
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) {
+            comb_o[(warp * G + g) * HD + j * 8 + 2 * tq] = o[j][0];
+            comb_o[(warp * G + g) * HD + j * 8 + 2 * tq + 1] = o[j][1];
+        }
+    }
+    if (G > 8 && g + 8 < G) {
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) {
+            comb_o[(warp * G + g + 8) * HD + j * 8 + 2 * tq] = o[j][2];
+            comb_o[(warp * G + g + 8) * HD + j * 8 + 2 * tq + 1] = o[j][3];
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < G * HD; i += kDecThreads) {
+        const int h = i / HD, d = i - h * HD;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) M = fmaxf(M, comb_m[w * 16 + h]);
+        float num = 0.f, den = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const float f = exp2f((comb_m[w * 16 + h] - M) * scale_log2);   // 0 for a warp that saw no keys
+            num += f * comb_o[(w * G + h) * HD + d];
+            den += f * comb_l[w * 16 + h];
+        }
+        out[(size_t)b * out_ld + (size_t)(kvh * G + h) * HD + d] = __float2bfloat16(num / den);
+    }
+}
+
 // ---- greedy argmax over fp32 logits; ties -> lowest index (torch.argmax) ------------
 __global__ void __launch_bounds__(256)
 argmax_kernel(const float *__restrict__ logits, int V, int ld, int *__restrict__ out, int *__restrict__ out2) {
@@ -563,10 +572,10 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
                    int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
                    cudaStream_t st) {
     const int G = n_q / n_kv;
-    (void)max_T;                                      // any context length: K/V are consumed in 32 KB chunks
-    const int ch = 32768 / (hd * 2);
-    const size_t smem = 128 + (size_t)2 * ch * hd * 2 + sizeof(float) * ((size_t)G * hd + (size_t)G * ch + 3 * G) + 4 * hd + 64;
-    const float scale = 1.0f / sqrtf((float)hd);
+    (void)max_T;                                      // any context length: K/V are consumed 256 keys per round
+    KX_REQUIRE(G <= 16, KX_EINVAL, "attention: GQA group of %d query heads per kv head exceeds 16", G);
+    const size_t smem = (size_t)16 * hd * 2 + (size_t)2 * 256 * hd * 2 + 4 * hd + 128;
+    const float scale = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;   // softmax scale in log2 units
     dim3 grid(n_kv, B);
     int rc;
     if (hd == 64)
