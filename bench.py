@@ -376,9 +376,9 @@ def run_generate(args):
         dist.init_process_group("nccl", device_id=dev)
     cfg = model_config.get_config(args.arch)
     total = args.requests
-    per_rank = (total + world - 1) // world                      # strong scaling: the box serves `total` requests
-    r0 = min(total, rank * per_rank)
-    mine = max(1, min(total, r0 + per_rank) - r0)
+    from kubectl_b200 import dist_utils
+    r0, r1 = dist_utils.shard_range(total, rank, world)          # strong scaling: the box serves `total` requests
+    mine = max(1, r1 - r0)
     S, NEW = args.prompt_len, args.new_tokens
     prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
     eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank)
@@ -449,6 +449,12 @@ def run_generate(args):
     sample = max(1, min(mine, args.cpu_requests))
     cpu_rate, cpu_ids, _ = cpu_generation_rate(args.arch, prompts[:sample], S, NEW, args.seed)
     first_diff = [int(np.argmax(np.append(cpu_ids[i] != ids[i], True))) for i in range(sample)]
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "pair_gemm_traffic.json")
+    if os.path.exists(tp):
+        tj = json.load(open(tp))
+        if tj.get("shape") == [gM, 2 * cfg.inter, cfg.hidden]:
+            traffic = tj["dram_bytes_per_launch"]
     line = {
         "metric": "generated kubectl commands/sec (box)", "value": total * args.steps / (dev_ms / 1e3),
         "unit": "commands/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -465,7 +471,7 @@ def run_generate(args):
         "decode_hbm_frac": decode_gbs / pk["hbm_gbs"], "prefill_tflops": prefill_flops / (prefill_ms * 1e-3) / 1e12,
         "prefill_tensor_frac": prefill_flops / (prefill_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
         "roofline": {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / pk["bf16_tflops"], "traffic": None, "peak_source": pk["source"] + " (burst: kernel timed alone)",
+                     "frac": gemm_tflops / pk["bf16_tflops"], "traffic": traffic, "peak_source": pk["source"] + " (burst: kernel timed alone)",
                      "kernel": "kx_gemm_bf16_kernel (prefill, SwiGLU epilogue)", "kernel_ms": gemm_ms,
                      "shape": [gM, 2 * cfg.inter, cfg.hidden],
                      "algorithmic_flops_per_launch": 2.0 * gM * 2 * cfg.inter * cfg.hidden},
