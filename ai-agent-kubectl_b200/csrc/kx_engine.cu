@@ -41,6 +41,12 @@ struct kx_engine {
     void *scratch = nullptr;
     size_t scratch_bytes = 0;
     cudaStream_t stream = nullptr;                 // the engine's own stream (the decode loop is captured on it)
+    // tensor parallelism: partial sums of the row-parallel layers, argmax pairs, NCCL entry points
+    float *tp_buf = nullptr;
+    void *tp_pairs = nullptr, *tp_gathered = nullptr;
+    void *comm = nullptr;
+    int (*allreduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*allgather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
     int64_t device_bytes = 0;
     std::vector<void *> owned;
 };
@@ -126,6 +132,18 @@ int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, co
                         out, ldo, bias}, st);
 }
 
+// Row-parallel linear layer whose result is added to the residual stream.  With tensor
+// parallelism every rank holds a partial sum: it goes to tp_buf, is all-reduced, then added.
+int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    if (d.tp_size <= 1) return linear(e, l, M, EPI_RESID, e->resid, d.hidden, nullptr, st);
+    KX_REQUIRE(e->comm && e->allreduce, KX_EINVAL, "engine: tensor parallelism needs kx_engine_set_collectives");
+    KX_TRY(linear(e, l, M, EPI_F32, e->tp_buf, d.hidden, nullptr, st));
+    const int rc = e->allreduce(e->tp_buf, e->tp_buf, (size_t)M * d.hidden, /*ncclFloat32*/ 7, /*ncclSum*/ 0, e->comm, st);
+    KX_REQUIRE(rc == 0, KX_ECUDA, "engine: ncclAllReduce failed with %d", rc);
+    return op_add_inplace(e->resid, e->tp_buf, (size_t)M * d.hidden, st);
+}
+
 // One transformer layer over M token rows.  decode: rows are one token per sequence.
 int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st) {
     const kx_model_desc &d = e->d;
@@ -145,11 +163,22 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, 0, d.n_q, d.n_kv, d.head_dim, st));
     }
-    KX_TRY(linear(e, wo, M, EPI_RESID, e->resid, d.hidden, nullptr, st));
+    KX_TRY(linear_resid(e, wo, M, st));
     KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
     KX_TRY(linear(e, wgu, M, EPI_SWIGLU, e->mlp, d.inter, nullptr, st));
-    KX_TRY(linear(e, wd, M, EPI_RESID, e->resid, d.hidden, nullptr, st));
+    KX_TRY(linear_resid(e, wd, M, st));
     return KX_OK;
+}
+
+// greedy token per sequence from e->logits (this rank's vocabulary shard under tensor parallelism)
+int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    if (d.tp_size <= 1) return op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st);
+    KX_REQUIRE(e->comm && e->allgather, KX_EINVAL, "engine: tensor parallelism needs kx_engine_set_collectives");
+    KX_TRY(op_argmax_pairs(e->logits, B, d.vocab, d.vocab, d.vocab_offset, e->tp_pairs, st));
+    const int rc = e->allgather(e->tp_pairs, e->tp_gathered, (size_t)B * 8, /*ncclInt8*/ 0, e->comm, st);
+    KX_REQUIRE(rc == 0, KX_ECUDA, "engine: ncclAllGather failed with %d", rc);
+    return op_pick(e->tp_gathered, d.tp_size, B, e->next_tok, st);
 }
 
 // final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
@@ -160,7 +189,7 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
     KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
-    KX_TRY(op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st));
+    KX_TRY(greedy_pick(e, B, st));
     store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
     count_launch();
     KX_CUDA(cudaGetLastError());
@@ -207,6 +236,11 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     KX_E(dev_alloc(e, (void **)&e->out_ids, (size_t)d.max_batch * d.max_seq * 4));
     KX_E(dev_alloc(e, (void **)&e->block_table, (size_t)d.max_batch * e->max_pages * 4));
     KX_E(dev_alloc(e, (void **)&e->step, 4));
+    if (d.tp_size > 1) {
+        KX_E(dev_alloc(e, (void **)&e->tp_buf, Mx * d.hidden * 4));
+        KX_E(dev_alloc(e, &e->tp_pairs, (size_t)d.max_batch * 8));
+        KX_E(dev_alloc(e, &e->tp_gathered, (size_t)d.max_batch * 8 * d.tp_size));
+    }
     // split-K scratch for the largest decode GEMM: tiles * 128 * bn floats + tickets
     {
         size_t best = 0;
@@ -258,6 +292,14 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     }
 #undef KX_E
     *out = e;
+    return KX_OK;
+}
+
+extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allreduce, void *allgather) {
+    KX_REQUIRE(e && comm && allreduce && allgather, KX_EINVAL, "kx_engine_set_collectives: NULL argument");
+    e->comm = comm;
+    e->allreduce = reinterpret_cast<decltype(e->allreduce)>(allreduce);
+    e->allgather = reinterpret_cast<decltype(e->allgather)>(allgather);
     return KX_OK;
 }
 
@@ -318,7 +360,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         }
     }
     if (d_logits) KX_CUDA(cudaMemcpyAsync(d_logits, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
-    KX_TRY(op_argmax(e->logits, B, d.vocab, d.vocab, e->next_tok, nullptr, st));
+    KX_TRY(greedy_pick(e, B, st));
     store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
     count_launch();
     KX_CUDA(cudaEventRecord(ev1, st));

@@ -512,6 +512,56 @@ argmax_kernel(const float *__restrict__ logits, int V, int ld, int *__restrict__
     }
 }
 
+// ---- tensor-parallel helpers -----------------------------------------------------
+__global__ void add_inplace_kernel(float *__restrict__ x, const float *__restrict__ d, size_t n4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n4) {
+        float4 a = reinterpret_cast<float4 *>(x)[i];
+        const float4 b = reinterpret_cast<const float4 *>(d)[i];
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        reinterpret_cast<float4 *>(x)[i] = a;
+    }
+}
+// per-shard argmax -> (value bits, global id) pairs; merged by pick_kernel after an all-gather
+__global__ void __launch_bounds__(256)
+argmax_pair_kernel(const float *__restrict__ logits, int V, int ld, int id_offset, int2 *__restrict__ pairs) {
+    const int b = blockIdx.x;
+    const float *row = logits + (size_t)b * ld;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < V; i += 256) {
+        const float a = row[i];
+        if (a > best || (a == best && i < bi)) { best = a; bi = i; }
+    }
+    __shared__ float sb[8];
+    __shared__ int si[8];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sb[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w)
+            if (sb[w] > best || (sb[w] == best && si[w] < bi)) { best = sb[w]; bi = si[w]; }
+        pairs[b] = make_int2(__float_as_int(best), bi + id_offset);
+    }
+}
+__global__ void pick_kernel(const int2 *__restrict__ gathered, int tp, int B, int *__restrict__ out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int r = 0; r < tp; ++r) {
+        const int2 p = gathered[(size_t)r * B + b];
+        const float v = __int_as_float(p.x);
+        if (v > best || (v == best && p.y < bi)) { best = v; bi = p.y; }
+    }
+    out[b] = bi;
+}
+
 // positions / bookkeeping for the decode loop, kept on the device so a step can be a CUDA graph
 __global__ void advance_kernel(int *pos, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -618,6 +668,28 @@ int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const vo
 
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st) {
     argmax_kernel<<<B, 256, 0, st>>>(logits, V, ld, out, out2);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st) {
+    const size_t n4 = n / 4;
+    add_inplace_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(x, d, n4);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+int op_argmax_pairs(const float *logits, int B, int V, int ld, int id_offset, void *pairs, cudaStream_t st) {
+    argmax_pair_kernel<<<B, 256, 0, st>>>(logits, V, ld, id_offset, (int2 *)pairs);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+int op_pick(const void *gathered, int tp, int B, int *out, cudaStream_t st) {
+    pick_kernel<<<(B + 127) / 128, 128, 0, st>>>((const int2 *)gathered, tp, B, out);
     count_launch();
     KX_CUDA(cudaGetLastError());
     return KX_OK;

@@ -19,5 +19,9 @@ int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const vo
                     int max_pages, int B, int S, int pos0, int n_q, int n_kv, int hd, cudaStream_t st);
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st);
 int op_advance(int *pos, int n, cudaStream_t st);
+// tensor-parallel helpers
+int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st);
+int op_argmax_pairs(const float *logits, int B, int V, int ld, int id_offset, void *pairs, cudaStream_t st);
+int op_pick(const void *gathered, int tp, int B, int *out, cudaStream_t st);
 
 }  // namespace kx

@@ -22,7 +22,8 @@ c_int32, c_float, c_void_p = ctypes.c_int32, ctypes.c_float, ctypes.c_void_p
 
 class KxModelDesc(ctypes.Structure):
     _fields_ = [(n, c_int32) for n in ("hidden", "layers", "n_q", "n_kv", "head_dim", "inter", "vocab", "max_pos")] + \
-               [("eps", c_float), ("max_batch", c_int32), ("max_seq", c_int32), ("prefill_chunk", c_int32)]
+               [("eps", c_float), ("max_batch", c_int32), ("max_seq", c_int32), ("prefill_chunk", c_int32),
+                ("tp_size", c_int32), ("tp_rank", c_int32), ("vocab_offset", c_int32)]
 
 
 class KxLayerWeights(ctypes.Structure):
@@ -40,35 +41,93 @@ class KxGenStats(ctypes.Structure):
 
 _lib.declare("kx_engine_create", ctypes.c_int, [ctypes.POINTER(KxModelDesc), ctypes.POINTER(KxModelWeights),
                                                  ctypes.POINTER(c_void_p)])
+_lib.declare("kx_engine_set_collectives", ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_generate", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p,
                                                    ctypes.POINTER(KxGenStats), c_void_p])
 
 
-def pack_weights(cfg: ModelConfig, w: Dict, device) -> Dict:
-    """Logical tensors (weights.make_weights) -> the layouts of include/kx.h on `device`."""
+def pack_weights(cfg: ModelConfig, w: Dict, device, tp_rank: int = 0, tp_size: int = 1) -> Dict:
+    """Logical tensors (weights.make_weights) -> the layouts of include/kx.h on `device`.
+    With tp_size > 1 only this rank's shard is packed: q/k/v heads, gate/up rows and the
+    vocabulary are split by rows (column-parallel), wo / wd by input columns (row-parallel)."""
     import torch
+
+    def rows(t, n_units, unit):           # contiguous block of n_units/tp units of `unit` rows
+        per = n_units // tp_size
+        return t[tp_rank * per * unit:(tp_rank + 1) * per * unit]
+
+    hd = cfg.head_dim
+    head = w["embed"] if cfg.tied else w["lm_head"]
     out = {"embed": w["embed"].to(device), "norm": w["norm"].to(device), "layers": []}
-    out["lm_head"] = out["embed"] if cfg.tied else w["lm_head"].to(device)
+    if tp_size == 1:
+        out["lm_head"] = out["embed"] if cfg.tied else head.to(device)
+    else:
+        out["lm_head"] = rows(head, cfg.vocab, 1).contiguous().to(device)
     for i in range(cfg.layers):
-        wgu = torch.stack([w[f"wg.{i}"], w[f"wu.{i}"]], dim=1).reshape(2 * cfg.inter, cfg.hidden)   # rows g0,u0,g1,u1,...
+        wg, wu = rows(w[f"wg.{i}"], cfg.inter, 1), rows(w[f"wu.{i}"], cfg.inter, 1)
+        wgu = torch.stack([wg, wu], dim=1).reshape(2 * wg.shape[0], cfg.hidden)   # rows g0,u0,g1,u1,...
+        qcols = slice(tp_rank * cfg.q_dim // tp_size, (tp_rank + 1) * cfg.q_dim // tp_size)
+        icols = slice(tp_rank * cfg.inter // tp_size, (tp_rank + 1) * cfg.inter // tp_size)
         layer = {
             "ln1": w[f"ln1.{i}"].to(device), "ln2": w[f"ln2.{i}"].to(device),
-            "wqkv": torch.cat([w[f"wq.{i}"], w[f"wk.{i}"], w[f"wv.{i}"]], dim=0).contiguous().to(device),
-            "bqkv": (torch.cat([w[f"bq.{i}"], w[f"bk.{i}"], w[f"bv.{i}"]]).float().to(device) if cfg.qkv_bias else None),
-            "wo": w[f"wo.{i}"].contiguous().to(device), "wgu": wgu.contiguous().to(device),
-            "wd": w[f"wd.{i}"].contiguous().to(device),
+            "wqkv": torch.cat([rows(w[f"wq.{i}"], cfg.n_q, hd), rows(w[f"wk.{i}"], cfg.n_kv, hd),
+                               rows(w[f"wv.{i}"], cfg.n_kv, hd)], dim=0).contiguous().to(device),
+            "bqkv": (torch.cat([rows(w[f"bq.{i}"], cfg.n_q, hd), rows(w[f"bk.{i}"], cfg.n_kv, hd),
+                                rows(w[f"bv.{i}"], cfg.n_kv, hd)]).float().to(device) if cfg.qkv_bias else None),
+            "wo": w[f"wo.{i}"][:, qcols].contiguous().to(device), "wgu": wgu.contiguous().to(device),
+            "wd": w[f"wd.{i}"][:, icols].contiguous().to(device),
         }
         out["layers"].append(layer)
     return out
+
+
+class NcclComm:
+    """A NCCL communicator created through the C API of the libnccl torch already loaded,
+    so that the engine (C++) can enqueue collectives on its own stream.  The unique id is
+    shared through torch.distributed (any backend)."""
+
+    def __init__(self, rank: int, world: int, device: int, group=None):
+        import glob
+        import os
+        import torch
+        import torch.distributed as dist
+        cands = glob.glob(os.path.join(os.path.dirname(os.path.dirname(torch.__file__)), "nvidia", "nccl", "lib", "libnccl.so*"))
+        self.lib = ctypes.CDLL(cands[0] if cands else "libnccl.so.2")
+        uid = (ctypes.c_byte * 128)()
+        if rank == 0:
+            assert self.lib.ncclGetUniqueId(ctypes.byref(uid)) == 0
+        box = [bytes(uid)]
+        dist.broadcast_object_list(box, src=0, group=group)
+        ctypes.memmove(uid, box[0], 128)
+        self.comm = c_void_p()
+
+        class _Uid(ctypes.Structure):
+            _fields_ = [("b", ctypes.c_byte * 128)]
+        u = _Uid()
+        ctypes.memmove(ctypes.byref(u), uid, 128)
+        self.lib.ncclCommInitRank.argtypes = [ctypes.POINTER(c_void_p), ctypes.c_int, _Uid, ctypes.c_int]
+        with torch.cuda.device(device):
+            rc = self.lib.ncclCommInitRank(ctypes.byref(self.comm), world, u, rank)
+        if rc != 0:
+            raise RuntimeError(f"ncclCommInitRank failed with {rc}")
+        self.allreduce = ctypes.cast(self.lib.ncclAllReduce, c_void_p)
+        self.allgather = ctypes.cast(self.lib.ncclAllGather, c_void_p)
+
+    def close(self):
+        if self.comm:
+            self.lib.ncclCommDestroy.argtypes = [c_void_p]
+            self.lib.ncclCommDestroy(self.comm)
+            self.comm = None
 
 
 class Generator:
     """One model replica on one GPU."""
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, max_seq: int = 320, device: int = 0,
-                 weights: Optional[Dict] = None, prefill_chunk: int = 32768):
+                 weights: Optional[Dict] = None, prefill_chunk: int = 32768, tp_rank: int = 0, tp_size: int = 1,
+                 nccl: Optional["NcclComm"] = None):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("the generator needs a CUDA device; there is no CPU fallback")
@@ -77,11 +136,16 @@ class Generator:
         self.max_batch, self.max_seq = max_batch, max_seq
         self.logical = weights if weights is not None else weights_mod.make_weights(self.cfg, seed)
         with torch.cuda.device(self.device):
-            self.packed = pack_weights(self.cfg, self.logical, self.device)
+            self.packed = pack_weights(self.cfg, self.logical, self.device, tp_rank, tp_size)
             self.rope = weights_mod.rope_table(self.cfg, self.cfg.max_pos).to(self.device)
             c = self.cfg
-            desc = KxModelDesc(c.hidden, c.layers, c.n_q, c.n_kv, c.head_dim, c.inter, c.vocab, c.max_pos, c.eps,
-                               max_batch, max_seq, prefill_chunk)
+            if tp_size > 1 and (c.n_q % tp_size or c.n_kv % tp_size or c.inter % tp_size or c.vocab % (8 * tp_size)):
+                raise ValueError(f"{arch} cannot be split {tp_size} ways")
+            self.tp_rank, self.tp_size = tp_rank, tp_size
+            self.vocab_local = c.vocab // tp_size
+            desc = KxModelDesc(c.hidden, c.layers, c.n_q // tp_size, c.n_kv // tp_size, c.head_dim, c.inter // tp_size,
+                               self.vocab_local, c.max_pos, c.eps, max_batch, max_seq, prefill_chunk,
+                               tp_size, tp_rank, tp_rank * self.vocab_local)
             arr = (KxLayerWeights * c.layers)()
             for i, l in enumerate(self.packed["layers"]):
                 arr[i] = KxLayerWeights(l["ln1"].data_ptr(), l["wqkv"].data_ptr(),
@@ -93,6 +157,11 @@ class Generator:
             h = c_void_p()
             _lib.check(_lib.lib().kx_engine_create(ctypes.byref(desc), ctypes.byref(mw), ctypes.byref(h)))
             self._h = h
+            if tp_size > 1:
+                if nccl is None:
+                    raise ValueError("tensor parallelism needs an NcclComm")
+                self.nccl = nccl
+                _lib.check(_lib.lib().kx_engine_set_collectives(h, nccl.comm, nccl.allreduce, nccl.allgather))
         self.last_stats: Optional[KxGenStats] = None
 
     def device_bytes(self) -> int:
@@ -106,7 +175,7 @@ class Generator:
         out = np.empty((B, n_new), np.int32)
         stats = KxGenStats()
         with torch.cuda.device(self.device):
-            logits = torch.empty((n_new, B, self.cfg.vocab), dtype=torch.float32, device=self.device) if want_logits else None
+            logits = torch.empty((n_new, B, self.vocab_local), dtype=torch.float32, device=self.device) if want_logits else None
             st = torch.cuda.current_stream(self.device).cuda_stream
             _lib.check(_lib.lib().kx_engine_generate(self._h, tokens.ctypes.data, B, S, n_new, out.ctypes.data,
                                                      logits.data_ptr() if want_logits else None, ctypes.byref(stats), st))

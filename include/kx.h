@@ -156,6 +156,11 @@ typedef struct kx_model_desc {
     int32_t max_batch;      /* sequences resident at once                              */
     int32_t max_seq;        /* prompt + generated tokens per sequence                  */
     int32_t prefill_chunk;  /* max tokens per prefill pass (0 = default 32768)         */
+    /* tensor parallelism: with tp_size > 1 the head counts, `inter` and
+     * `vocab` above are this rank's SHARD (column-parallel wqkv / wgu, row-parallel wo / wd,
+     * vocabulary-parallel lm_head); `hidden` is full.  vocab_offset = first vocabulary id of
+     * the shard.  The collectives are supplied with kx_engine_set_collectives.             */
+    int32_t tp_size, tp_rank, vocab_offset;
 } kx_model_desc;
 
 typedef struct kx_layer_weights {
@@ -180,6 +185,16 @@ typedef struct kx_gen_stats {
 typedef struct kx_engine kx_engine;
 
 int kx_engine_create(const kx_model_desc *desc, const kx_model_weights *weights, kx_engine **out);
+
+/*
+ * Tensor-parallel engines reduce the row-parallel partial sums (two all-reduces of
+ * [tokens, hidden] fp32 per layer) and merge the per-shard argmax (one all-gather of
+ * [batch] (value, id) pairs per step) through caller-supplied NCCL entry points:
+ *   comm       an ncclComm_t spanning the tp_size ranks
+ *   allreduce  address of ncclAllReduce, allgather address of ncclAllGather
+ * They are enqueued on the engine's stream (and captured into its decode graph).
+ */
+int kx_engine_set_collectives(kx_engine *e, void *comm, void *allreduce, void *allgather);
 void kx_engine_destroy(kx_engine *e);
 int64_t kx_engine_device_bytes(const kx_engine *e);
 

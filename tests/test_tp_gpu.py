@@ -1,0 +1,59 @@
+"""Tensor parallelism: TP=2 over two GPUs against the CPU oracle.
+Needs two CUDA devices (run with `gpurun --gpus 2`); skipped on a single-GPU box."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, arch, B, S, n_new, out_dir):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine, model_config, weights
+    cfg = model_config.get_config(arch)
+    w = weights.make_weights(cfg, 3)
+    nccl = engine.NcclComm(rank, world, rank)
+    gen = engine.Generator(arch, weights=w, max_batch=B, max_seq=S + n_new, device=rank, tp_rank=rank, tp_size=world, nccl=nccl)
+    toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(103)).numpy().astype(np.int32)
+    ids, logits = gen.generate_ids(toks, n_new, want_logits=True)
+    ids2, _ = gen.generate_ids(toks, n_new)                       # CUDA-graph decode with captured collectives
+    torch.save({"ids": ids, "ids2": ids2, "logits": logits.cpu()}, os.path.join(out_dir, f"tp{rank}.pt"))
+    gen.close()
+    nccl.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-qwen2"])
+def test_tp2_matches_the_oracle(tmp_path, arch):
+    import torch.multiprocessing as mp
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import model_config, weights
+    from oracle.cpu_model import RefModel
+    B, S, n_new = 6, 70, 6
+    mp.spawn(_worker, args=(2, _free_port(), arch, B, S, n_new, str(tmp_path)), nprocs=2, join=True)
+    r = [torch.load(tmp_path / f"tp{i}.pt", weights_only=False) for i in range(2)]
+    assert np.array_equal(r[0]["ids"], r[1]["ids"]) and np.array_equal(r[0]["ids"], r[0]["ids2"])
+    cfg = model_config.get_config(arch)
+    w = weights.make_weights(cfg, 3)
+    ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True)
+    toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(103))
+    want_ids, want_logits = ref.generate(toks, n_new, return_logits=True)
+    logits = torch.cat([r[0]["logits"], r[1]["logits"]], dim=-1)   # vocabulary shards side by side
+    for t in range(n_new):
+        err = (logits[t] - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
+        assert err <= 1e-2, f"step {t}: logits off by {err:.2e}"
+    assert np.array_equal(r[0]["ids"], want_ids.numpy())
