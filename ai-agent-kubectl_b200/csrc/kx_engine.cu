@@ -27,6 +27,7 @@ struct LayerPlan {
 struct kx_engine {
     kx_model_desc d;
     int qkv_dim, q_dim, max_pages, num_pages, max_tokens;
+    int prefix_len = 0;                            // tokens of shared prefix whose KV is already cached (multiple of 16)
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
     const float *rope;
@@ -145,7 +146,7 @@ int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st) {
 }
 
 // One transformer layer over M token rows.  decode: rows are one token per sequence.
-int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st) {
+int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st, int pos0 = 0) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
     const Linear qkv{&L.wqkv, L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden};
@@ -161,7 +162,7 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
                               d.n_q, d.n_kv, d.head_dim, st));
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
-                               e->max_pages, nb, S, 0, d.n_q, d.n_kv, d.head_dim, st));
+                               e->max_pages, nb, S, pos0, d.n_q, d.n_kv, d.head_dim, st));
     }
     KX_TRY(linear_resid(e, wo, M, st));
     KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
@@ -212,7 +213,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
     e->q_dim = d.n_q * d.head_dim;
     e->max_pages = (d.max_seq + KX_KV_PAGE - 1) / KX_KV_PAGE;
-    e->num_pages = e->max_pages * d.max_batch;
+    e->num_pages = e->max_pages * (d.max_batch + 1);   // + one sequence worth of pages for a shared prefix
     if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { delete e; set_error("kx_engine_create: cannot create a stream"); return KX_ECUDA; }
     e->embed = w->embed; e->lm_head = w->lm_head; e->norm = w->norm; e->rope = w->rope;
     // prefill works on whole sequences, so the token buffers hold at least one chunk or one full batch of prompts
@@ -234,7 +235,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     KX_E(dev_alloc(e, (void **)&e->last_rows, (size_t)d.max_batch * 4));
     KX_E(dev_alloc(e, (void **)&e->next_tok, (size_t)d.max_batch * 4));
     KX_E(dev_alloc(e, (void **)&e->out_ids, (size_t)d.max_batch * d.max_seq * 4));
-    KX_E(dev_alloc(e, (void **)&e->block_table, (size_t)d.max_batch * e->max_pages * 4));
+    KX_E(dev_alloc(e, (void **)&e->block_table, (size_t)(d.max_batch + 1) * e->max_pages * 4));
     KX_E(dev_alloc(e, (void **)&e->step, 4));
     if (d.tp_size > 1) {
         KX_E(dev_alloc(e, (void **)&e->tp_buf, Mx * d.hidden * 4));
@@ -256,7 +257,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     }
     // static block table: sequence b owns pages [b * max_pages, (b+1) * max_pages)
     {
-        std::vector<int> bt((size_t)d.max_batch * e->max_pages);
+        std::vector<int> bt((size_t)(d.max_batch + 1) * e->max_pages);
         for (size_t i = 0; i < bt.size(); ++i) bt[i] = (int)i;
         if (cudaMemcpy(e->block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) return fail(KX_ECUDA);
     }
@@ -303,6 +304,42 @@ extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allredu
     return KX_OK;
 }
 
+extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32_t n, void *stream) {
+    KX_REQUIRE(e, KX_EINVAL, "kx_engine_set_prefix: NULL engine");
+    const kx_model_desc &d = e->d;
+    KX_REQUIRE(n >= 0 && n % KX_KV_PAGE == 0, KX_EINVAL, "kx_engine_set_prefix: length %d is not a multiple of %d", n, KX_KV_PAGE);
+    KX_REQUIRE(n < d.max_seq && n <= e->max_tokens, KX_ETOOBIG, "kx_engine_set_prefix: prefix of %d tokens is too long", n);
+    KX_REQUIRE(n == 0 || h_tokens, KX_EINVAL, "kx_engine_set_prefix: NULL tokens");
+    cudaStream_t st = e->stream;
+    cudaEvent_t ev;
+    KX_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    KX_CUDA(cudaEventRecord(ev, (cudaStream_t)stream));
+    KX_CUDA(cudaStreamWaitEvent(st, ev, 0));
+    cudaEventDestroy(ev);
+    // block table: every sequence's first n/16 pages alias the prefix sequence's pages (row max_batch)
+    const int pp = n / KX_KV_PAGE;
+    std::vector<int> bt((size_t)(d.max_batch + 1) * e->max_pages);
+    for (int b = 0; b <= d.max_batch; ++b)
+        for (int i = 0; i < e->max_pages; ++i)
+            bt[(size_t)b * e->max_pages + i] = (b < d.max_batch && i < pp) ? d.max_batch * e->max_pages + i : b * e->max_pages + i;
+    KX_CUDA(cudaMemcpyAsync(e->block_table, bt.data(), bt.size() * 4, cudaMemcpyHostToDevice, st));
+    KX_CUDA(cudaStreamSynchronize(st));
+    e->prefix_len = 0;
+    if (n == 0) return KX_OK;
+    // prefill the prefix once, as the extra sequence `max_batch`
+    std::vector<int> hpos(n), hseq(n, d.max_batch);
+    for (int t = 0; t < n; ++t) hpos[t] = t;
+    KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    KX_CUDA(cudaStreamSynchronize(st));
+    KX_TRY(op_embed(e->tokens, e->embed, e->resid, n, d.hidden, st));
+    for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, n, false, 1, n, d.max_batch, 0, st, 0));
+    KX_CUDA(cudaStreamSynchronize(st));
+    e->prefix_len = n;
+    return KX_OK;
+}
+
 extern "C" void kx_engine_destroy(kx_engine *e) {
     if (!e) return;
     for (void *p : e->owned) cudaFree(p);
@@ -317,8 +354,9 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     KX_REQUIRE(e && h_tokens && h_out, KX_EINVAL, "kx_engine_generate: NULL argument");
     const kx_model_desc &d = e->d;
     KX_REQUIRE(B >= 1 && B <= d.max_batch, KX_ETOOBIG, "kx_engine_generate: batch %d exceeds max_batch %d", B, d.max_batch);
-    KX_REQUIRE(S >= 1 && n_new >= 1 && S + n_new <= d.max_seq, KX_ETOOBIG,
-               "kx_engine_generate: %d prompt + %d new tokens exceed max_seq %d", S, n_new, d.max_seq);
+    const int P = e->prefix_len;
+    KX_REQUIRE(S >= 1 && n_new >= 1 && P + S + n_new <= d.max_seq, KX_ETOOBIG,
+               "kx_engine_generate: %d cached + %d prompt + %d new tokens exceed max_seq %d", P, S, n_new, d.max_seq);
     // Work runs on the engine's own stream (a legacy default stream cannot be captured into a
     // graph); it is ordered after whatever the caller already enqueued on `stream`.
     cudaStream_t st = e->stream;
@@ -341,13 +379,13 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         const int M = nb * S;
         hpos.resize(M); hseq.resize(M);
         for (int b = 0; b < nb; ++b)
-            for (int t = 0; t < S; ++t) { hpos[b * S + t] = t; hseq[b * S + t] = b0 + b; }
+            for (int t = 0; t < S; ++t) { hpos[b * S + t] = P + t; hseq[b * S + t] = b0 + b; }
         KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens + (size_t)b0 * S, (size_t)M * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaStreamSynchronize(st));          // hpos/hseq are reused by the next chunk
         KX_TRY(op_embed(e->tokens, e->embed, e->resid, M, d.hidden, st));
-        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, b0, 0, st));
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, b0, 0, st, P));
         // first token of this chunk's sequences: final norm on each last prompt row
         std::vector<int> rows(nb);
         for (int b = 0; b < nb; ++b) rows[b] = b * S + S - 1;
@@ -367,13 +405,13 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
 
     // ---- decode: positions S, S+1, ... one token per sequence ----
     {
-        std::vector<int> p0(B, S - 1), sq(B);          // advance_step_kernel moves to S before the first use
+        std::vector<int> p0(B, P + S - 1), sq(B);      // advance_step_kernel moves to P + S before the first use
         for (int b = 0; b < B; ++b) sq[b] = b;
         KX_CUDA(cudaMemcpyAsync(e->pos, p0.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->seq, sq.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaStreamSynchronize(st));
     }
-    const int max_T = S + n_new;
+    const int max_T = P + S + n_new;
     auto step_once = [&](float *logits_dst) -> int {
         // pos[b] currently holds the previous token's position
         advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);

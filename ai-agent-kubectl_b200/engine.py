@@ -42,6 +42,7 @@ class KxGenStats(ctypes.Structure):
 _lib.declare("kx_engine_create", ctypes.c_int, [ctypes.POINTER(KxModelDesc), ctypes.POINTER(KxModelWeights),
                                                  ctypes.POINTER(c_void_p)])
 _lib.declare("kx_engine_set_collectives", ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p])
+_lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_generate", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p,
@@ -166,6 +167,14 @@ class Generator:
 
     def device_bytes(self) -> int:
         return int(_lib.lib().kx_engine_device_bytes(self._h))
+
+    def set_prefix(self, tokens) -> None:
+        """Prefill a shared prefix once (length a multiple of 16); later prompts continue it."""
+        import torch
+        toks = np.ascontiguousarray(tokens, np.int32).reshape(-1)
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            _lib.check(_lib.lib().kx_engine_set_prefix(self._h, toks.ctypes.data if toks.size else None, toks.size, st))
 
     def generate_ids(self, tokens: np.ndarray, n_new: int, want_logits: bool = False):
         """tokens int32 [B, S] -> (ids int32 [B, n_new], logits torch fp32 [n_new, B, V] or None)."""

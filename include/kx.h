@@ -199,6 +199,15 @@ void kx_engine_destroy(kx_engine *e);
 int64_t kx_engine_device_bytes(const kx_engine *e);
 
 /*
+ * kx_engine_set_prefix -- prefill `n` tokens (a multiple of 16; host int32) ONCE and keep their
+ * KV pages; every later kx_engine_generate treats its prompts as continuing that prefix
+ * (positions start at n, the pages are shared by all sequences through the block table).
+ * This is the prefix cache for the constant part of the reference's prompt template
+ * (app.py:50-57) and for BASELINE config 5's system prompt.  n = 0 removes the prefix.
+ */
+int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32_t n, void *stream);
+
+/*
  * kx_engine_generate -- prefill `batch` prompts of `prompt_len` tokens each (host int32
  * [batch, prompt_len]) and decode `n_new` tokens greedily; h_out receives int32
  * [batch, n_new].  d_logits (device fp32 [n_new, batch, vocab]) may be NULL; when given,

@@ -102,3 +102,26 @@ def test_qwen25_05b_full_architecture():
     q/k/v biases), 256-token prompts, 32 greedy tokens, on a subset of the batch the CPU oracle
     can finish in seconds."""
     _check("qwen2.5-0.5b", B=4, S=256, n_new=32, seed=3)
+
+
+@pytest.mark.parametrize("arch", ["tiny-llama", "tiny-qwen2"])
+def test_prefix_cached_kv_equals_full_prefill(arch):
+    """A shared prefix prefilled once (kx_engine_set_prefix) + per-request suffixes must give
+    what prefilling prefix + suffix for every request gives (oracle: the full prompts)."""
+    B, P, S, n_new = 6, 64, 23, 6
+    cfg, gen, ref_emu, _ = _setup(arch, 3, B, P + S, n_new)
+    g = torch.Generator().manual_seed(5)
+    prefix = torch.randint(0, cfg.vocab, (P,), generator=g)
+    suffix = torch.randint(0, cfg.vocab, (B, S), generator=g)
+    gen.set_prefix(prefix.numpy())
+    ids, logits = gen.generate_ids(suffix.numpy().astype(np.int32), n_new, want_logits=True)
+    full = torch.cat([prefix[None, :].expand(B, P), suffix], dim=1)
+    want_ids, want_logits = ref_emu.generate(full, n_new, return_logits=True)
+    for t in range(n_new):
+        err = (logits[t].cpu() - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
+        assert err <= 1e-2, f"step {t}: {err:.2e}"
+    assert np.array_equal(ids, want_ids.numpy())
+    gen.set_prefix(np.zeros(0, np.int32))                       # and the engine still works without a prefix
+    ids2, _ = gen.generate_ids(full.numpy().astype(np.int32)[:, :P + S], n_new)
+    assert np.array_equal(ids2, want_ids.numpy())
+    gen.close()
