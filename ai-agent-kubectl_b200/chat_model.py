@@ -162,6 +162,7 @@ class BatchingFrontend:
         self.engine, self.max_wait = engine, max_wait_ms / 1e3
         self.q: "queue.Queue[Optional[_Request]]" = queue.Queue()
         self.dropped = 0
+        self.coalesced = 0
         self._thr = threading.Thread(target=self._run, name="kx-engine", daemon=True)
         self._thr.start()
 
@@ -172,6 +173,11 @@ class BatchingFrontend:
         self.q.put(None)
         self._thr.join(timeout=5)
         self.engine.close()
+
+    @staticmethod
+    def _group_cancelled(live, prompt):
+        group = [r for r in live if r.prompt == prompt]
+        return lambda: all(r.cancelled() for r in group)     # only drop the work if every waiter is gone
 
     def _resolve(self, req: _Request, result=None, exc: Optional[BaseException] = None):
         def set_async():
@@ -215,12 +221,22 @@ class BatchingFrontend:
                     live.append(r)
             if not live:
                 continue
+            # Single flight inside the batch: identical prompts (the reference generates twice when two
+            # identical queries miss the cache concurrently, app.py:312-322) are generated once and the
+            # completion is fanned out.  Greedy decoding makes the duplicates' outputs identical anyway.
+            first, uniq = {}, []
+            for r in live:
+                if r.prompt not in first:
+                    first[r.prompt] = len(uniq)
+                    uniq.append(r)
+            self.coalesced += len(live) - len(uniq)
             try:
-                outs = self.engine.generate([r.prompt for r in live], [r.cancelled for r in live])
-                if len(outs) != len(live):
-                    raise RuntimeError(f"engine returned {len(outs)} completions for {len(live)} prompts")
-                for r, o in zip(live, outs):
-                    self._resolve(r, result=o)
+                outs = self.engine.generate([r.prompt for r in uniq],
+                                            [self._group_cancelled(live, r.prompt) for r in uniq])
+                if len(outs) != len(uniq):
+                    raise RuntimeError(f"engine returned {len(outs)} completions for {len(uniq)} prompts")
+                for r in live:
+                    self._resolve(r, result=outs[first[r.prompt]])
             except BaseException as e:  # noqa: BLE001 - surfaced to every waiter as a 500
                 err = e if isinstance(e, RuntimeError) else RuntimeError(f"{type(e).__name__}: {e}")
                 for r in live:

@@ -209,18 +209,54 @@ class B200Engine(Engine):
     tokens are decoded greedily and the ids are mapped back to text."""
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
-                 device: int = 0):
-        self.gen = Generator(arch, seed=seed, max_batch=max_batch, max_seq=prompt_len + max_new, device=device)
+                 device: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl: Optional[NcclComm] = None,
+                 prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512):
+        self.auto_prefix, self.max_prefix = auto_prefix, (max_prefix // 16) * 16
+        self._prefix_bytes, self.prefix_sets = b"", 0
+        if auto_prefix:
+            prefix_len = self.max_prefix
+        self.gen = Generator(arch, seed=seed, max_batch=max_batch, max_seq=prefix_len + prompt_len + max_new, device=device,
+                             tp_rank=tp_rank, tp_size=tp_size, nccl=nccl,
+                             prefill_chunk=max(32768, prefix_len))
         self.max_batch, self.prompt_len, self.max_new = max_batch, prompt_len, max_new
+        if prefix_len and not auto_prefix:
+            # constant instruction prefix (app.py:50-57 in the service; a system prompt in BASELINE config 5),
+            # byte-tokenised and padded/truncated to a whole number of KV pages, prefilled once
+            self.gen.set_prefix(np.asarray(tokenizer.encode_fixed(prefix or "", prefix_len), np.int32))
 
     def generate(self, prompts: Sequence[str], cancelled=None) -> List[str]:
-        toks = np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
+        if self.auto_prefix:
+            toks = self._with_learned_prefix(prompts)
+        else:
+            toks = np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
         ids, _ = self.gen.generate_ids(toks, self.max_new)
         return [tokenizer.decode(row) for row in ids]
+
+    def _with_learned_prefix(self, prompts: Sequence[str]) -> np.ndarray:
+        """Prefix cache for the service's own template: every prompt the chain renders starts with the
+        same instruction text (app.py:50-57).  The longest common byte prefix of the batch (and of the
+        prefix already cached) is rounded down to whole KV pages, prefilled once, and only the remainder
+        of each prompt is prefilled per request."""
+        import os.path
+        raw = [p.encode("utf-8") for p in prompts]
+        common = os.path.commonprefix(raw + ([self._prefix_bytes] if self._prefix_bytes else []))
+        page = 16
+        n_tok = min(((1 + len(common)) // page) * page, self.max_prefix)      # BOS + bytes, whole pages
+        want = common[:max(0, n_tok - 1)]
+        if n_tok and want != self._prefix_bytes:
+            self.gen.set_prefix(np.asarray([tokenizer.BOS] + list(want), np.int32))
+            self._prefix_bytes, self.prefix_sets = want, self.prefix_sets + 1
+        elif not n_tok and self._prefix_bytes:
+            self.gen.set_prefix(np.zeros(0, np.int32))
+            self._prefix_bytes = b""
+        if not n_tok:
+            return np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
+        return np.asarray([tokenizer.encode_suffix(r[len(want):], self.prompt_len) for r in raw], np.int32)
 
     def close(self):
         self.gen.close()
 
 
 def default_engine_factory(arch: str) -> Engine:
-    return B200Engine(arch)
+    # the service's prompts share the template's instruction text: cache its KV, prefill only the rest
+    return B200Engine(arch, prompt_len=128, auto_prefix=True)

@@ -34,3 +34,12 @@ def encode_fixed(text: str, length: int, pad: int = 32) -> List[int]:
     if len(ids) >= length - 1:
         return [BOS] + ids[len(ids) - (length - 1):]
     return [BOS] + [pad] * (length - 1 - len(ids)) + ids
+
+
+def encode_suffix(data: bytes, length: int, pad: int = 32) -> List[int]:
+    """Bytes that continue a cached prefix, as exactly ``length`` tokens: left-padded with spaces or,
+    if too long, truncated keeping the tail (no BOS: the prefix carries it)."""
+    ids = list(data)
+    if len(ids) >= length:
+        return ids[len(ids) - length:]
+    return [pad] * (length - len(ids)) + ids

@@ -315,10 +315,12 @@ PROMPT_SUFFIX = "\nKubectl Command:\n"
 
 def gen_prompts(n, seed):
     from kubectl_b200 import synth
-    return [PROMPT_PREFIX + q + PROMPT_SUFFIX for q in synth.queries(n, seed=seed)]
+    # every request is distinct (a request id is appended) so that the front end's single-flight
+    # coalescing of identical prompts cannot shrink the work that is being timed
+    return [PROMPT_PREFIX + f"{q} (request {i})" + PROMPT_SUFFIX for i, q in enumerate(synth.queries(n, seed=seed))]
 
 
-def cpu_generation_rate(arch, prompts, prompt_len, new_tokens, seed):
+def cpu_generation_rate(arch, prompts, prompt_len, new_tokens, seed, prefix_tokens=None):
     """The repo pipeline on host cores: fp32 PyTorch CPU model of the same architecture
     and weights in the llm slot, then parser + validator (Python port of app.py:95-104)."""
     import torch
@@ -329,6 +331,8 @@ def cpu_generation_rate(arch, prompts, prompt_len, new_tokens, seed):
     w = weights.make_weights(cfg, seed)
     ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos))
     toks = torch.tensor([tokenizer.encode_fixed(p, prompt_len) for p in prompts], dtype=torch.int64)
+    if prefix_tokens is not None:      # same token stream the GPU sees: cached prefix, then the request's own tokens
+        toks = torch.cat([torch.tensor(prefix_tokens, dtype=torch.int64)[None, :].expand(len(prompts), -1), toks], dim=1)
     t0 = time.perf_counter()
     ids, _ = ref.generate(toks, new_tokens)
     texts = [tokenizer.decode(r.tolist()) for r in ids]
@@ -377,11 +381,24 @@ def run_generate(args):
     cfg = model_config.get_config(args.arch)
     total = args.requests
     from kubectl_b200 import dist_utils
-    r0, r1 = dist_utils.shard_range(total, rank, world)          # strong scaling: the box serves `total` requests
+    tp = max(1, args.tp)
+    assert world % tp == 0, "--tp must divide the number of ranks"
+    replicas, replica, tp_rank = world // tp, rank // tp, rank % tp
+    r0, r1 = dist_utils.shard_range(total, replica, replicas)    # strong scaling: the box serves `total` requests
     mine = max(1, r1 - r0)
-    S, NEW = args.prompt_len, args.new_tokens
-    prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
-    eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank)
+    S, NEW, PFX = args.prompt_len, args.new_tokens, args.prefix_len
+    nccl = None
+    if tp > 1:
+        import torch.distributed as dist
+        groups = [dist.new_group(ranks=list(range(r * tp, (r + 1) * tp))) for r in range(replicas)]
+        nccl = engine.NcclComm(tp_rank, tp, local_rank, group=groups[replica])
+    if PFX:   # config 5: the instruction prefix is a shared, prefix-cached system prompt; prompts are the short suffixes
+        from kubectl_b200 import synth
+        prompts = [f"{q} (request {i})" + PROMPT_SUFFIX for i, q in enumerate(synth.queries(total, seed=1))][r0:r0 + mine]
+    else:
+        prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
+    eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank,
+                            tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX)
     model = B200ChatModel(temperature=0, api_key=None, model=args.arch, request_timeout=600, engine=eng, max_wait_ms=50)
     parser = strings.KubectlOutputParser()
     toks = np.asarray([tokenizer.encode_fixed(p, S) for p in prompts], np.int32)
@@ -413,17 +430,22 @@ def run_generate(args):
         dev_ms = e0.elapsed_time(e1)
         # ---- end-to-end leg: strings in, validated commands out, through the drop-in's public API ----
         e2e_steps = max(2, min(args.steps, 3))
-        outs = model.batch(prompts)
+        def api_pass():
+            if tp > 1:      # TP ranks must form identical batches: drive the engine below the batching front end
+                texts = eng.generate(prompts)
+            else:
+                texts = [o.content for o in model.batch(prompts)]        # tokenise -> H2D -> generate -> D2H -> text
+            return texts, parser.parse_batch(texts)                      # fence strip + validator on the GPU (k9)
+        outs, cmds = api_pass()
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
-            outs = model.batch(prompts)                                  # tokenise -> H2D -> generate -> D2H -> text
-            cmds = parser.parse_batch([o.content for o in outs])         # fence strip + validator on the GPU (k9)
+            outs, cmds = api_pass()
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
         # ---- the dominant kernel alone: prefill GEMM at the gate/up shape ----
         gM = min(mine * S, 32768)
-        gemm_ms, gemm_tflops = time_gemm_live(gM, 2 * cfg.inter, cfg.hidden, 20)
+        gemm_ms, gemm_tflops = time_gemm_live(gM, 2 * cfg.inter // tp, cfg.hidden, 20)
     clocks = sampler.summary()
     prefill_ms = float(np.mean([s[0] for s in stats]))
     decode_ms = float(np.mean([s[1] for s in stats]))
@@ -440,20 +462,21 @@ def run_generate(args):
     pk = peaks()
     n_safe = sum(c is not None for c in cmds)
     step_ms = decode_ms / max(1, dsteps)
-    kv_avg = mine * (S + NEW / 2.0) * cfg.kv_bytes_per_token()
-    decode_gbs = (cfg.decode_weight_bytes() + kv_avg) / (step_ms * 1e-3) / 1e9
-    prefill_flops = 2.0 * cfg.matmul_params() * mine * S
+    kv_avg = mine * (PFX + S + NEW / 2.0) * cfg.kv_bytes_per_token() / tp
+    decode_gbs = (cfg.decode_weight_bytes() / tp + kv_avg) / (step_ms * 1e-3) / 1e9          # per rank
+    prefill_flops = 2.0 * cfg.matmul_params() * mine * S / tp
     # CPU baseline: same pipeline with the fp32 CPU model, bounded sample, checked against the GPU ids
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     sample = max(1, min(mine, args.cpu_requests))
-    cpu_rate, cpu_ids, _ = cpu_generation_rate(args.arch, prompts[:sample], S, NEW, args.seed)
+    pfx_toks = tokenizer.encode_fixed(PROMPT_PREFIX * 8, PFX) if PFX else None
+    cpu_rate, cpu_ids, _ = cpu_generation_rate(args.arch, prompts[:sample], S, NEW, args.seed, pfx_toks)
     first_diff = [int(np.argmax(np.append(cpu_ids[i] != ids[i], True))) for i in range(sample)]
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "pair_gemm_traffic.json")
-    if os.path.exists(tp):
-        tj = json.load(open(tp))
-        if tj.get("shape") == [gM, 2 * cfg.inter, cfg.hidden]:
+    tpath = os.path.join(ROOT, "profiles", "pair_gemm_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("shape") == [gM, 2 * cfg.inter // tp, cfg.hidden]:
             traffic = tj["dram_bytes_per_launch"]
     line = {
         "metric": "generated kubectl commands/sec (box)", "value": total * args.steps / (dev_ms / 1e3),
@@ -464,23 +487,26 @@ def run_generate(args):
                                f"{total} concurrent requests split over {world} replica(s), {S}-token prompt, "
                                f"{NEW} greedy tokens, byte-level tokenizer",
                    "requests": total, "requests_per_gpu": mine, "prompt_len": S, "new_tokens": NEW,
-                   "parallelism": f"dp{world} replicas, no collective on the request path",
+                   "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (NCCL all-reduce over NVLink)" if tp > 1 else "") +
+                                   ", no collective between replicas"),
+                   "prefix_cached_tokens": PFX,
                    "l2": "weights + KV + activations per step exceed the 126 MB L2 (%.2f GB weights)" % (cfg.decode_weight_bytes() / 1e9),
-                   "validator_verdicts": {"safe": n_safe, "rejected": len(cmds) - n_safe}},
+                   "validator_verdicts": {"safe": n_safe, "rejected": len(cmds) - n_safe},
+                   "coalesced_duplicates": int(model.frontend.coalesced)},
         "ttft_p50_ms": prefill_ms, "decode_ms_per_step": step_ms, "decode_hbm_gbs": decode_gbs,
         "decode_hbm_frac": decode_gbs / pk["hbm_gbs"], "prefill_tflops": prefill_flops / (prefill_ms * 1e-3) / 1e12,
         "prefill_tensor_frac": prefill_flops / (prefill_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
         "roofline": {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                      "frac": gemm_tflops / pk["bf16_tflops"], "traffic": traffic, "peak_source": pk["source"] + " (burst: kernel timed alone)",
                      "kernel": "kx_gemm_bf16_kernel (prefill, SwiGLU epilogue)", "kernel_ms": gemm_ms,
-                     "shape": [gM, 2 * cfg.inter, cfg.hidden],
-                     "algorithmic_flops_per_launch": 2.0 * gM * 2 * cfg.inter * cfg.hidden},
+                     "shape": [gM, 2 * cfg.inter // tp, cfg.hidden],
+                     "algorithmic_flops_per_launch": 2.0 * gM * 2 * cfg.inter // tp * cfg.hidden},
         "cpu_baseline": {"value": cpu_rate, "unit": "commands/s", "cores": cores, "kind": "port",
                          "sample": f"{sample} of the same requests: fp32 PyTorch CPU model of {args.arch} (same weights) "
                                    f"+ Python port of parser/validator, torch threads = {cores}",
                          "first_differing_token_vs_gpu": first_diff},
-        "e2e": {"value": world * mine * e2e_steps / e2e_s, "unit": "commands/s",
-                "h2d_bytes_per_step": int(toks.nbytes + sum(len(o.content.encode()) for o in outs) + 8 * (len(outs) + 1)),
+        "e2e": {"value": total * e2e_steps / e2e_s, "unit": "commands/s",
+                "h2d_bytes_per_step": int(toks.nbytes + sum(len(o.encode()) for o in outs) + 8 * (len(outs) + 1)),
                 "d2h_bytes_per_step": int(mine * NEW * 4 + 5 * len(outs)),
                 "api": "B200ChatModel.batch(prompts) -> KubectlOutputParser.parse_batch (strings in, validated commands out)",
                 "steps": e2e_steps},
@@ -533,6 +559,8 @@ def main():
     ap.add_argument("--new-tokens", type=int, default=32)
     ap.add_argument("--seed", type=int, default=4)
     ap.add_argument("--cpu-requests", type=int, default=4)
+    ap.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per replica (config 5: 2)")
+    ap.add_argument("--prefix-len", type=int, default=0, help="tokens of shared, prefix-cached system prompt (config 5: 1024)")
     ap.add_argument("--strings", type=int, default=10_000_000)
     ap.add_argument("--cpu-sample", type=int, default=0)
     args = ap.parse_args()

@@ -135,3 +135,14 @@ def test_zero_diff_install_into_unmodified_app_py():
         assert r.status_code == 500 and "out of KV pages" in r.json()["detail"]
         assert c.post("/kubectl-command", json={"query": "ab"}).status_code == 422    # pydantic min_length
     made[0].close()
+
+
+def test_identical_prompts_in_flight_are_generated_once():
+    m, eng = make(lambda p: p.upper(), max_wait_ms=50)
+
+    async def go():
+        return await asyncio.gather(*(m.ainvoke(f"q{i % 3}") for i in range(30)))
+    outs = asyncio.run(go())
+    assert [o.content for o in outs] == [f"Q{i % 3}" for i in range(30)]
+    assert sum(eng.batches) < 30 and m.frontend.coalesced == 30 - sum(eng.batches)
+    m.close()

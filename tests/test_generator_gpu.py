@@ -4,6 +4,8 @@
   2. logits within 1e-2 (relative to the largest logit) of the pure-fp32 CPU oracle
      evaluated on the same token history,
 through the C ABI (kx_engine_create / kx_engine_generate)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -125,3 +127,24 @@ def test_prefix_cached_kv_equals_full_prefill(arch):
     ids2, _ = gen.generate_ids(full.numpy().astype(np.int32)[:, :P + S], n_new)
     assert np.array_equal(ids2, want_ids.numpy())
     gen.close()
+
+
+def test_service_engine_learns_the_template_prefix():
+    """B200Engine(auto_prefix=True): prompts that share a long instruction prefix are generated with
+    that prefix prefilled once; the result must equal generation from the explicitly tokenised prompts."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine, tokenizer
+    head = "You are a Kubernetes CLI specialist. " * 6 + "User Request: "
+    prompts = [head + q + "\nKubectl Command:\n" for q in ("list pods", "show all nodes in namespace ns3", "get svc")]
+    eng = engine.B200Engine("tiny-qwen2", max_batch=4, prompt_len=48, max_new=6, auto_prefix=True, max_prefix=256)
+    out1 = eng.generate(prompts)
+    out2 = eng.generate(prompts[::-1])
+    assert out2 == out1[::-1] and eng.prefix_sets == 1                   # prefix prefilled once, reused
+    want = len(os.path.commonprefix([p.encode() for p in prompts]))
+    n_tok = ((1 + want) // 16) * 16
+    plain = engine.Generator("tiny-qwen2", weights=eng.gen.logical, max_batch=4, max_seq=n_tok + 48 + 6)
+    toks = np.asarray([[tokenizer.BOS] + list(p.encode()[:n_tok - 1]) + tokenizer.encode_suffix(p.encode()[n_tok - 1:], 48)
+                       for p in prompts], np.int32)
+    ids, _ = plain.generate_ids(toks, 6)
+    assert [tokenizer.decode(r) for r in ids] == out1
+    eng.close(); plain.close()
