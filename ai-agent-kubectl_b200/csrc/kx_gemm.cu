@@ -461,6 +461,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+    asm volatile("griddepcontrol.launch_dependents;");        // our own dependents may begin their prologue
     const int S = gridDim.z, z = blockIdx.z;                  // cluster = the z column; rank == z
     const int total_kb = (p.k + BK - 1) / BK;
     const int kb0 = z * p.kb_per_split;
@@ -482,7 +483,18 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     if (warp == 0) {
         if (lane == 0) {
             const uint64_t pol_w = policy_evict_first(), pol_x = policy_evict_last();
-            for (int i = 0; i < nkb; ++i) {
+            // Programmatic dependent launch: this grid may start while its predecessor (which produces
+            // the activations) is still running.  Weights do not depend on it, so the first ring of
+            // weight tiles is already in flight before griddepcontrol.wait; activations follow after.
+            const int pre = nkb < C::STAGES ? nkb : C::STAGES;
+            for (int i = 0; i < pre; ++i) {
+                mbar_expect_tx(full + i, C::STAGE_BYTES);
+                tma_load_2d_hint(smem + i * C::STAGE_BYTES, &tmA, full + i, (kb0 + i) * BK, m0, pol_w);
+            }
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            for (int i = 0; i < pre; ++i)
+                tma_load_2d_hint(smem + i * C::STAGE_BYTES + C::A_BYTES, &tmB, full + i, (kb0 + i) * BK, n0, pol_x);
+            for (int i = pre; i < nkb; ++i) {
                 const int s = i % C::STAGES;
                 mbar_wait(empty + s, ((i / C::STAGES) & 1) ^ 1);
                 mbar_expect_tx(full + s, C::STAGE_BYTES);
@@ -508,6 +520,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         }
     } else {
         const int q = warp & 3, r = q * 32 + lane;
+        asm volatile("griddepcontrol.wait;" ::: "memory");     // outputs (and the residual read) follow the predecessor
         mbar_wait(tmem_full, 0);                               // all MMAs retired: the stage ring is free
         tc_fence_after();
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
@@ -563,11 +576,13 @@ int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = Cfg<BN>::SMEM_BYTES;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = grid.z;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // may overlap the tail of its predecessor
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     count_launch();
     return KX_OK;

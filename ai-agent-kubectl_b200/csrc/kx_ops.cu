@@ -77,6 +77,46 @@ __global__ void rmsnorm_kernel(const float *__restrict__ x, const __nv_bfloat16 
     }
 }
 
+// Same, one CTA of 128 threads per row: for the few rows of a decode step one warp per row leaves
+// the GPU idle and is latency bound; here the row is read once into registers.
+template <int PER>   // float4 chunks per thread: H = 512 * PER
+__global__ void __launch_bounds__(128)
+rmsnorm_row_kernel(const float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, __nv_bfloat16 *__restrict__ y,
+                   int H, float eps, const int *__restrict__ row_map) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    const int row = blockIdx.x, tid = threadIdx.x;
+    const float *xr = x + (size_t)(row_map ? row_map[row] : row) * H;
+    float4 v[PER];
+    float ss = 0.f;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+        const int i = (u * 128 + tid) * 4;
+        v[u] = i < H ? *reinterpret_cast<const float4 *>(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+    }
+    ss = warp_sum(ss);
+    __shared__ float part[4];
+    if ((tid & 31) == 0) part[tid >> 5] = ss;
+    __syncthreads();
+    const float r = 1.0f / sqrtf((part[0] + part[1] + part[2] + part[3]) / (float)H + eps);
+    __nv_bfloat16 *yr = y + (size_t)row * H;
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+        const int i = (u * 128 + tid) * 4;
+        if (i >= H) continue;
+        const uint2 gq = *reinterpret_cast<const uint2 *>(g + i);
+        const __nv_bfloat162 *gh = reinterpret_cast<const __nv_bfloat162 *>(&gq);
+        __nv_bfloat162 o0 = __floats2bfloat162_rn(__fmul_rn(__fmul_rn(v[u].x, r), __low2float(gh[0])),
+                                                  __fmul_rn(__fmul_rn(v[u].y, r), __high2float(gh[0])));
+        __nv_bfloat162 o1 = __floats2bfloat162_rn(__fmul_rn(__fmul_rn(v[u].z, r), __low2float(gh[1])),
+                                                  __fmul_rn(__fmul_rn(v[u].w, r), __high2float(gh[1])));
+        uint2 out;
+        out.x = *reinterpret_cast<uint32_t *>(&o0);
+        out.y = *reinterpret_cast<uint32_t *>(&o1);
+        *reinterpret_cast<uint2 *>(yr + i) = out;
+    }
+}
+
 // ---- RoPE (rotate-half pairs i, i + hd/2) on q and k, then append k, v to the cache ----
 __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, const int *__restrict__ pos,
                                    const int *__restrict__ seq, const float2 *__restrict__ rope,
@@ -300,6 +340,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
                    __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
                    const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2) {
     extern __shared__ __align__(128) uint8_t smem_dec[];
+    asm volatile("griddepcontrol.launch_dependents;");   // let a dependent GEMM start prefetching its weights
     constexpr int CH = HD / 8;                        // 16 B chunks per row
     constexpr int HALF = HD / 2;
     constexpr int ROUND = 256;                        // keys staged per round (4 warps x 64)
@@ -603,6 +644,18 @@ int op_embed(const int *tokens, const void *table, float *x, int M, int H, cudaS
 }
 
 int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st) {
+    if (M <= 2048 && H <= 8192) {
+        const int per = (H + 511) / 512;
+        const __nv_bfloat16 *gg = (const __nv_bfloat16 *)g;
+        __nv_bfloat16 *yy = (__nv_bfloat16 *)y;
+        if (per <= 2) rmsnorm_row_kernel<2><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
+        else if (per <= 4) rmsnorm_row_kernel<4><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
+        else if (per <= 8) rmsnorm_row_kernel<8><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
+        else rmsnorm_row_kernel<16><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
+        count_launch();
+        KX_CUDA(cudaGetLastError());
+        return KX_OK;
+    }
     rmsnorm_kernel<<<(M + 7) / 8, 256, 0, st>>>(x, (const __nv_bfloat16 *)g, (__nv_bfloat16 *)y, M, H, eps, row_map);
     count_launch();
     KX_CUDA(cudaGetLastError());
