@@ -19,6 +19,19 @@ namespace {
 
 constexpr int kPage = KX_KV_PAGE;
 
+// Launch with programmatic stream serialization: the grid may start while its predecessor drains;
+// the kernel itself calls griddepcontrol.wait before it touches the predecessor's output.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -84,6 +97,7 @@ __global__ void __launch_bounds__(128)
 rmsnorm_row_kernel(const float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, __nv_bfloat16 *__restrict__ y,
                    int H, float eps, const int *__restrict__ row_map) {
     asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int row = blockIdx.x, tid = threadIdx.x;
     const float *xr = x + (size_t)(row_map ? row_map[row] : row) * H;
     float4 v[PER];
@@ -341,6 +355,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
                    const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2) {
     extern __shared__ __align__(128) uint8_t smem_dec[];
     asm volatile("griddepcontrol.launch_dependents;");   // let a dependent GEMM start prefetching its weights
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic serialization: qkv comes from the predecessor
     constexpr int CH = HD / 8;                        // 16 B chunks per row
     constexpr int HALF = HD / 2;
     constexpr int ROUND = 256;                        // keys staged per round (4 warps x 64)
@@ -621,7 +636,7 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
             granted = smem;                                                                                 \
         }                                                                                                   \
-        k<<<grid, kDecThreads, smem, st>>>(qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale); \
+        KX_CUDA(launch_pdl(k, grid, dim3(kDecThreads), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale)); \
         break;                                                                                              \
     }
     switch (G) {
@@ -648,12 +663,11 @@ int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, 
         const int per = (H + 511) / 512;
         const __nv_bfloat16 *gg = (const __nv_bfloat16 *)g;
         __nv_bfloat16 *yy = (__nv_bfloat16 *)y;
-        if (per <= 2) rmsnorm_row_kernel<2><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
-        else if (per <= 4) rmsnorm_row_kernel<4><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
-        else if (per <= 8) rmsnorm_row_kernel<8><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
-        else rmsnorm_row_kernel<16><<<M, 128, 0, st>>>(x, gg, yy, H, eps, row_map);
+        if (per <= 2) KX_CUDA(launch_pdl(rmsnorm_row_kernel<2>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
+        else if (per <= 4) KX_CUDA(launch_pdl(rmsnorm_row_kernel<4>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
+        else if (per <= 8) KX_CUDA(launch_pdl(rmsnorm_row_kernel<8>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
+        else KX_CUDA(launch_pdl(rmsnorm_row_kernel<16>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
         count_launch();
-        KX_CUDA(cudaGetLastError());
         return KX_OK;
     }
     rmsnorm_kernel<<<(M + 7) / 8, 256, 0, st>>>(x, (const __nv_bfloat16 *)g, (__nv_bfloat16 *)y, M, H, eps, row_map);
