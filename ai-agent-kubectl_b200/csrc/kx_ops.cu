@@ -171,6 +171,13 @@ __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, 
 // grid (ceil(S/64), n_q, B), 128 threads; warp w owns query rows 16w .. 16w+15 of the
 // 64-row block.  QK^T and PV run on tensor cores (mma.sync m16n8k16 bf16, fp32 acc) with
 // the online softmax in fp32 registers.
+__device__ __forceinline__ void cp_async16_zfill(uint32_t smem_dst, const void *src, bool valid) {
+    const int n = valid ? 16 : 0;                     // src-size 0: the 16 destination bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
@@ -202,52 +209,55 @@ attn_prefill_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bflo
     extern __shared__ __align__(128) uint8_t smem_attn[];
     constexpr int CH = HD / 8;                       // 16 B chunks per row
     constexpr int TILE = 64 * HD * 2;
-    uint8_t *Qs = smem_attn, *Ks = Qs + TILE, *Vs = Ks + TILE;
-    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ks_u = qs_u + TILE, vs_u = ks_u + TILE;
+    // Q tile, then two (K, V) buffers: tile kb+1 is fetched with cp.async while tile kb is consumed
+    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(smem_attn);
     const int qb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
     const int kvh = head / (n_q / n_kv);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int *bt = block_table + (size_t)b * max_pages;
+    const int T = pos0 + S;
+    const int last_key = min(T, pos0 + (qb + 1) * 64);          // keys needed by this query block
+    const int nkb = (last_key + 63) / 64;
 
-    // Q tile -> smem (zero rows past S)
-    for (int i = tid; i < 64 * CH; i += 128) {
+    auto fetch_kv = [&](int kb) {
+        const uint32_t kdst = qs_u + TILE + (uint32_t)(kb & 1) * 2 * TILE, vdst = kdst + TILE;
+        for (int i = tid; i < 64 * CH; i += 128) {
+            const int r = i / CH, c = i - r * CH;
+            const int t = kb * 64 + r;
+            const bool ok = t < T;
+            const int tt = ok ? t : 0;
+            const __nv_bfloat16 *kp = pages + (((size_t)bt[tt / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(tt % kPage) * HD + c * 8;
+            cp_async16_zfill(kdst + swz<HD>(r, c), kp, ok);
+            cp_async16_zfill(vdst + swz<HD>(r, c), kp + (size_t)n_kv * kPage * HD, ok);
+        }
+    };
+    for (int i = tid; i < 64 * CH; i += 128) {                   // Q tile (rows past S are zero-filled)
         const int r = i / CH, c = i - r * CH;
         const int t = qb * 64 + r;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (t < S) v = *reinterpret_cast<const uint4 *>(qkv + (size_t)(b * S + t) * qkv_ld + (size_t)head * HD + c * 8);
-        *reinterpret_cast<uint4 *>(Qs + swz<HD>(r, c)) = v;
+        const bool ok = t < S;
+        cp_async16_zfill(qs_u + swz<HD>(r, c), qkv + (size_t)(b * S + (ok ? t : 0)) * qkv_ld + (size_t)head * HD + c * 8, ok);
     }
-    __syncthreads();
-    uint32_t qf[HD / 16][4];
-#pragma unroll
-    for (int ks = 0; ks < HD / 16; ++ks)
-        ldsm_x4(qf[ks], qs_u + swz<HD>(warp * 16 + (lane & 15), 2 * ks + (lane >> 4)));
+    fetch_kv(0);
+    cp_async_commit();
 
+    uint32_t qf[HD / 16][4];
     float o[HD / 8][4];
 #pragma unroll
     for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
     float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
     const int g = lane >> 2, tq = lane & 3;
     const int qpos0 = pos0 + qb * 64 + warp * 16 + g;           // absolute position of row g (row g+8: +8)
-    const int T = pos0 + S;
-    const int last_key = min(T, pos0 + (qb + 1) * 64);          // keys needed by this query block
-    const int nkb = (last_key + 63) / 64;
 
     for (int kb = 0; kb < nkb; ++kb) {
-        __syncthreads();                                         // previous tile fully consumed
-        for (int i = tid; i < 64 * CH; i += 128) {
-            const int r = i / CH, c = i - r * CH;
-            const int t = kb * 64 + r;
-            uint4 kq = make_uint4(0, 0, 0, 0), vq = kq;
-            if (t < T) {
-                const __nv_bfloat16 *kp = pages + (((size_t)bt[t / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(t % kPage) * HD + c * 8;
-                kq = *reinterpret_cast<const uint4 *>(kp);
-                vq = *reinterpret_cast<const uint4 *>(kp + (size_t)n_kv * kPage * HD);
-            }
-            *reinterpret_cast<uint4 *>(Ks + swz<HD>(r, c)) = kq;
-            *reinterpret_cast<uint4 *>(Vs + swz<HD>(r, c)) = vq;
+        if (kb + 1 < nkb) { fetch_kv(kb + 1); cp_async_commit(); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncthreads();                                         // tile kb (and Q) visible to every warp
+        if (kb == 0) {
+#pragma unroll
+            for (int ks = 0; ks < HD / 16; ++ks)
+                ldsm_x4(qf[ks], qs_u + swz<HD>(warp * 16 + (lane & 15), 2 * ks + (lane >> 4)));
         }
-        __syncthreads();
+        const uint32_t ks_u = qs_u + TILE + (uint32_t)(kb & 1) * 2 * TILE, vs_u = ks_u + TILE;
 
         // S = Q K^T for 64 keys: 8 n-tiles of 8 keys
         float s[8][4];
@@ -312,6 +322,7 @@ attn_prefill_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bflo
                 mma_bf16(o[2 * dp + 1], pf[kk], vf[2], vf[3]);
             }
         }
+        __syncthreads();                                         // buffer kb&1 may be refilled by the next iteration's prefetch
     }
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -716,13 +727,13 @@ int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const vo
     const float scale_log2 = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
     dim3 grid((S + 63) / 64, n_q, B);
     if (hd == 64) {
-        attn_prefill_kernel<64><<<grid, 128, 3 * 64 * 64 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
+        attn_prefill_kernel<64><<<grid, 128, 5 * 64 * 64 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else if (hd == 128) {
         auto k = attn_prefill_kernel<128>;
         static bool granted = false;
-        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 64 * 128 * 2)); granted = true; }
-        k<<<grid, 128, 3 * 64 * 128 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
+        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); granted = true; }
+        k<<<grid, 128, 5 * 64 * 128 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else {
         set_error("attention: head_dim %d not supported (64 or 128)", hd);
