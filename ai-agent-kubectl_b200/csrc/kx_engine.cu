@@ -93,12 +93,18 @@ struct GemmCall {
     void *out; int ldo; const float *bias;
     const CUtensorMap *b_half = nullptr;           // token-major pair kernel: weight map with a half-tile box
     int pair_bn = 0;                               // ... and its tile width (128 or 256)
+    const GemmParams *extra = nullptr;             // EPI_QKV_ROPE: the rope / cache fields
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     GemmParams p{};
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
     p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits;
+    if (c.extra) {
+        p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
+        p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
+        p.n_q = c.extra->n_q; p.n_kv = c.extra->n_kv; p.hd = c.extra->hd;
+    }
     if (!c.swap && c.b_half) return gemm_launch_pair(*c.a, *c.b_half, p, c.pair_bn, st);
     KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
     return gemm_launch(*c.a, *c.b, p, c.bn, e->scratch, st);
@@ -115,16 +121,19 @@ struct Linear {
     int features, k;
 };
 
-int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st) {
-    if (M >= 256) {
-        const int m_pairs = (M + 255) / 256;
-        const int t256 = m_pairs * ((l.features + 255) / 256), t128 = m_pairs * ((l.features + 127) / 128);
-        const bool wide_ok = l.features % 256 == 0 || l.features >= 2048;
-        if (wide_ok && t256 >= 64)
-            return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + 1, 256}, st);
-        if (t128 >= 24)
-            return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + 0, 128}, st);
-    }
+// tile width the CTA-pair kernel would use for this layer at M rows (0: another kernel is chosen)
+int linear_pair_bn(const Linear &l, int M) {
+    if (M < 256) return 0;
+    const int m_pairs = (M + 255) / 256;
+    const int t256 = m_pairs * ((l.features + 255) / 256), t128 = m_pairs * ((l.features + 127) / 128);
+    if ((l.features % 256 == 0 || l.features >= 2048) && t256 >= 64) return 256;
+    return t128 >= 24 ? 128 : 0;
+}
+
+int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st,
+           const GemmParams *extra = nullptr) {
+    if (const int pbn = linear_pair_bn(l, M))
+        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + (pbn == 256), pbn, extra}, st);
     if (M > 512)   // tall but very narrow: the single-CTA token-major kernel (128 x 128 tiles)
         return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias}, st);
     const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
@@ -154,13 +163,24 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     const Linear wgu{&L.wgu, L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
     const Linear wd{&L.wd, L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
     KX_TRY(op_rmsnorm(e->resid, L.w.ln1, e->xn, M, d.hidden, d.eps, nullptr, st));
-    KX_TRY(linear(e, qkv, M, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, st));
+    const int head_w = d.head_dim;
+    const int qkv_pbn = linear_pair_bn(qkv, M);
+    const bool fused_rope = !decode && qkv_pbn && qkv_pbn % head_w == 0;   // QKV epilogue also rotates and appends
+    if (fused_rope) {
+        GemmParams x{};
+        x.pos = e->pos; x.seq = e->seq; x.rope = e->rope; x.kv_pages = L.kv_pages; x.block_table = e->block_table;
+        x.max_pages = e->max_pages; x.n_q = d.n_q; x.n_kv = d.n_kv; x.hd = d.head_dim;
+        KX_TRY(linear(e, qkv, M, EPI_QKV_ROPE, e->qkv, e->qkv_dim, L.w.bqkv, st, &x));
+    } else {
+        KX_TRY(linear(e, qkv, M, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, st));
+    }
     if (decode) {
         KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos,
                               e->rope, M, max_T, d.n_q, d.n_kv, d.head_dim, st));
     } else {
-        KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
-                              d.n_q, d.n_kv, d.head_dim, st));
+        if (!fused_rope)
+            KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
+                                  d.n_q, d.n_kv, d.head_dim, st));
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, pos0, d.n_q, d.n_kv, d.head_dim, st));
     }

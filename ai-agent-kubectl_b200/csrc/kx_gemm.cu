@@ -27,6 +27,7 @@
 #include "kx_common.cuh"
 #include "kx_sm100.cuh"
 #include "kx_gemm.cuh"
+#include "kx_ops.cuh"
 
 namespace kx {
 
@@ -269,6 +270,51 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // cluster per SM pair walks the tile list) and the accumulator is double buffered in
 // TMEM (2 x BN columns), so the epilogue of tile i overlaps the MMAs of tile i+1.
 // ---------------------------------------------------------------------------------
+// QKV epilogue with RoPE + KV append for one (row, head, 32-wide half-pair): x1 = columns d0..d0+31 of the
+// head, x2 = columns d0+hd/2.. of the same head (rotate-half partners).  Values are rounded to bf16 after the
+// bias (what the unfused path stores), rotated in fp32 without FMA contraction, rounded again.
+__device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[32], float (&x2)[32], int row, int head, int d0) {
+    const int half = p.hd >> 1;
+    const int pos = __ldg(p.pos + row);
+    const int fcol = head * p.hd + d0;
+    __nv_bfloat16 *dst1, *dst2;
+    const bool is_v = head >= p.n_q + p.n_kv;
+    if (head < p.n_q) {
+        dst1 = reinterpret_cast<__nv_bfloat16 *>(p.out) + (size_t)row * p.ldo + fcol;
+    } else {
+        const int kvh = head - p.n_q - (is_v ? p.n_kv : 0);
+        const int page = __ldg(p.block_table + (size_t)__ldg(p.seq + row) * p.max_pages + pos / KX_KV_PAGE);
+        dst1 = reinterpret_cast<__nv_bfloat16 *>(p.kv_pages) +
+               (((size_t)page * 2 + (is_v ? 1 : 0)) * p.n_kv + kvh) * KX_KV_PAGE * p.hd + (size_t)(pos % KX_KV_PAGE) * p.hd + d0;
+    }
+    dst2 = dst1 + half;
+    const float2 *cs = reinterpret_cast<const float2 *>(p.rope) + (size_t)pos * half + d0;
+    uint32_t o1[16], o2[16];
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+        float a[2], b[2];
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            const float bias1 = p.bias ? __ldg(p.bias + fcol + j + t) : 0.f, bias2 = p.bias ? __ldg(p.bias + fcol + half + j + t) : 0.f;
+            const float v1 = __bfloat162float(__float2bfloat16(x1[j + t] + bias1));
+            const float v2 = __bfloat162float(__float2bfloat16(x2[j + t] + bias2));
+            if (is_v) { a[t] = v1; b[t] = v2; }
+            else {
+                const float2 c = __ldg(cs + j + t);
+                a[t] = __fsub_rn(__fmul_rn(v1, c.x), __fmul_rn(v2, c.y));
+                b[t] = __fadd_rn(__fmul_rn(v2, c.x), __fmul_rn(v1, c.y));
+            }
+        }
+        o1[j >> 1] = pack_bf16(a[0], a[1]);
+        o2[j >> 1] = pack_bf16(b[0], b[1]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        reinterpret_cast<uint4 *>(dst1)[j] = make_uint4(o1[4 * j], o1[4 * j + 1], o1[4 * j + 2], o1[4 * j + 3]);
+        reinterpret_cast<uint4 *>(dst2)[j] = make_uint4(o2[4 * j], o2[4 * j + 1], o2[4 * j + 2], o2[4 * j + 3]);
+    }
+}
+
 template <int BN> struct Cfg2 {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
@@ -363,17 +409,38 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
+            if (EPI == EPI_QKV_ROPE) {
+                // head by head: the rotate-half partners of a head live hd/2 columns apart in the same row
+                const int hd = p.hd, half = hd >> 1;
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                float v[32];
-                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
-                tmem_ld_wait();
-                if (c + 32 >= BN) {                                     // last read of this accumulator: hand it back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(tmem_empty + ab);
+                for (int h0 = 0; h0 < BN; h0 += hd) {
+#pragma unroll 1
+                    for (int d0 = 0; d0 < half; d0 += 32) {
+                        float x1[32], x2[32];
+                        tmem_ld_32x32(taddr + h0 + d0, reinterpret_cast<uint32_t(&)[32]>(x1));
+                        tmem_ld_32x32(taddr + h0 + half + d0, reinterpret_cast<uint32_t(&)[32]>(x2));
+                        tmem_ld_wait();
+                        if (h0 + hd >= BN && d0 + 32 >= half) {            // last read of this accumulator
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(tmem_empty + ab);
+                        }
+                        if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0);
+                    }
                 }
-                epilogue_chunk<EPI, false>(p, v, arow, n0 + c, false);
+            } else {
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    float v[32];
+                    tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                    tmem_ld_wait();
+                    if (c + 32 >= BN) {                                     // last read of this accumulator: hand it back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tmem_empty + ab);
+                    }
+                    epilogue_chunk<EPI, false>(p, v, arow, n0 + c, false);
+                }
             }
         }
     }
@@ -412,6 +479,7 @@ int launch_pair_epi(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmPar
         case EPI_RESID: return launch_pair<BN, EPI_RESID>(ta, tbh, p, st);
         case EPI_SWIGLU: return launch_pair<BN, EPI_SWIGLU>(ta, tbh, p, st);
         case EPI_F32: return launch_pair<BN, EPI_F32>(ta, tbh, p, st);
+        case EPI_QKV_ROPE: return launch_pair<BN, EPI_QKV_ROPE>(ta, tbh, p, st);
     }
     set_error("kx_gemm: unknown epilogue %d", p.epilogue);
     return KX_EINVAL;

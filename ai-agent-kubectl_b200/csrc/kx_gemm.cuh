@@ -6,7 +6,7 @@
 
 namespace kx {
 
-enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3 };
+enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3, EPI_QKV_ROPE = 4 };
 
 struct GemmParams {
     int a_rows, b_rows, k;   // D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T
@@ -19,6 +19,13 @@ struct GemmParams {
     int kb_per_split;        // filled by gemm_launch
     float *ws;               // split-K scratch, filled by gemm_launch
     uint32_t *tickets;
+    // EPI_QKV_ROPE (token-major pair kernel only): bias, bf16 rounding, RoPE on q and k, q -> out,
+    // k and v -> the paged KV cache; replaces the separate rope/append kernel in prefill
+    const int *pos, *seq;    // per token row: absolute position, sequence (block-table row)
+    const void *rope;        // float2 [max_pos][hd/2]
+    void *kv_pages;          // this layer's pages
+    const int *block_table;
+    int max_pages, n_q, n_kv, hd;
 };
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);

@@ -357,26 +357,29 @@ __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
-constexpr int kDecThreads = 128;
+// NW warps x 64 keys per round: 8 warps hold a whole <= 512-key context in one round (few CTAs, latency
+// matters); 4 warps / 256-key rounds keep three CTAs per SM resident (many CTAs, bandwidth matters)
 
-template <int HD, int G>
-__global__ void __launch_bounds__(kDecThreads)
+template <int HD, int G, int NW>
+__global__ void __launch_bounds__(NW * 32)
 attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
                    __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
-                   const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2) {
+                   const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
+                   int round_keys) {
     extern __shared__ __align__(128) uint8_t smem_dec[];
     asm volatile("griddepcontrol.launch_dependents;");   // let a dependent GEMM start prefetching its weights
     asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic serialization: qkv comes from the predecessor
     constexpr int CH = HD / 8;                        // 16 B chunks per row
     constexpr int HALF = HD / 2;
-    constexpr int ROUND = 256;                        // keys staged per round (4 warps x 64)
-    constexpr int QT = 16 * HD * 2, KT = ROUND * HD * 2;
+    const int ROUND = round_keys;                     // keys staged per round: a multiple of 64, at most 64 per warp
+    constexpr int QT = 16 * HD * 2;
+    const int KT = ROUND * HD * 2;
     uint8_t *Qs = smem_dec, *Ks = Qs + QT, *Vs = Ks + KT;
     __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Vs + KT), *vnew = knew + HD;
     const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ks_u = qs_u + QT, vs_u = ks_u + KT;
-    float *comb_m = reinterpret_cast<float *>(Ks);    // after the last round: [4][16] max, [4][16] sum, [4][G][HD] O
-    float *comb_l = comb_m + 64;
-    float *comb_o = comb_l + 64;
+    float *comb_m = reinterpret_cast<float *>(Ks);    // after the last round: [8][16] max, [8][16] sum, [8][G][HD] O
+    float *comb_l = comb_m + NW * 16;
+    float *comb_o = comb_l + NW * 16;
 
     const int kvh = blockIdx.x, b = blockIdx.y;
     const int p = pos[b], T = p + 1;                  // keys 0 .. p (p = the new token)
@@ -389,7 +392,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         const float2 *cs = rope + (size_t)p * HALF;
         __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
         __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
-        for (int i = tid; i < (G + 1) * HALF; i += kDecThreads) {
+        for (int i = tid; i < (G + 1) * HALF; i += (NW * 32)) {
             const int h = i / HALF, d = i - h * HALF;
             const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
             const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
@@ -404,8 +407,8 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
             }
         }
         const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
-        for (int i = tid; i < HD; i += kDecThreads) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
-        for (int i = tid; i < (16 - G) * CH; i += kDecThreads)          // padding rows of the Q tile
+        for (int i = tid; i < HD; i += (NW * 32)) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
+        for (int i = tid; i < (16 - G) * CH; i += (NW * 32))          // padding rows of the Q tile
             *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
@@ -422,7 +425,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
     for (int c0 = 0; c0 < T; c0 += ROUND) {
         const int n = min(T, c0 + ROUND) - c0;        // valid keys this round
         const int nfill = (n + 63) & ~63;             // whole 64-key blocks are read by ldmatrix
-        for (int i = tid; i < nfill * CH; i += kDecThreads) {
+        for (int i = tid; i < nfill * CH; i += (NW * 32)) {
             const int r = i / CH, c = i - r * CH;
             if (r < n) {
                 const int t = c0 + r;
@@ -506,7 +509,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         __syncthreads();                              // K/V of this round fully consumed
     }
 
-    // merge the four warps' (max, sum, O) -- only rows < G are real query heads
+    // merge the warps' (max, sum, O) -- only rows < G are real query heads
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
         lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
@@ -531,14 +534,14 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         }
     }
     __syncthreads();
-    for (int i = tid; i < G * HD; i += kDecThreads) {
+    for (int i = tid; i < G * HD; i += (NW * 32)) {
         const int h = i / HD, d = i - h * HD;
         float M = -INFINITY;
 #pragma unroll
-        for (int w = 0; w < 4; ++w) M = fmaxf(M, comb_m[w * 16 + h]);
+        for (int w = 0; w < NW; ++w) M = fmaxf(M, comb_m[w * 16 + h]);
         float num = 0.f, den = 0.f;
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
+        for (int w = 0; w < NW; ++w) {
             const float f = exp2f((comb_m[w * 16 + h] - M) * scale_log2);   // 0 for a warp that saw no keys
             num += f * comb_o[(w * G + h) * HD + d];
             den += f * comb_l[w * 16 + h];
@@ -638,16 +641,16 @@ __global__ void advance_kernel(int *pos, int n) {
 template <int HD>
 int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_bfloat16 *qkv, int qkv_ld,
                     __nv_bfloat16 *out, int out_ld, __nv_bfloat16 *pages, const int *bt, int max_pages,
-                    const int *pos, const float2 *rope, int n_q, int n_kv, float scale) {
+                    const int *pos, const float2 *rope, int n_q, int n_kv, float scale, int round_keys, int nw) {
 #define KX_DEC(GV)                                                                                          \
     case GV: {                                                                                              \
-        auto k = attn_decode_kernel<HD, GV>;                                                                \
-        static size_t granted = 48 * 1024;   /* raised outside any stream capture by the first, eager call */  \
-        if (smem > granted) {                                                                               \
+        auto k = nw == 8 ? attn_decode_kernel<HD, GV, 8> : attn_decode_kernel<HD, GV, 4>;                   \
+        static size_t granted[2] = {48 * 1024, 48 * 1024};   /* raised outside any capture by the first, eager call */ \
+        if (smem > granted[nw == 8]) {                                                                      \
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-            granted = smem;                                                                                 \
+            granted[nw == 8] = smem;                                                                        \
         }                                                                                                   \
-        KX_CUDA(launch_pdl(k, grid, dim3(kDecThreads), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale)); \
+        KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys)); \
         break;                                                                                              \
     }
     switch (G) {
@@ -702,16 +705,23 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     const int G = n_q / n_kv;
     (void)max_T;                                      // any context length: K/V are consumed 256 keys per round
     KX_REQUIRE(G <= 16, KX_EINVAL, "attention: GQA group of %d query heads per kv head exceeds 16", G);
-    const size_t smem = (size_t)16 * hd * 2 + (size_t)2 * 256 * hd * 2 + 4 * hd + 128;
+    // one round holds the whole context when it fits (<= 512 keys); shared memory is sized for it
+    const int nw = (int64_t)n_kv * B > 600 ? 4 : 8;
+    int round_keys = ((max_T + 63) / 64) * 64;
+    if (round_keys > 64 * nw) round_keys = 64 * nw;
+    const size_t comb = sizeof(float) * (2 * 8 * 16 + (size_t)8 * G * hd);       // merge area aliases the K buffer
+    size_t kv = (size_t)2 * round_keys * hd * 2;
+    if (kv < comb) kv = comb;
+    const size_t smem = (size_t)16 * hd * 2 + kv + 4 * hd + 128;
     const float scale = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;   // softmax scale in log2 units
     dim3 grid(n_kv, B);
     int rc;
     if (hd == 64)
         rc = launch_decode_g<64>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                 (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale);
+                                 (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw);
     else if (hd == 128)
         rc = launch_decode_g<128>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                  (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale);
+                                  (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw);
     else {
         set_error("attention: head_dim %d not supported (64 or 128)", hd);
         return KX_EINVAL;

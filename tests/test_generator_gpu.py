@@ -148,3 +148,8 @@ def test_service_engine_learns_the_template_prefix():
     ids, _ = plain.generate_ids(toks, 6)
     assert [tokenizer.decode(r) for r in ids] == out1
     eng.close(); plain.close()
+
+
+def test_fused_rope_epilogue_with_head_dim_128():
+    """Prefill large enough for the CTA-pair QKV GEMM, whose epilogue rotates q/k and appends k/v itself."""
+    _check("tiny-llama-hd128", B=40, S=128, n_new=4)
