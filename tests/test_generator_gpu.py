@@ -153,3 +153,24 @@ def test_service_engine_learns_the_template_prefix():
 def test_fused_rope_epilogue_with_head_dim_128():
     """Prefill large enough for the CTA-pair QKV GEMM, whose epilogue rotates q/k and appends k/v itself."""
     _check("tiny-llama-hd128", B=40, S=128, n_new=4)
+
+
+def test_engine_edge_shapes_and_argument_errors():
+    """Smallest shapes (one sequence, one prompt token, one new token), a prompt that is not a multiple
+    of the KV page, and the limits the engine must refuse."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import _lib
+    cfg, gen, ref_emu, _ = _setup("tiny-qwen2", 3, 4, 40, 8)
+    g = torch.Generator().manual_seed(9)
+    for B, S, n_new in ((1, 1, 1), (1, 17, 3), (3, 33, 8), (4, 40, 1)):
+        toks = torch.randint(0, cfg.vocab, (B, S), generator=g)
+        ids, _ = gen.generate_ids(toks.numpy().astype(np.int32), n_new)
+        want, _ = ref_emu.generate(toks, n_new)
+        assert np.array_equal(ids, want.numpy()), (B, S, n_new)
+    with pytest.raises(_lib.KxError, match="exceeds max_batch"):
+        gen.generate_ids(np.zeros((5, 8), np.int32), 2)
+    with pytest.raises(_lib.KxError, match="exceed max_seq"):
+        gen.generate_ids(np.zeros((2, 45), np.int32), 8)
+    with pytest.raises(_lib.KxError, match="multiple of 16"):
+        gen.set_prefix(np.zeros(10, np.int32))
+    gen.close()
