@@ -68,7 +68,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams &p, float (&v)[3
                 float b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 if (p.bias) {
 #pragma unroll
-                    for (int t = 0; t < 8; ++t) b[t] = __ldg(p.bias + bcol0 + j + t);
+                    for (int t = 0; t < 8; ++t) b[t] = p.bias[bcol0 + j + t];
                 }
                 uint4 q;
                 q.x = pack_bf16(v[j + 0] + b[0], v[j + 1] + b[1]);
@@ -114,7 +114,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams &p, float (&v)[3
     } else {
         // accumulator row = feature, columns = batch entries: out[b * ldo + feature]
         const bool ok = arow < p.a_rows;
-        const float bias = (ok && p.bias) ? __ldg(p.bias + arow) : 0.0f;
+        const float bias = (ok && p.bias) ? p.bias[arow] : 0.0f;   // plain load: ld.global.nc may be hoisted above the null test
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const int b = bcol0 + j;
@@ -295,7 +295,7 @@ __device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[
         float a[2], b[2];
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
-            const float bias1 = p.bias ? __ldg(p.bias + fcol + j + t) : 0.f, bias2 = p.bias ? __ldg(p.bias + fcol + half + j + t) : 0.f;
+            const float bias1 = p.bias ? p.bias[fcol + j + t] : 0.f, bias2 = p.bias ? p.bias[fcol + half + j + t] : 0.f;
             const float v1 = __bfloat162float(__float2bfloat16(x1[j + t] + bias1));
             const float v2 = __bfloat162float(__float2bfloat16(x2[j + t] + bias2));
             if (is_v) { a[t] = v1; b[t] = v2; }
@@ -608,7 +608,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     if (warp >= 2) {
         const int r = (warp & 3) * 32 + lane, arow = m0 + r;
         const bool ok = arow < p.a_rows;
-        const float bias = (ok && p.bias) ? __ldg(p.bias + arow) : 0.0f;
+        const float bias = (ok && p.bias) ? p.bias[arow] : 0.0f;   // plain load: ld.global.nc may be hoisted above the null test
         const int cols_per = (BN + S - 1) / S;
         const int j0 = z * cols_per, j1 = min(BN, j0 + cols_per);
         const uint32_t local = smem_u32(partial);
