@@ -136,3 +136,12 @@ def stub_completion(prompt: str, unsafe_rate: float = 0.05) -> str:
     if (h >> 20) % 1000 < unsafe_rate * 1000:
         cmd += "; rm -rf /"
     return cmd
+
+
+def query_of_prompt(prompt: str) -> str:
+    """The request text inside a rendered prompt: what follows the last "User Request: " marker up to
+    the "Kubectl Command:" cue (both markers are part of the reference's template, app.py:50-57)."""
+    start = prompt.rfind("User Request: ")
+    start = 0 if start < 0 else start + len("User Request: ")
+    end = prompt.find("\nKubectl Command:", start)
+    return prompt[start:end if end >= 0 else len(prompt)]
