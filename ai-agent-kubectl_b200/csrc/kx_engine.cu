@@ -45,6 +45,11 @@ struct kx_engine {
     // tensor parallelism: partial sums of the row-parallel layers, argmax pairs, NCCL entry points
     float *tp_buf = nullptr;
     void *tp_pairs = nullptr, *tp_gathered = nullptr;
+    // fused P2P all-reduce (decode): receive buffers / flags on this GPU, and the peer's, mapped through CUDA IPC
+    float *p2p_recv = nullptr, *p2p_peer_recv = nullptr;
+    uint32_t *p2p_flag = nullptr, *p2p_peer_flag = nullptr, *p2p_epoch = nullptr;
+    int p2p_rows = 0;
+    int64_t p2p_launches = 0;
     void *comm = nullptr;
     int (*allreduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
     int (*allgather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
@@ -94,6 +99,7 @@ struct GemmCall {
     const CUtensorMap *b_half = nullptr;           // token-major pair kernel: weight map with a half-tile box
     int pair_bn = 0;                               // ... and its tile width (128 or 256)
     const GemmParams *extra = nullptr;             // EPI_QKV_ROPE: the rope / cache fields
+    bool tp_fused = false;                         // EPI_RESID + all-reduce over peer memory in the epilogue
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
@@ -104,6 +110,10 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
         p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
         p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
         p.n_q = c.extra->n_q; p.n_kv = c.extra->n_kv; p.hd = c.extra->hd;
+    }
+    if (c.tp_fused) {
+        p.tp_peer_recv = e->p2p_peer_recv; p.tp_peer_flag = e->p2p_peer_flag; p.tp_recv = e->p2p_recv;
+        p.tp_flag = e->p2p_flag; p.tp_epoch = e->p2p_epoch; p.tp_rows = e->p2p_rows;
     }
     if (!c.swap && c.b_half) return gemm_launch_pair(*c.a, *c.b_half, p, c.pair_bn, st);
     KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
@@ -147,6 +157,16 @@ int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, co
 int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     if (d.tp_size <= 1) return linear(e, l, M, EPI_RESID, e->resid, d.hidden, nullptr, st);
+    if (d.tp_size == 2 && e->p2p_peer_recv && M <= e->p2p_rows && M < 256 && linear_pair_bn(l, M) == 0) {
+        // decode: the swap-AB cluster GEMM reduces across the two ranks itself, over NVLink peer memory
+        const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
+        const int b_tiles = (M + bn - 1) / bn;
+        GemmCall c{l.w_full, l.x_b + bi, l.features, M, l.k, EPI_RESID, 1, pick_splits(l.features, l.k, b_tiles), bn,
+                   e->resid, d.hidden, nullptr};
+        c.tp_fused = true;
+        ++e->p2p_launches;
+        return run_gemm(e, c, st);
+    }
     KX_REQUIRE(e->comm && e->allreduce, KX_EINVAL, "engine: tensor parallelism needs kx_engine_set_collectives");
     KX_TRY(linear(e, l, M, EPI_F32, e->tp_buf, d.hidden, nullptr, st));
     const int rc = e->allreduce(e->tp_buf, e->tp_buf, (size_t)M * d.hidden, /*ncclFloat32*/ 7, /*ncclSum*/ 0, e->comm, st);
@@ -316,6 +336,37 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     return KX_OK;
 }
 
+// ---- fused P2P all-reduce set-up: export this rank's buffers, import the peer's (CUDA IPC) ----
+namespace { constexpr int kP2pSlots = 8192; }
+
+extern "C" int kx_engine_p2p_export(kx_engine *e, void *handles /* 2 x 64 bytes */) {
+    KX_REQUIRE(e && handles, KX_EINVAL, "kx_engine_p2p_export: NULL argument");
+    KX_REQUIRE(e->d.tp_size == 2, KX_EINVAL, "kx_engine_p2p_export: the fused all-reduce is built for tp_size 2");
+    if (!e->p2p_recv) {
+        e->p2p_rows = e->d.max_batch < 256 ? e->d.max_batch : 255;
+        const size_t bytes = (size_t)2 * e->p2p_rows * e->d.hidden * sizeof(float);
+        KX_TRY(dev_alloc(e, (void **)&e->p2p_recv, bytes));
+        KX_TRY(dev_alloc(e, (void **)&e->p2p_flag, kP2pSlots * 4));
+        KX_TRY(dev_alloc(e, (void **)&e->p2p_epoch, kP2pSlots * 4));
+        KX_CUDA(cudaMemset(e->p2p_flag, 0, kP2pSlots * 4));
+        KX_CUDA(cudaMemset(e->p2p_epoch, 0, kP2pSlots * 4));
+    }
+    cudaIpcMemHandle_t *h = reinterpret_cast<cudaIpcMemHandle_t *>(handles);
+    KX_CUDA(cudaIpcGetMemHandle(&h[0], e->p2p_recv));
+    KX_CUDA(cudaIpcGetMemHandle(&h[1], e->p2p_flag));
+    return KX_OK;
+}
+
+extern "C" int64_t kx_engine_p2p_launches(const kx_engine *e) { return e ? e->p2p_launches : 0; }
+
+extern "C" int kx_engine_p2p_import(kx_engine *e, const void *peer_handles /* 2 x 64 bytes */) {
+    KX_REQUIRE(e && peer_handles && e->p2p_recv, KX_EINVAL, "kx_engine_p2p_import: export first");
+    const cudaIpcMemHandle_t *h = reinterpret_cast<const cudaIpcMemHandle_t *>(peer_handles);
+    KX_CUDA(cudaIpcOpenMemHandle((void **)&e->p2p_peer_recv, h[0], cudaIpcMemLazyEnablePeerAccess));
+    KX_CUDA(cudaIpcOpenMemHandle((void **)&e->p2p_peer_flag, h[1], cudaIpcMemLazyEnablePeerAccess));
+    return KX_OK;
+}
+
 extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allreduce, void *allgather) {
     KX_REQUIRE(e && comm && allreduce && allgather, KX_EINVAL, "kx_engine_set_collectives: NULL argument");
     e->comm = comm;
@@ -362,6 +413,8 @@ extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32
 
 extern "C" void kx_engine_destroy(kx_engine *e) {
     if (!e) return;
+    if (e->p2p_peer_recv) cudaIpcCloseMemHandle(e->p2p_peer_recv);
+    if (e->p2p_peer_flag) cudaIpcCloseMemHandle(e->p2p_peer_flag);
     for (void *p : e->owned) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;

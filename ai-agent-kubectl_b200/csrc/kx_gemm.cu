@@ -615,8 +615,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         uint32_t peer[8];
 #pragma unroll
         for (int src = 0; src < 8; ++src) peer[src] = dsmem_addr(local, (uint32_t)(src < S ? src : 0));
-        for (int j = j0; j < j1; ++j) {
-            if (n0 + j >= p.b_rows) break;                     // warp-uniform
+        auto column_sum = [&](int j) -> float {
             float part[8];
 #pragma unroll
             for (int src = 0; src < 8; ++src)                  // all remote loads in flight together
@@ -624,7 +623,42 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             float v = 0.f;
 #pragma unroll
             for (int src = 0; src < 8; ++src) v += part[src];  // fixed order: deterministic sum
-            epilogue_swap_elem<EPI>(p, v, arow, n0 + j, ok, bias);
+            return v;
+        };
+        if (EPI == EPI_RESID && p.tp_peer_recv) {
+            // ---- fused tensor-parallel all-reduce (2 ranks) over peer memory ----
+            const uint32_t slot = (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z;
+            const uint32_t epoch = p.tp_epoch[slot] + 1;       // same count on both ranks: they run the same launches
+            const size_t buf = (size_t)(epoch & 1) * (size_t)p.tp_rows * p.ldo;
+            for (int j = j0; j < j1; ++j) {
+                if (n0 + j >= p.b_rows) break;
+                const float v = column_sum(j);
+                if (ok) p.tp_peer_recv[buf + (size_t)(n0 + j) * p.ldo + arow] = v;      // NVLink store
+            }
+            __threadfence_system();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) {
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.tp_peer_flag + slot), "r"(epoch) : "memory");
+                uint32_t seen;
+                do {
+                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.tp_flag + slot) : "memory");
+                } while ((int32_t)(seen - epoch) < 0);
+                p.tp_epoch[slot] = epoch;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            for (int j = j0; j < j1; ++j) {
+                if (n0 + j >= p.b_rows) break;
+                const float v = column_sum(j);                 // this rank's partial again (still in shared memory)
+                if (ok) {
+                    const float other = __ldcv(p.tp_recv + buf + (size_t)(n0 + j) * p.ldo + arow);   // the peer's partial
+                    reinterpret_cast<float *>(p.out)[(size_t)(n0 + j) * p.ldo + arow] += v + other;
+                }
+            }
+        } else {
+            for (int j = j0; j < j1; ++j) {
+                if (n0 + j >= p.b_rows) break;                 // warp-uniform
+                epilogue_swap_elem<EPI>(p, column_sum(j), arow, n0 + j, ok, bias);
+            }
         }
     }
     cluster_sync_all();                                        // peers may still be reading this CTA's partial
@@ -761,7 +795,7 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;      // no empty slice
     p.splits = splits;
-    if (p.swap && splits > 1) {
+    if (p.swap && (splits > 1 || p.tp_peer_recv)) {
         // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory
         if (splits > 8) splits = 8;
         p.kb_per_split = (total_kb + splits - 1) / splits;

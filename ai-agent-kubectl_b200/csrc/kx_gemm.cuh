@@ -26,6 +26,16 @@ struct GemmParams {
     void *kv_pages;          // this layer's pages
     const int *block_table;
     int max_pages, n_q, n_kv, hd;
+    // Tensor-parallel residual epilogue fused with the all-reduce (decode, 2 ranks, swap-AB cluster kernel):
+    // each CTA pushes its slice of this rank's partial sum straight into the PEER GPU's receive buffer over
+    // NVLink, publishes an epoch flag there, waits for the peer CTA of the same tile to do the same here, and
+    // adds both partials to the residual.  Buffers are double-buffered by epoch parity.
+    float *tp_peer_recv;     // peer GPU:  float [2][tp_rows * ldo]   (written by this rank)
+    uint32_t *tp_peer_flag;  // peer GPU:  uint32 [tiles]             (epoch published by this rank)
+    const float *tp_recv;    // this GPU:  the same two arrays, written by the peer
+    const uint32_t *tp_flag;
+    uint32_t *tp_epoch;      // this GPU:  uint32 [tiles], launches seen so far per tile slot
+    int tp_rows;             // rows of one receive buffer (max decode batch)
 };
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);

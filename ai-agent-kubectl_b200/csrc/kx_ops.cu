@@ -709,6 +709,8 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     const int nw = (int64_t)n_kv * B > 600 ? 4 : 8;
     int round_keys = ((max_T + 63) / 64) * 64;
     if (round_keys > 64 * nw) round_keys = 64 * nw;
+    const int fit = (int)((160 * 1024) / (4 * hd)) / 64 * 64;          // K and V of one round must fit in shared memory
+    if (round_keys > fit) round_keys = fit;
     const size_t comb = sizeof(float) * (2 * 8 * 16 + (size_t)8 * G * hd);       // merge area aliases the K buffer
     size_t kv = (size_t)2 * round_keys * hd * 2;
     if (kv < comb) kv = comb;

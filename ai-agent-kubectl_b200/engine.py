@@ -42,6 +42,9 @@ class KxGenStats(ctypes.Structure):
 _lib.declare("kx_engine_create", ctypes.c_int, [ctypes.POINTER(KxModelDesc), ctypes.POINTER(KxModelWeights),
                                                  ctypes.POINTER(c_void_p)])
 _lib.declare("kx_engine_set_collectives", ctypes.c_int, [c_void_p, c_void_p, c_void_p, c_void_p])
+_lib.declare("kx_engine_p2p_export", ctypes.c_int, [c_void_p, c_void_p])
+_lib.declare("kx_engine_p2p_import", ctypes.c_int, [c_void_p, c_void_p])
+_lib.declare("kx_engine_p2p_launches", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
@@ -90,6 +93,7 @@ class NcclComm:
     shared through torch.distributed (any backend)."""
 
     def __init__(self, rank: int, world: int, device: int, group=None):
+        self.group = group
         import glob
         import os
         import torch
@@ -128,7 +132,7 @@ class Generator:
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, max_seq: int = 320, device: int = 0,
                  weights: Optional[Dict] = None, prefill_chunk: int = 32768, tp_rank: int = 0, tp_size: int = 1,
-                 nccl: Optional["NcclComm"] = None):
+                 nccl: Optional["NcclComm"] = None, p2p: bool = True):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("the generator needs a CUDA device; there is no CPU fallback")
@@ -163,7 +167,23 @@ class Generator:
                     raise ValueError("tensor parallelism needs an NcclComm")
                 self.nccl = nccl
                 _lib.check(_lib.lib().kx_engine_set_collectives(h, nccl.comm, nccl.allreduce, nccl.allgather))
+                if tp_size == 2 and p2p:
+                    self._setup_p2p(h, tp_rank, nccl.group)
         self.last_stats: Optional[KxGenStats] = None
+
+    @staticmethod
+    def _setup_p2p(h, tp_rank, group):
+        """Swap CUDA IPC handles with the peer rank so the decode GEMMs can reduce over NVLink themselves."""
+        import torch.distributed as dist
+        mine = ctypes.create_string_buffer(128)
+        _lib.check(_lib.lib().kx_engine_p2p_export(h, mine))
+        box = [None, None]
+        dist.all_gather_object(box, bytes(mine.raw), group=group)
+        peer = ctypes.create_string_buffer(box[1 - tp_rank], 128)
+        _lib.check(_lib.lib().kx_engine_p2p_import(h, peer))
+
+    def p2p_launches(self) -> int:
+        return int(_lib.lib().kx_engine_p2p_launches(self._h))
 
     def device_bytes(self) -> int:
         return int(_lib.lib().kx_engine_device_bytes(self._h))

@@ -199,6 +199,17 @@ void kx_engine_destroy(kx_engine *e);
 int64_t kx_engine_device_bytes(const kx_engine *e);
 
 /*
+ * Fused tensor-parallel all-reduce for decode (tp_size 2): the row-parallel GEMMs (wo, wd) push their
+ * partial sums into the peer GPU's memory from their epilogue and add the peer's, instead of calling
+ * NCCL.  Each rank exports two CUDA IPC handles (2 x 64 bytes: receive buffer, flags), the host swaps
+ * them between the ranks, and each rank imports its peer's.  Without this set-up the engine uses the
+ * NCCL path of kx_engine_set_collectives for every token count.
+ */
+int kx_engine_p2p_export(kx_engine *e, void *handles);
+int kx_engine_p2p_import(kx_engine *e, const void *peer_handles);
+int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the fused all-reduce so far */
+
+/*
  * kx_engine_set_prefix -- prefill `n` tokens (a multiple of 16; host int32) ONCE and keep their
  * KV pages; every later kx_engine_generate treats its prompts as continuing that prefix
  * (positions start at n, the pages are shared by all sequences through the block table).

@@ -174,3 +174,8 @@ def test_engine_edge_shapes_and_argument_errors():
     with pytest.raises(_lib.KxError, match="multiple of 16"):
         gen.set_prefix(np.zeros(10, np.int32))
     gen.close()
+
+
+def test_long_context_head_dim_128_decode_rounds():
+    """Context longer than one shared-memory round of the decode attention kernel (head_dim 128)."""
+    _check("tiny-llama-hd128", B=3, S=700, n_new=4)

@@ -29,8 +29,15 @@ def _worker(rank, world, port, arch, B, S, n_new, out_dir):
     gen = engine.Generator(arch, weights=w, max_batch=B, max_seq=S + n_new, device=rank, tp_rank=rank, tp_size=world, nccl=nccl)
     toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(103)).numpy().astype(np.int32)
     ids, logits = gen.generate_ids(toks, n_new, want_logits=True)
-    ids2, _ = gen.generate_ids(toks, n_new)                       # CUDA-graph decode with captured collectives
-    torch.save({"ids": ids, "ids2": ids2, "logits": logits.cpu()}, os.path.join(out_dir, f"tp{rank}.pt"))
+    ids2, _ = gen.generate_ids(toks, n_new)                       # CUDA-graph decode, all-reduce fused in the GEMM epilogue
+    fused = gen.p2p_launches()
+    gen.close()
+    # the same with NCCL all-reduces only (no peer-memory set-up)
+    gen = engine.Generator(arch, weights=w, max_batch=B, max_seq=S + n_new, device=rank, tp_rank=rank, tp_size=world, nccl=nccl,
+                           p2p=False)
+    ids3, _ = gen.generate_ids(toks, n_new)
+    torch.save({"ids": ids, "ids2": ids2, "ids3": ids3, "fused": fused, "nccl_only_fused": gen.p2p_launches(),
+                "logits": logits.cpu()}, os.path.join(out_dir, f"tp{rank}.pt"))
     gen.close()
     nccl.close()
     dist.destroy_process_group()
@@ -47,6 +54,8 @@ def test_tp2_matches_the_oracle(tmp_path, arch):
     mp.spawn(_worker, args=(2, _free_port(), arch, B, S, n_new, str(tmp_path)), nprocs=2, join=True)
     r = [torch.load(tmp_path / f"tp{i}.pt", weights_only=False) for i in range(2)]
     assert np.array_equal(r[0]["ids"], r[1]["ids"]) and np.array_equal(r[0]["ids"], r[0]["ids2"])
+    assert np.array_equal(r[0]["ids"], r[0]["ids3"])                       # fused P2P all-reduce == NCCL all-reduce
+    assert r[0]["fused"] > 0 and r[1]["fused"] == r[0]["fused"] and r[0]["nccl_only_fused"] == 0
     cfg = model_config.get_config(arch)
     w = weights.make_weights(cfg, 3)
     ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True)
