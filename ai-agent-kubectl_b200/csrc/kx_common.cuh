@@ -13,7 +13,7 @@ extern std::atomic<int64_t> g_launches;
 
 // Library-owned device scratch, cached per (current device, stream, purpose) and grown on demand
 // (cudaMalloc only when it has to grow).  Valid until the next call on the same stream.
-enum ScratchTag { SCRATCH_K9_QUEUE = 0, SCRATCH_GEMM = 1, SCRATCH_TAGS = 2 };
+enum ScratchTag { SCRATCH_K9_QUEUE = 0, SCRATCH_GEMM = 1, SCRATCH_ATTN = 2, SCRATCH_TAGS = 3 };
 int stream_scratch(cudaStream_t stream, int tag, size_t bytes, void **out, bool zero_on_alloc = false);
 void release_scratch();
 

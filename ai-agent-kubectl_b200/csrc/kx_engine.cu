@@ -7,6 +7,7 @@
 // chunks of at most `prefill_chunk` tokens; every decode step is the same sequence of
 // launches, so after the first (eager) step the rest are replayed as one CUDA graph
 // with the positions and the step counter advanced on the device.
+#include <cstdlib>
 #include <vector>
 #include <cuda_bf16.h>
 #include "kx_common.cuh"
@@ -28,6 +29,10 @@ struct kx_engine {
     kx_model_desc d;
     int qkv_dim, q_dim, max_pages, num_pages, max_tokens;
     int prefix_len = 0;                            // tokens of shared prefix whose KV is already cached (multiple of 16)
+    // decode attention over the shared prefix: per-chunk partial (O, max/sum) of every (sequence, q head)
+    float *prefix_o = nullptr, *prefix_ml = nullptr;
+    size_t prefix_rows = 0;                        // capacity in (chunk, sequence, head) rows
+    bool share_prefix = true;                      // KX_SHARED_PREFIX=0: every sequence re-reads the prefix (for A/B timing)
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
     const float *rope;
@@ -195,8 +200,16 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(linear(e, qkv, M, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, st));
     }
     if (decode) {
+        int key0 = 0, n_part = 0;
+        if (e->share_prefix && e->prefix_len >= 64 && M >= 2 && e->prefix_o &&
+            (size_t)attn_prefix_parts(M, d.n_q, d.n_kv, e->prefix_len, nullptr) * M * d.n_q <= e->prefix_rows) {
+            // the batch shares its first prefix_len keys: read them once per 64 query rows, not once per sequence
+            KX_TRY(op_attn_prefix(e->qkv, e->qkv_dim, L.kv_pages, e->block_table + (size_t)d.max_batch * e->max_pages, e->pos,
+                                  e->rope, M, d.n_q, d.n_kv, d.head_dim, e->prefix_len, e->prefix_o, e->prefix_ml, &n_part, st));
+            key0 = e->prefix_len;
+        }
         KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos,
-                              e->rope, M, max_T, d.n_q, d.n_kv, d.head_dim, st));
+                              e->rope, M, max_T, d.n_q, d.n_kv, d.head_dim, key0, e->prefix_o, e->prefix_ml, n_part, st));
     } else {
         if (!fused_rope)
             KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
@@ -249,6 +262,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     KX_REQUIRE(d.max_seq <= d.max_pos, KX_EINVAL, "kx_engine_create: max_seq exceeds the rope table");
     kx_engine *e = new kx_engine();
     e->d = d;
+    if (const char *v = getenv("KX_SHARED_PREFIX")) e->share_prefix = v[0] != '0';
     if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
     e->q_dim = d.n_q * d.head_dim;
@@ -397,6 +411,18 @@ extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32
     KX_CUDA(cudaStreamSynchronize(st));
     e->prefix_len = 0;
     if (n == 0) return KX_OK;
+    if (e->share_prefix && n >= 64) {                // partial-result buffers of the shared-prefix decode attention
+        size_t need = 0;
+        for (int b = 2; b <= d.max_batch; ++b) {
+            const size_t r = (size_t)attn_prefix_parts(b, d.n_q, d.n_kv, n, nullptr) * b * d.n_q;
+            if (r > need) need = r;
+        }
+        if (need > e->prefix_rows) {                 // grown, never shrunk; the old buffers stay owned until destroy
+            KX_TRY(dev_alloc(e, (void **)&e->prefix_o, need * d.head_dim * sizeof(float)));
+            KX_TRY(dev_alloc(e, (void **)&e->prefix_ml, need * 2 * sizeof(float)));
+            e->prefix_rows = need;
+        }
+    }
     // prefill the prefix once, as the extra sequence `max_batch`
     std::vector<int> hpos(n), hseq(n, d.max_batch);
     for (int t = 0; t < n; ++t) hpos[t] = t;

@@ -365,7 +365,7 @@ __global__ void __launch_bounds__(NW * 32)
 attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
                    __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
                    const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
-                   int round_keys) {
+                   int round_keys, int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part) {
     extern __shared__ __align__(128) uint8_t smem_dec[];
     asm volatile("griddepcontrol.launch_dependents;");   // let a dependent GEMM start prefetching its weights
     asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic serialization: qkv comes from the predecessor
@@ -422,7 +422,9 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
     float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
     const int g = lane >> 2, tq = lane & 3;
 
-    for (int c0 = 0; c0 < T; c0 += ROUND) {
+    // keys below key0 belong to a prefix shared by the whole batch: attn_prefix_kernel has already
+    // reduced them to n_part partial (max, sum, O) triples per query head, merged in below
+    for (int c0 = key0; c0 < T; c0 += ROUND) {
         const int n = min(T, c0 + ROUND) - c0;        // valid keys this round
         const int nfill = (n + 63) & ~63;             // whole 64-key blocks are read by ldmatrix
         for (int i = tid; i < nfill * CH; i += (NW * 32)) {
@@ -534,11 +536,14 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         }
     }
     __syncthreads();
+    const size_t part_rows = (size_t)gridDim.y * n_q;                       // rows of one prefix partial: (sequence, q head)
     for (int i = tid; i < G * HD; i += (NW * 32)) {
         const int h = i / HD, d = i - h * HD;
+        const size_t prow = (size_t)b * n_q + kvh * G + h;
         float M = -INFINITY;
 #pragma unroll
         for (int w = 0; w < NW; ++w) M = fmaxf(M, comb_m[w * 16 + h]);
+        for (int c = 0; c < n_part; ++c) M = fmaxf(M, part_ml[(c * part_rows + prow) * 2]);
         float num = 0.f, den = 0.f;
 #pragma unroll
         for (int w = 0; w < NW; ++w) {
@@ -546,7 +551,365 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
             num += f * comb_o[(w * G + h) * HD + d];
             den += f * comb_l[w * 16 + h];
         }
+        for (int c = 0; c < n_part; ++c) {
+            const float2 ml = *reinterpret_cast<const float2 *>(part_ml + (c * part_rows + prow) * 2);
+            const float f = exp2f((ml.x - M) * scale_log2);
+            num += f * part_o[(c * part_rows + prow) * HD + d];
+            den += f * ml.y;
+        }
         out[(size_t)b * out_ld + (size_t)(kvh * G + h) * HD + d] = __float2bfloat16(num / den);
+    }
+}
+
+// ---- decode attention, one WARP per (sequence, kv head) -------------------------------------
+// For a wide batch there are more (sequence, kv head) pairs than the GPU has warps to spare, so splitting
+// one pair's keys over a CTA (attn_decode_kernel) only adds barriers and a merge.  Here a warp owns a pair:
+// it streams the pair's keys through its private NS-stage cp.async ring, KB keys per stage, with the same
+// 16-row tensor-core tile for the G query heads, and no block-level synchronisation at all.  The first
+// stages are requested before griddepcontrol.wait (cached K/V were written by earlier steps, pos by the
+// step's first kernel, both complete before the predecessor GEMM could start).
+template <int HD, int G, int KB, int NS>
+__global__ void __launch_bounds__(128)
+attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
+                        __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
+                        const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
+                        int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part, int n_tasks) {
+    extern __shared__ __align__(128) uint8_t smem_dw[];
+    asm volatile("griddepcontrol.launch_dependents;");
+    constexpr int CH = HD / 8, HALF = HD / 2;
+    constexpr int QT = 16 * HD * 2, ST = KB * HD * 2, NEWB = 2 * HD * 2;
+    constexpr int WARP_BYTES = QT + NS * 2 * ST + NEWB;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int task = blockIdx.x * 4 + warp;
+    const bool live = task < n_tasks;
+    const int b = live ? task / n_kv : 0, kvh = live ? task - b * n_kv : 0;
+    uint8_t *Qs = smem_dw + warp * WARP_BYTES;
+    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ring_u = qs_u + QT;
+    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Qs + QT + NS * 2 * ST), *vnew = knew + HD;
+    const int p = pos[b], T = p + 1;
+    const int *bt = block_table + (size_t)b * max_pages;
+    const int nblk = live ? (T - key0 + KB - 1) / KB : 0;
+
+    auto fetch = [&](int blk) {                       // keys key0 + blk KB ... into stage blk % NS
+        const uint32_t kdst = ring_u + (uint32_t)(blk % NS) * 2 * ST, vdst = kdst + ST;
+        const int c0 = key0 + blk * KB;
+#pragma unroll
+        for (int i = lane; i < KB * CH; i += 32) {
+            const int r = i / CH, c = i - r * CH;
+            const int t = c0 + r;
+            const bool ok = t < T;
+            const int tt = ok ? t : p;
+            const __nv_bfloat16 *kp = pages + (((size_t)bt[tt / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(tt % kPage) * HD + c * 8;
+            cp_async16_zfill(kdst + swz<HD>(r, c), kp, ok);
+            cp_async16_zfill(vdst + swz<HD>(r, c), kp + (size_t)n_kv * kPage * HD, ok);
+        }
+    };
+#pragma unroll
+    for (int i = 0; i < NS - 1; ++i) {                // prologue: NS-1 stages in flight (empty groups keep the count uniform)
+        if (i < nblk) fetch(i);
+        cp_async_commit();
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // qkv comes from the predecessor
+    if (!live) return;
+
+    // RoPE: q heads -> Q tile rows 0..G-1, k -> cache and knew, v -> cache and vnew
+    {
+        const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
+        const float2 *cs = rope + (size_t)p * HALF;
+        __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
+        __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
+        for (int i = lane; i < (G + 1) * HALF; i += 32) {
+            const int h = i / HALF, d = i - h * HALF;
+            const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
+            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
+            const float2 c = cs[d];
+            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
+            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            if (h < G) {
+                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, d >> 3) + (d & 7) * 2) = o1;
+                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+            } else {
+                kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2;
+            }
+        }
+        const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
+        for (int i = lane; i < HD; i += 32) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
+        for (int i = lane; i < (16 - G) * CH; i += 32)
+            *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
+    uint32_t qf[HD / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], qs_u + swz<HD>(lane & 15, 2 * ks + (lane >> 4)));
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+    const int g = lane >> 2, tq = lane & 3;
+
+    for (int blk = 0; blk < nblk; ++blk) {
+        if (blk + NS - 1 < nblk) fetch(blk + NS - 1);
+        cp_async_commit();
+        cp_async_wait<NS - 1>();                      // block blk has landed (for this lane)
+        __syncwarp();                                 // ... and for the whole warp
+        const uint32_t ks_u = ring_u + (uint32_t)(blk % NS) * 2 * ST, vs_u = ks_u + ST;
+        const int c0 = key0 + blk * KB;
+        const int n = min(T - c0, KB);
+        if (blk == nblk - 1) {                        // the new token's row comes from this warp, not from the copy
+            if (lane < CH) {
+                uint8_t *ring = Qs + QT + (blk % NS) * 2 * ST;
+                *reinterpret_cast<uint4 *>(ring + swz<HD>(p - c0, lane)) = reinterpret_cast<const uint4 *>(knew)[lane];
+                *reinterpret_cast<uint4 *>(ring + ST + swz<HD>(p - c0, lane)) = reinterpret_cast<const uint4 *>(vnew)[lane];
+            }
+            __syncwarp();
+        }
+        float s[KB / 8][4];
+#pragma unroll
+        for (int j = 0; j < KB / 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+#pragma unroll
+        for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+            for (int jp = 0; jp < KB / 16; ++jp) {
+                uint32_t kf[4];
+                ldsm_x4(kf, ks_u + swz<HD>(jp * 16 + (lane & 7) + ((lane >> 4) << 3), 2 * ks + ((lane >> 3) & 1)));
+                mma_bf16(s[2 * jp], qf[ks], kf[0], kf[1]);
+                mma_bf16(s[2 * jp + 1], qf[ks], kf[2], kf[3]);
+            }
+        }
+        float mx[2] = {mrow[0], mrow[1]};
+#pragma unroll
+        for (int j = 0; j < KB / 8; ++j) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (j * 8 + 2 * tq + (e & 1) >= n) s[j][e] = -INFINITY;
+                mx[e >> 1] = fmaxf(mx[e >> 1], s[j][e]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+        }
+        float corr[2], msc[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            corr[r] = exp2f((mrow[r] - mx[r]) * scale_log2);
+            mrow[r] = mx[r];
+            msc[r] = mx[r] * scale_log2;
+            lrow[r] *= corr[r];
+        }
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) { o[j][0] *= corr[0]; o[j][1] *= corr[0]; o[j][2] *= corr[1]; o[j][3] *= corr[1]; }
+        uint32_t pf[KB / 16][4];
+#pragma unroll
+        for (int j = 0; j < KB / 8; ++j) {
+            const float p0 = exp2f(s[j][0] * scale_log2 - msc[0]), p1 = exp2f(s[j][1] * scale_log2 - msc[0]);
+            const float p2 = exp2f(s[j][2] * scale_log2 - msc[1]), p3 = exp2f(s[j][3] * scale_log2 - msc[1]);
+            lrow[0] += p0 + p1;
+            lrow[1] += p2 + p3;
+            pf[j >> 1][(j & 1) * 2] = pack2(p0, p1);
+            pf[j >> 1][(j & 1) * 2 + 1] = pack2(p2, p3);
+        }
+#pragma unroll
+        for (int kk = 0; kk < KB / 16; ++kk) {
+#pragma unroll
+            for (int dp = 0; dp < HD / 16; ++dp) {
+                uint32_t vf[4];
+                ldsm_x4_t(vf, vs_u + swz<HD>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), 2 * dp + (lane >> 4)));
+                mma_bf16(o[2 * dp], pf[kk], vf[0], vf[1]);
+                mma_bf16(o[2 * dp + 1], pf[kk], vf[2], vf[3]);
+            }
+        }
+        __syncwarp();                                 // every lane is done with this stage before it is refilled
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 2);
+    }
+    // merge with the shared-prefix partials (if any), normalise, store the G real rows
+    const size_t part_rows = (size_t)(n_tasks / n_kv) * n_q;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int h = g + 8 * r;
+        if (h >= G) continue;
+        const size_t prow = (size_t)b * n_q + kvh * G + h;
+        float M = mrow[r];
+        for (int c = 0; c < n_part; ++c) M = fmaxf(M, part_ml[(c * part_rows + prow) * 2]);
+        const float fs = exp2f((mrow[r] - M) * scale_log2);
+        float den = fs * lrow[r];
+        float acc[HD / 8][2];
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) { acc[j][0] = fs * o[j][2 * r]; acc[j][1] = fs * o[j][2 * r + 1]; }
+        for (int c = 0; c < n_part; ++c) {
+            const float2 ml = *reinterpret_cast<const float2 *>(part_ml + (c * part_rows + prow) * 2);
+            const float f = exp2f((ml.x - M) * scale_log2);
+            den += f * ml.y;
+            const float *po = part_o + (c * part_rows + prow) * HD + 2 * tq;
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) {
+                const float2 v = *reinterpret_cast<const float2 *>(po + j * 8);
+                acc[j][0] += f * v.x; acc[j][1] += f * v.y;
+            }
+        }
+        const float inv = 1.0f / den;
+        __nv_bfloat16 *orow = out + (size_t)b * out_ld + (size_t)(kvh * G + h) * HD + 2 * tq;
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j)
+            *reinterpret_cast<uint32_t *>(orow + j * 8) = pack2(acc[j][0] * inv, acc[j][1] * inv);
+    }
+}
+
+// ---- decode attention over a prefix shared by the whole batch ("read the prefix once") ----
+// Every sequence's first P keys are the same cached pages (kx_engine_set_prefix), so for one kv head the
+// B x G query rows of the step attend to them as one tall tile problem: grid (n_kv, ceil(B G / 64), chunks),
+// 128 threads, each CTA takes 64 query rows (row = b G + g, rotated here like the decode kernel rotates
+// them) against one chunk of the prefix and writes an unnormalised partial (max, sum, O[HD]) per row.
+// K/V of the prefix are read once per 64 rows instead of once per sequence.  The prefix pages do not depend
+// on the preceding GEMM, so the first K/V tile is requested before griddepcontrol.wait.
+template <int HD>
+__global__ void __launch_bounds__(128)
+attn_prefix_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, const __nv_bfloat16 *__restrict__ pages,
+                   const int *__restrict__ bt, const int *__restrict__ pos, const float2 *__restrict__ rope,
+                   int B, int G, int n_q, int n_kv, int P, int chunk_keys, float scale_log2,
+                   float *__restrict__ part_o, float *__restrict__ part_ml) {
+    extern __shared__ __align__(128) uint8_t smem_attn[];
+    asm volatile("griddepcontrol.launch_dependents;");
+    constexpr int CH = HD / 8, HALF = HD / 2;
+    constexpr int TILE = 64 * HD * 2;
+    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(smem_attn);
+    const int kvh = blockIdx.x, rt = blockIdx.y, chunk = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int kbeg = chunk * chunk_keys, kend = min(P, kbeg + chunk_keys);
+    const int nkb = (kend - kbeg + 63) / 64;
+    const int rows = B * G;
+
+    auto fetch_kv = [&](int kb) {
+        const uint32_t kdst = qs_u + TILE + (uint32_t)(kb & 1) * 2 * TILE, vdst = kdst + TILE;
+        for (int i = tid; i < 64 * CH; i += 128) {
+            const int r = i / CH, c = i - r * CH;
+            const int t = kbeg + kb * 64 + r;
+            const bool ok = t < kend;
+            const int tt = ok ? t : kbeg;
+            const __nv_bfloat16 *kp = pages + (((size_t)bt[tt / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(tt % kPage) * HD + c * 8;
+            cp_async16_zfill(kdst + swz<HD>(r, c), kp, ok);
+            cp_async16_zfill(vdst + swz<HD>(r, c), kp + (size_t)n_kv * kPage * HD, ok);
+        }
+    };
+    fetch_kv(0);
+    cp_async_commit();
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // q comes from the QKV GEMM
+    for (int i = tid; i < 64 * HALF; i += 128) {          // rotated q rows -> Q tile (rows past B G are zero)
+        const int r = i / HALF, d = i - r * HALF;
+        const int row = rt * 64 + r;
+        __nv_bfloat16 o1 = __float2bfloat16(0.f), o2 = o1;
+        if (row < rows) {
+            const int b = row / G, g = row - b * G;
+            const __nv_bfloat16 *src = qkv + (size_t)b * qkv_ld + (size_t)(kvh * G + g) * HD;
+            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
+            const float2 c = rope[(size_t)pos[b] * HALF + d];
+            o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
+            o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+        }
+        *reinterpret_cast<__nv_bfloat16 *>(smem_attn + swz<HD>(r, d >> 3) + (d & 7) * 2) = o1;
+        *reinterpret_cast<__nv_bfloat16 *>(smem_attn + swz<HD>(r, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+    }
+
+    uint32_t qf[HD / 16][4];
+    float o[HD / 8][4];
+#pragma unroll
+    for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+    const int g8 = lane >> 2, tq = lane & 3;
+
+    for (int kb = 0; kb < nkb; ++kb) {
+        if (kb + 1 < nkb) { fetch_kv(kb + 1); cp_async_commit(); cp_async_wait<1>(); }
+        else cp_async_wait<0>();
+        __syncthreads();
+        if (kb == 0) {
+#pragma unroll
+            for (int ks = 0; ks < HD / 16; ++ks)
+                ldsm_x4(qf[ks], qs_u + swz<HD>(warp * 16 + (lane & 15), 2 * ks + (lane >> 4)));
+        }
+        const uint32_t ks_u = qs_u + TILE + (uint32_t)(kb & 1) * 2 * TILE, vs_u = ks_u + TILE;
+        float s[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+#pragma unroll
+        for (int ks = 0; ks < HD / 16; ++ks) {
+#pragma unroll
+            for (int jp = 0; jp < 4; ++jp) {
+                uint32_t kf[4];
+                ldsm_x4(kf, ks_u + swz<HD>(jp * 16 + (lane & 7) + ((lane >> 4) << 3), 2 * ks + ((lane >> 3) & 1)));
+                mma_bf16(s[2 * jp], qf[ks], kf[0], kf[1]);
+                mma_bf16(s[2 * jp + 1], qf[ks], kf[2], kf[3]);
+            }
+        }
+        const int nvalid = kend - kbeg - kb * 64;              // keys of this tile inside the chunk
+        float mx[2] = {mrow[0], mrow[1]};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (j * 8 + 2 * tq + (e & 1) >= nvalid) s[j][e] = -INFINITY;
+                mx[e >> 1] = fmaxf(mx[e >> 1], s[j][e]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+        }
+        float corr[2], msc[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            corr[r] = exp2f((mrow[r] - mx[r]) * scale_log2);
+            mrow[r] = mx[r];
+            msc[r] = mx[r] * scale_log2;
+            lrow[r] *= corr[r];
+        }
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j) { o[j][0] *= corr[0]; o[j][1] *= corr[0]; o[j][2] *= corr[1]; o[j][3] *= corr[1]; }
+        uint32_t pf[4][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float p0 = exp2f(s[j][0] * scale_log2 - msc[0]), p1 = exp2f(s[j][1] * scale_log2 - msc[0]);
+            const float p2 = exp2f(s[j][2] * scale_log2 - msc[1]), p3 = exp2f(s[j][3] * scale_log2 - msc[1]);
+            lrow[0] += p0 + p1;
+            lrow[1] += p2 + p3;
+            pf[j >> 1][(j & 1) * 2] = pack2(p0, p1);
+            pf[j >> 1][(j & 1) * 2 + 1] = pack2(p2, p3);
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+            for (int dp = 0; dp < HD / 16; ++dp) {
+                uint32_t vf[4];
+                ldsm_x4_t(vf, vs_u + swz<HD>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), 2 * dp + (lane >> 4)));
+                mma_bf16(o[2 * dp], pf[kk], vf[0], vf[1]);
+                mma_bf16(o[2 * dp + 1], pf[kk], vf[2], vf[3]);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
+        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 2);
+    }
+    const size_t part_rows = (size_t)B * n_q;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const int row = rt * 64 + warp * 16 + g8 + r * 8;
+        if (row >= rows) continue;
+        const int b = row / G, g = row - b * G;
+        const size_t prow = (size_t)chunk * part_rows + (size_t)b * n_q + kvh * G + g;
+        if (tq == 0) *reinterpret_cast<float2 *>(part_ml + prow * 2) = make_float2(mrow[r], lrow[r]);
+        float *po = part_o + prow * HD + 2 * tq;
+#pragma unroll
+        for (int j = 0; j < HD / 8; ++j)
+            *reinterpret_cast<float2 *>(po + j * 8) = make_float2(o[j][2 * r], o[j][2 * r + 1]);
     }
 }
 
@@ -638,10 +1001,37 @@ __global__ void advance_kernel(int *pos, int n) {
     if (i < n) pos[i] += 1;
 }
 
+template <int HD, int NS>
+int launch_decode_warp(int G, int n_tasks, cudaStream_t st, const __nv_bfloat16 *qkv, int qkv_ld, __nv_bfloat16 *out, int out_ld,
+                       __nv_bfloat16 *pages, const int *bt, int max_pages, const int *pos, const float2 *rope, int n_q, int n_kv,
+                       float scale, int key0, const float *part_o, const float *part_ml, int n_part) {
+    constexpr int KB = HD == 64 ? 32 : 16;
+    constexpr size_t smem = (size_t)4 * (16 * HD * 2 + NS * 2 * KB * HD * 2 + 2 * HD * 2);
+    const dim3 grid((n_tasks + 3) / 4);
+#define KX_DECW(GV)                                                                                          \
+    case GV: {                                                                                               \
+        auto k = attn_decode_warp_kernel<HD, GV, KB, NS>;                                                    \
+        static bool granted = false;   /* first use is the eager decode step, outside any capture */         \
+        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); granted = true; } \
+        KX_CUDA(launch_pdl(k, grid, dim3(128), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, \
+                           key0, part_o, part_ml, n_part, n_tasks));                                         \
+        break;                                                                                               \
+    }
+    switch (G) {
+        KX_DECW(1) KX_DECW(2) KX_DECW(4) KX_DECW(7) KX_DECW(8)
+        default:
+            set_error("attention: unsupported GQA group size %d", G);
+            return KX_EINVAL;
+    }
+#undef KX_DECW
+    return KX_OK;
+}
+
 template <int HD>
 int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_bfloat16 *qkv, int qkv_ld,
                     __nv_bfloat16 *out, int out_ld, __nv_bfloat16 *pages, const int *bt, int max_pages,
-                    const int *pos, const float2 *rope, int n_q, int n_kv, float scale, int round_keys, int nw) {
+                    const int *pos, const float2 *rope, int n_q, int n_kv, float scale, int round_keys, int nw,
+                    int key0, const float *part_o, const float *part_ml, int n_part) {
 #define KX_DEC(GV)                                                                                          \
     case GV: {                                                                                              \
         auto k = nw == 8 ? attn_decode_kernel<HD, GV, 8> : attn_decode_kernel<HD, GV, 4>;                   \
@@ -650,7 +1040,7 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
             granted[nw == 8] = smem;                                                                        \
         }                                                                                                   \
-        KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys)); \
+        KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys, key0, part_o, part_ml, n_part)); \
         break;                                                                                              \
     }
     switch (G) {
@@ -701,13 +1091,13 @@ int op_rope_append(void *qkv, int qkv_ld, const int *pos, const int *seq, const 
 
 int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pages, const int *block_table,
                    int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
-                   cudaStream_t st) {
+                   int key0, const float *part_o, const float *part_ml, int n_part, cudaStream_t st) {
     const int G = n_q / n_kv;
-    (void)max_T;                                      // any context length: K/V are consumed 256 keys per round
     KX_REQUIRE(G <= 16, KX_EINVAL, "attention: GQA group of %d query heads per kv head exceeds 16", G);
-    // one round holds the whole context when it fits (<= 512 keys); shared memory is sized for it
-    const int nw = (int64_t)n_kv * B > 600 ? 4 : 8;
-    int round_keys = ((max_T + 63) / 64) * 64;
+    KX_REQUIRE(key0 == 0 || (part_o && part_ml && n_part > 0), KX_EINVAL, "attention: shared-prefix partials missing");
+    // one round holds the whole (non-shared) context when it fits (<= 512 keys); shared memory is sized for it
+    int round_keys = ((max_T - key0 + 63) / 64) * 64;
+    const int nw = ((int64_t)n_kv * B > 600 || round_keys <= 256) ? 4 : 8;
     if (round_keys > 64 * nw) round_keys = 64 * nw;
     const int fit = (int)((160 * 1024) / (4 * hd)) / 64 * 64;          // K and V of one round must fit in shared memory
     if (round_keys > fit) round_keys = fit;
@@ -718,12 +1108,31 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     const float scale = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;   // softmax scale in log2 units
     dim3 grid(n_kv, B);
     int rc;
+    const int n_tasks = n_kv * B;
+    if ((hd == 64 || hd == 128) && (n_tasks >= 512 || max_T - key0 <= 128)) {
+        // many (sequence, kv head) pairs, or few keys each: one warp per pair, no CTA-level split of the keys
+        const bool deep = (n_tasks + 3) / 4 <= 148;            // one CTA per SM anyway: spend the shared memory on a deeper ring
+        const __nv_bfloat16 *q = (const __nv_bfloat16 *)qkv;
+        __nv_bfloat16 *o = (__nv_bfloat16 *)out, *pg = (__nv_bfloat16 *)pages;
+        const float2 *rp = (const float2 *)rope;
+        if (hd == 64)
+            rc = deep ? launch_decode_warp<64, 4>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part)
+                      : launch_decode_warp<64, 2>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part);
+        else
+            rc = deep ? launch_decode_warp<128, 4>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part)
+                      : launch_decode_warp<128, 2>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part);
+        if (rc != KX_OK) return rc;
+        count_launch();
+        return KX_OK;
+    }
     if (hd == 64)
         rc = launch_decode_g<64>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                 (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw);
+                                 (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw,
+                                 key0, part_o, part_ml, n_part);
     else if (hd == 128)
         rc = launch_decode_g<128>(G, grid, smem, st, (const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
-                                  (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw);
+                                  (__nv_bfloat16 *)pages, block_table, max_pages, pos, (const float2 *)rope, n_q, n_kv, scale, round_keys, nw,
+                                  key0, part_o, part_ml, n_part);
     else {
         set_error("attention: head_dim %d not supported (64 or 128)", hd);
         return KX_EINVAL;
@@ -731,6 +1140,46 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     if (rc != KX_OK) return rc;
     count_launch();
     KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+// chunks the shared prefix is cut into for a batch of B: enough CTAs for two per SM, 64-key granularity
+int attn_prefix_parts(int B, int n_q, int n_kv, int P, int *chunk_keys) {
+    const int G = n_q / n_kv;
+    const int tiles = n_kv * ((B * G + 63) / 64);
+    int nc = (296 + tiles - 1) / tiles;
+    if (nc > 16) nc = 16;
+    const int blocks = (P + 63) / 64;
+    if (nc > blocks) nc = blocks;
+    if (nc < 1) nc = 1;
+    const int ck = ((blocks + nc - 1) / nc) * 64;
+    if (chunk_keys) *chunk_keys = ck;
+    return (P + ck - 1) / ck;
+}
+
+int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt_prefix, const int *pos, const float *rope,
+                   int B, int n_q, int n_kv, int hd, int P, float *part_o, float *part_ml, int *n_part, cudaStream_t st) {
+    KX_REQUIRE(P > 0 && part_o && part_ml && n_part, KX_EINVAL, "prefix attention: bad argument");
+    const int G = n_q / n_kv;
+    int ck = 0;
+    const int nc = attn_prefix_parts(B, n_q, n_kv, P, &ck);
+    *n_part = nc;
+    const float scale_log2 = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
+    dim3 grid(n_kv, (B * G + 63) / 64, nc);
+    if (hd == 64) {
+        KX_CUDA(launch_pdl(attn_prefix_kernel<64>, grid, dim3(128), (size_t)5 * 64 * 64 * 2, st, (const __nv_bfloat16 *)qkv, qkv_ld,
+                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
+    } else if (hd == 128) {
+        auto k = attn_prefix_kernel<128>;
+        static bool granted = false;                   // first use is the eager decode step, outside any capture
+        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); granted = true; }
+        KX_CUDA(launch_pdl(k, grid, dim3(128), (size_t)5 * 64 * 128 * 2, st, (const __nv_bfloat16 *)qkv, qkv_ld,
+                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
+    } else {
+        set_error("attention: head_dim %d not supported (64 or 128)", hd);
+        return KX_EINVAL;
+    }
+    count_launch();
     return KX_OK;
 }
 
@@ -793,3 +1242,32 @@ int op_advance(int *pos, int n, cudaStream_t st) {
 }
 
 }  // namespace kx
+
+extern "C" int kx_attn_decode(const void *d_qkv, int32_t qkv_ld, void *d_out, int32_t out_ld, void *d_pages,
+                              const int32_t *d_block_table, int32_t max_pages, const int32_t *d_pos, const float *d_rope,
+                              int32_t B, int32_t max_T, int32_t n_q, int32_t n_kv, int32_t hd, int32_t prefix_len,
+                              int32_t prefix_row, void *stream) {
+    using namespace kx;
+    KX_REQUIRE(d_qkv && d_out && d_pages && d_block_table && d_pos && d_rope, KX_EINVAL, "kx_attn_decode: NULL argument");
+    KX_REQUIRE(B >= 1 && n_kv >= 1 && n_q % n_kv == 0 && max_T >= 1, KX_EINVAL, "kx_attn_decode: bad shape");
+    KX_REQUIRE(prefix_len >= 0 && prefix_len % KX_KV_PAGE == 0 && prefix_len < max_T, KX_EINVAL,
+               "kx_attn_decode: prefix_len %d must be a multiple of %d below max_T", prefix_len, KX_KV_PAGE);
+    cudaStream_t st = (cudaStream_t)stream;
+    int key0 = 0, n_part = 0;
+    float *part_o = nullptr, *part_ml = nullptr;
+    if (prefix_len > 0) {
+        KX_REQUIRE(prefix_len >= 64 && prefix_row >= 0, KX_EINVAL, "kx_attn_decode: a shared prefix needs >= 64 keys and its block-table row");
+        const size_t rows = (size_t)attn_prefix_parts(B, n_q, n_kv, prefix_len, nullptr) * B * n_q;
+        void *scratch = nullptr;
+        int rc = stream_scratch(st, SCRATCH_ATTN, rows * (hd + 2) * sizeof(float), &scratch);
+        if (rc != KX_OK) return rc;
+        part_o = (float *)scratch;
+        part_ml = part_o + rows * hd;
+        rc = op_attn_prefix(d_qkv, qkv_ld, d_pages, d_block_table + (size_t)prefix_row * max_pages, d_pos, d_rope, B, n_q, n_kv, hd,
+                            prefix_len, part_o, part_ml, &n_part, st);
+        if (rc != KX_OK) return rc;
+        key0 = prefix_len;
+    }
+    return op_attn_decode(d_qkv, qkv_ld, d_out, out_ld, d_pages, d_block_table, max_pages, d_pos, d_rope, B, max_T, n_q, n_kv, hd,
+                          key0, part_o, part_ml, n_part, st);
+}

@@ -11,10 +11,15 @@ int op_embed(const int *tokens, const void *table, float *x, int M, int H, cudaS
 int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st);
 int op_rope_append(void *qkv, int qkv_ld, const int *pos, const int *seq, const float *rope, void *pages,
                    const int *block_table, int max_pages, int M, int n_q, int n_kv, int hd, cudaStream_t st);
-// decode attention also applies RoPE to the new token's q/k and appends its k, v to the cache
+// decode attention also applies RoPE to the new token's q/k and appends its k, v to the cache.
+// key0 > 0: keys [0, key0) are a prefix shared by the batch, already reduced by op_attn_prefix to n_part partials.
 int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pages, const int *block_table,
                    int max_pages, const int *pos, const float *rope, int B, int max_T, int n_q, int n_kv, int hd,
-                   cudaStream_t st);
+                   int key0, const float *part_o, const float *part_ml, int n_part, cudaStream_t st);
+// shared-prefix part of decode attention: the prefix K/V are read once per 64 query rows, not once per sequence
+int attn_prefix_parts(int B, int n_q, int n_kv, int P, int *chunk_keys);
+int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt_prefix, const int *pos, const float *rope,
+                   int B, int n_q, int n_kv, int hd, int P, float *part_o, float *part_ml, int *n_part, cudaStream_t st);
 int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
                     int max_pages, int B, int S, int pos0, int n_q, int n_kv, int hd, cudaStream_t st);
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st);

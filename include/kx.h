@@ -137,6 +137,25 @@ int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, 
                  void *stream);
 
 /*
+ * kx_attn_decode -- one decode step of attention over the paged KV cache, as the
+ * engine runs it: for sequence b the new token sits at position pos[b]; its q heads and k head are
+ * rotated (rope[pos][hd/2] = (cos, sin), rotate-half pairs), k and v are appended to the cache, and
+ * out[b, head, :] = softmax(q K^T / sqrt(hd)) V over keys 0 .. pos[b] (bf16 in/out, fp32 softmax).
+ *   d_qkv          [B, qkv_ld] bf16 rows laid out (q heads | k heads | v heads), not yet rotated
+ *   d_pages        [num_pages][2 (k, v)][n_kv][16 tokens][hd] bf16
+ *   d_block_table  [B (+1), max_pages]: page of tokens 16 i .. 16 i + 15 of each sequence
+ *   prefix_len     > 0: the first prefix_len keys (a multiple of 16, >= 64) of EVERY sequence are the
+ *                  same pages, listed in block-table row prefix_row; they are read once per 64 query
+ *                  rows instead of once per sequence (partials in library scratch, kx_release_scratch)
+ *   max_T          upper bound of pos[b] + 1 (sizes the shared-memory rounds)
+ * No reference counterpart (the reference calls a remote LLM, app.py:117).
+ */
+int kx_attn_decode(const void *d_qkv, int32_t qkv_ld, void *d_out, int32_t out_ld, void *d_pages,
+                   const int32_t *d_block_table, int32_t max_pages, const int32_t *d_pos, const float *d_rope,
+                   int32_t B, int32_t max_T, int32_t n_q, int32_t n_kv, int32_t hd, int32_t prefix_len,
+                   int32_t prefix_row, void *stream);
+
+/*
  * Generation engine: a decoder-only transformer (Llama / Qwen2 family) with a paged
  * bf16 KV cache, greedy decoding (temperature 0, app.py:109).  This is what
  * B200ChatModel (the occupant of the reference's `llm` slot, app.py:117-118) drives.

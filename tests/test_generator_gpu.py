@@ -129,6 +129,51 @@ def test_prefix_cached_kv_equals_full_prefill(arch):
     gen.close()
 
 
+@pytest.mark.parametrize("arch,B,P,S", [("tiny-llama-hd128", 40, 336, 20), ("tiny-qwen2", 70, 208, 9), ("tiny-llama", 2, 64, 5)])
+def test_shared_prefix_decode_attention(arch, B, P, S, monkeypatch):
+    """Decode over a prefix shared by the batch: the prefix K/V are reduced once per 64 query rows
+    (several row tiles, several chunks, a last chunk that is not a whole 64-key tile) and merged with each
+    sequence's own keys.  Against the oracle run on the full prompts the logits must be as close as those of
+    the engine that re-reads the prefix per sequence (KX_SHARED_PREFIX=0), and ids may differ from the
+    oracle's only where its top-2 margin is inside that noise."""
+    n_new = 5
+    g = torch.Generator().manual_seed(11)
+    results = {}
+    for shared in ("0", "1"):
+        monkeypatch.setenv("KX_SHARED_PREFIX", shared)
+        cfg, gen, ref_emu, _ = _setup(arch, 3, B, P + S, n_new)
+        if shared == "0":
+            prefix = torch.randint(0, cfg.vocab, (P,), generator=g)
+            suffix = torch.randint(0, cfg.vocab, (B, S), generator=g)
+        gen.set_prefix(prefix.numpy())
+        ids, logits = gen.generate_ids(suffix.numpy().astype(np.int32), n_new, want_logits=True)
+        ids_graph, _ = gen.generate_ids(suffix.numpy().astype(np.int32), n_new)
+        assert np.array_equal(ids, ids_graph)
+        results[shared] = (ids, [l.cpu() for l in logits])
+        gen.close()
+    full = torch.cat([prefix[None, :].expand(B, P), suffix], dim=1)
+    want_ids, want_logits = ref_emu.generate(full, n_new, return_logits=True)
+    worst = {}
+    for shared, (ids, logits) in results.items():
+        alive = np.ones(B, bool)
+        worst[shared] = 0.0
+        for t in range(n_new):
+            wl = want_logits[t]
+            scale = wl.abs().max().item()
+            noise = (logits[t][alive] - wl[alive]).abs().max().item()
+            worst[shared] = max(worst[shared], noise / scale)
+            top2 = wl.topk(2, dim=-1).values
+            margin = (top2[:, 0] - top2[:, 1]).numpy()
+            for b in np.flatnonzero(alive):
+                if ids[b, t] != want_ids[b, t].item():
+                    assert margin[b] <= 2 * noise, f"shared={shared} seq {b} step {t}: margin {margin[b]:.3e}, noise {noise:.3e}"
+                    alive[b] = False
+            if not alive.any():
+                break
+    print(f"{arch}: worst logit error vs oracle, per-sequence prefix {worst['0']:.2e}, shared prefix {worst['1']:.2e}")
+    assert worst["1"] <= 1e-2 and worst["1"] <= max(2 * worst["0"], 2e-3)
+
+
 def test_service_engine_learns_the_template_prefix():
     """B200Engine(auto_prefix=True): prompts that share a long instruction prefix are generated with
     that prefix prefilled once; the result must equal generation from the explicitly tokenised prompts."""
