@@ -79,8 +79,14 @@ int bn_index(int bn) { return bn == 32 ? 0 : bn == 64 ? 1 : 2; }
 int pick_splits(int features, int k, int b_tiles) {
     const int tiles = ((features + 127) / 128) * b_tiles;
     const int kb = (k + 63) / 64;
-    int s = 296 / tiles;                            // at most one wave of 2 CTAs per SM
-    if (s > 8) s = 8;                               // portable cluster size
+    // one wave at 2 CTAs per SM would be 296 CTAs, but clusters do not pack that tightly: measured
+    // (profiles/r01_sweep_decode_gemm.txt) the time jumps by ~50% once tiles * splits exceeds ~256
+    int s = 256 / tiles;
+    if (s > 8) {                                    // clusters above the portable size 8 (opt-in, up to 16) pack worse:
+        s = 192 / tiles;                            // they pay off only while tiles * splits stays below ~192
+        if (s > 16) s = 16;
+        if (s < 8) s = 8;
+    }
     if (s > kb) s = kb;
     if (s < 1) s = 1;
     return s;
@@ -142,7 +148,9 @@ int linear_pair_bn(const Linear &l, int M) {
     const int m_pairs = (M + 255) / 256;
     const int t256 = m_pairs * ((l.features + 255) / 256), t128 = m_pairs * ((l.features + 127) / 128);
     if ((l.features % 256 == 0 || l.features >= 2048) && t256 >= 64) return 256;
-    return t128 >= 24 ? 128 : 0;
+    // fewer 128-wide tiles than this leave most SMs idle: the weight-streaming kernel with split-K covers them
+    static const int min128 = [] { const char *v = getenv("KX_PAIR128_MIN_TILES"); return v ? atoi(v) : 24; }();
+    return t128 >= min128 ? 128 : 0;
 }
 
 int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st,

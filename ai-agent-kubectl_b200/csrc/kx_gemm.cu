@@ -341,6 +341,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    asm volatile("griddepcontrol.launch_dependents;");        // launched with programmatic serialization (see launch_pair)
     const int total_kb = (p.k + BK - 1) / BK;
     const int n_work = m_pairs * n_tiles;
 
@@ -362,15 +363,33 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (lane == 0) {
             const uint64_t pol_act = policy_evict_last(), pol_w = policy_evict_last();
             int it = 0;
+            // The grid may start while its predecessor (which produces the activations) drains: the first ring
+            // of weight half-tiles is requested before griddepcontrol.wait, the activation tiles after it.
+            int pre = 0;
+            if (cluster_id < n_work) {
+                const int mp = cluster_id / n_tiles, nt = cluster_id - mp * n_tiles;
+                const int n0 = nt * BN + (int)rank * (BN / 2);
+                pre = total_kb < C::STAGES ? total_kb : C::STAGES;
+                for (int i = 0; i < pre; ++i) {
+                    mbar_expect_tx(full + i, C::STAGE_BYTES);
+                    tma_load_2d_mcast(smem + i * C::STAGE_BYTES + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + i, i * BK, n0,
+                                      (uint16_t)3, pol_w);
+                }
+            }
+            asm volatile("griddepcontrol.wait;" ::: "memory");
             for (int wk = cluster_id; wk < n_work; wk += n_clusters) {
                 const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
                 const int m0 = (2 * mp + (int)rank) * BM, n0 = nt * BN + (int)rank * (BN / 2);
                 for (int i = 0; i < total_kb; ++i, ++it) {
                     const int s = it % C::STAGES;
+                    uint8_t *sa = smem + s * C::STAGE_BYTES;
+                    if (it < pre) {                                      // weights of this stage are already on their way
+                        tma_load_2d_hint(sa, &tmA, full + s, i * BK, m0, pol_act);
+                        continue;
+                    }
                     const uint32_t ph = (it / C::STAGES) & 1;
                     mbar_wait(empty + s, ph ^ 1);                       // both CTAs are done with this stage
                     mbar_expect_tx(full + s, C::STAGE_BYTES);
-                    uint8_t *sa = smem + s * C::STAGE_BYTES;
                     tma_load_2d_hint(sa, &tmA, full + s, i * BK, m0, pol_act);
                     tma_load_2d_mcast(sa + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + s, i * BK, n0, (uint16_t)3, pol_w);
                 }
@@ -402,6 +421,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     } else {
         const int q = warp & 3;
         int tile_it = 0;
+        asm volatile("griddepcontrol.wait;" ::: "memory");     // the epilogue reads / overwrites buffers earlier kernels used
         for (int wk = cluster_id; wk < n_work; wk += n_clusters, ++tile_it) {
             const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
             const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
@@ -466,9 +486,18 @@ int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams 
     const int m_pairs = (p.a_rows + 2 * BM - 1) / (2 * BM), n_tiles = (p.b_rows + BN - 1) / BN;
     int clusters = sms / 2;
     if (clusters > m_pairs * n_tiles) clusters = m_pairs * n_tiles;
-    kern<<<2 * clusters, kGemmThreads, Cfg2<BN>::SMEM_BYTES, st>>>(ta, tbh, p, m_pairs, n_tiles);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg2<BN>::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // prologue + first weight tiles overlap the predecessor's tail
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tbh, p, m_pairs, n_tiles));
     count_launch();
-    KX_CUDA(cudaGetLastError());
     return KX_OK;
 }
 
@@ -512,6 +541,8 @@ __device__ __forceinline__ void epilogue_swap_elem(const GemmParams &p, float v,
         reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] = v;
     }
 }
+
+constexpr int kMaxSplits = 16;   // cluster size: 8 is the portable limit, 16 needs the non-portable opt-in (see max_cluster_splits)
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 2)
@@ -612,17 +643,17 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         const int cols_per = (BN + S - 1) / S;
         const int j0 = z * cols_per, j1 = min(BN, j0 + cols_per);
         const uint32_t local = smem_u32(partial);
-        uint32_t peer[8];
+        uint32_t peer[kMaxSplits];
 #pragma unroll
-        for (int src = 0; src < 8; ++src) peer[src] = dsmem_addr(local, (uint32_t)(src < S ? src : 0));
+        for (int src = 0; src < kMaxSplits; ++src) peer[src] = dsmem_addr(local, (uint32_t)(src < S ? src : 0));
         auto column_sum = [&](int j) -> float {
-            float part[8];
+            float part[kMaxSplits];
 #pragma unroll
-            for (int src = 0; src < 8; ++src)                  // all remote loads in flight together
+            for (int src = 0; src < kMaxSplits; ++src)         // all remote loads in flight together
                 part[src] = src < S ? dsmem_ld_f32(peer[src] + (uint32_t)((j * BM + r) * 4)) : 0.f;
             float v = 0.f;
 #pragma unroll
-            for (int src = 0; src < 8; ++src) v += part[src];  // fixed order: deterministic sum
+            for (int src = 0; src < kMaxSplits; ++src) v += part[src];   // fixed order: deterministic sum
             return v;
         };
         if (EPI == EPI_RESID && p.tp_peer_recv) {
@@ -671,6 +702,7 @@ int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams
     static bool attr_set = false;
     if (!attr_set) {
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -797,7 +829,7 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.splits = splits;
     if (p.swap && (splits > 1 || p.tp_peer_recv)) {
         // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory
-        if (splits > 8) splits = 8;
+        if (splits > kMaxSplits) splits = kMaxSplits;
         p.kb_per_split = (total_kb + splits - 1) / splits;
         splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
         p.splits = splits;

@@ -196,6 +196,24 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
+// RoPE on 8 consecutive rotate-half pairs (d, d + half), d = 8 c .. 8 c + 7, of one head: 16-byte loads,
+// the same separately rounded products as rope_append_kernel (no FMA contraction).
+__device__ __forceinline__ void rope8(const __nv_bfloat16 *__restrict__ src, int half, const float2 *__restrict__ cs, int c,
+                                      uint4 &lo, uint4 &hi) {
+    const uint4 a = *reinterpret_cast<const uint4 *>(src + c * 8), b = *reinterpret_cast<const uint4 *>(src + half + c * 8);
+    const __nv_bfloat162 *ah = reinterpret_cast<const __nv_bfloat162 *>(&a), *bh = reinterpret_cast<const __nv_bfloat162 *>(&b);
+    uint32_t o1[4], o2[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const float4 cc = *reinterpret_cast<const float4 *>(cs + c * 8 + 2 * t);     // (cos, sin) of two dims
+        const float x1a = __low2float(ah[t]), x1b = __high2float(ah[t]), x2a = __low2float(bh[t]), x2b = __high2float(bh[t]);
+        o1[t] = pack2(__fsub_rn(__fmul_rn(x1a, cc.x), __fmul_rn(x2a, cc.y)), __fsub_rn(__fmul_rn(x1b, cc.z), __fmul_rn(x2b, cc.w)));
+        o2[t] = pack2(__fadd_rn(__fmul_rn(x2a, cc.x), __fmul_rn(x1a, cc.y)), __fadd_rn(__fmul_rn(x2b, cc.z), __fmul_rn(x1b, cc.w)));
+    }
+    lo = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+    hi = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+}
+
 template <int HD>
 __device__ __forceinline__ uint32_t swz(int row, int chunk) {       // byte offset of a 16 B chunk
     return (uint32_t)(row * HD * 2 + ((chunk ^ (row & 7)) << 4));
@@ -392,22 +410,24 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         const float2 *cs = rope + (size_t)p * HALF;
         __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
         __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
-        for (int i = tid; i < (G + 1) * HALF; i += (NW * 32)) {
-            const int h = i / HALF, d = i - h * HALF;
+        for (int i = tid; i < (G + 1) * (HALF / 8); i += (NW * 32)) {
+            const int h = i / (HALF / 8), c = i - h * (HALF / 8);
             const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
-            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
-            const float2 c = cs[d];
-            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
-            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            uint4 lo, hi;
+            rope8(src, HALF, cs, c, lo, hi);
             if (h < G) {
-                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, d >> 3) + (d & 7) * 2) = o1;
-                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c)) = lo;
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c + HALF / 8)) = hi;
             } else {
-                kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2;
+                reinterpret_cast<uint4 *>(kdst)[c] = lo; reinterpret_cast<uint4 *>(kdst)[c + HALF / 8] = hi;
+                reinterpret_cast<uint4 *>(knew)[c] = lo; reinterpret_cast<uint4 *>(knew)[c + HALF / 8] = hi;
             }
         }
         const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
-        for (int i = tid; i < HD; i += (NW * 32)) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
+        for (int i = tid; i < CH; i += (NW * 32)) {
+            const uint4 x = reinterpret_cast<const uint4 *>(vsrc)[i];
+            reinterpret_cast<uint4 *>(vdst)[i] = x; reinterpret_cast<uint4 *>(vnew)[i] = x;
+        }
         for (int i = tid; i < (16 - G) * CH; i += (NW * 32))          // padding rows of the Q tile
             *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
     }
@@ -618,22 +638,24 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
         const float2 *cs = rope + (size_t)p * HALF;
         __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
         __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
-        for (int i = lane; i < (G + 1) * HALF; i += 32) {
-            const int h = i / HALF, d = i - h * HALF;
+        for (int i = lane; i < (G + 1) * (HALF / 8); i += 32) {
+            const int h = i / (HALF / 8), c = i - h * (HALF / 8);
             const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
-            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
-            const float2 c = cs[d];
-            const __nv_bfloat16 o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
-            const __nv_bfloat16 o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            uint4 lo, hi;
+            rope8(src, HALF, cs, c, lo, hi);
             if (h < G) {
-                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, d >> 3) + (d & 7) * 2) = o1;
-                *reinterpret_cast<__nv_bfloat16 *>(Qs + swz<HD>(h, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c)) = lo;
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c + HALF / 8)) = hi;
             } else {
-                kdst[d] = o1; kdst[d + HALF] = o2; knew[d] = o1; knew[d + HALF] = o2;
+                reinterpret_cast<uint4 *>(kdst)[c] = lo; reinterpret_cast<uint4 *>(kdst)[c + HALF / 8] = hi;
+                reinterpret_cast<uint4 *>(knew)[c] = lo; reinterpret_cast<uint4 *>(knew)[c + HALF / 8] = hi;
             }
         }
         const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
-        for (int i = lane; i < HD; i += 32) { const __nv_bfloat16 x = vsrc[i]; vdst[i] = x; vnew[i] = x; }
+        for (int i = lane; i < CH; i += 32) {
+            const uint4 x = reinterpret_cast<const uint4 *>(vsrc)[i];
+            reinterpret_cast<uint4 *>(vdst)[i] = x; reinterpret_cast<uint4 *>(vnew)[i] = x;
+        }
         for (int i = lane; i < (16 - G) * CH; i += 32)
             *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
     }
@@ -800,20 +822,16 @@ attn_prefix_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, const __nv
     fetch_kv(0);
     cp_async_commit();
     asm volatile("griddepcontrol.wait;" ::: "memory");   // q comes from the QKV GEMM
-    for (int i = tid; i < 64 * HALF; i += 128) {          // rotated q rows -> Q tile (rows past B G are zero)
-        const int r = i / HALF, d = i - r * HALF;
+    for (int i = tid; i < 64 * (HALF / 8); i += 128) {    // rotated q rows -> Q tile (rows past B G are zero)
+        const int r = i / (HALF / 8), c = i - r * (HALF / 8);
         const int row = rt * 64 + r;
-        __nv_bfloat16 o1 = __float2bfloat16(0.f), o2 = o1;
+        uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
         if (row < rows) {
             const int b = row / G, g = row - b * G;
-            const __nv_bfloat16 *src = qkv + (size_t)b * qkv_ld + (size_t)(kvh * G + g) * HD;
-            const float x1 = __bfloat162float(src[d]), x2 = __bfloat162float(src[d + HALF]);
-            const float2 c = rope[(size_t)pos[b] * HALF + d];
-            o1 = __float2bfloat16(__fsub_rn(__fmul_rn(x1, c.x), __fmul_rn(x2, c.y)));
-            o2 = __float2bfloat16(__fadd_rn(__fmul_rn(x2, c.x), __fmul_rn(x1, c.y)));
+            rope8(qkv + (size_t)b * qkv_ld + (size_t)(kvh * G + g) * HD, HALF, rope + (size_t)pos[b] * HALF, c, lo, hi);
         }
-        *reinterpret_cast<__nv_bfloat16 *>(smem_attn + swz<HD>(r, d >> 3) + (d & 7) * 2) = o1;
-        *reinterpret_cast<__nv_bfloat16 *>(smem_attn + swz<HD>(r, (d + HALF) >> 3) + ((d + HALF) & 7) * 2) = o2;
+        *reinterpret_cast<uint4 *>(smem_attn + swz<HD>(r, c)) = lo;
+        *reinterpret_cast<uint4 *>(smem_attn + swz<HD>(r, c + HALF / 8)) = hi;
     }
 
     uint32_t qf[HD / 16][4];
@@ -1143,11 +1161,11 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     return KX_OK;
 }
 
-// chunks the shared prefix is cut into for a batch of B: enough CTAs for two per SM, 64-key granularity
+// chunks the shared prefix is cut into for a batch of B: enough CTAs for one per SM, 64-key granularity
 int attn_prefix_parts(int B, int n_q, int n_kv, int P, int *chunk_keys) {
     const int G = n_q / n_kv;
     const int tiles = n_kv * ((B * G + 63) / 64);
-    int nc = (296 + tiles - 1) / tiles;
+    int nc = (148 + tiles - 1) / tiles;               // about one CTA per SM: the kernel is latency-, not bandwidth-bound
     if (nc > 16) nc = 16;
     const int blocks = (P + 63) / 64;
     if (nc > blocks) nc = blocks;
