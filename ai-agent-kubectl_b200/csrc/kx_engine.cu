@@ -13,6 +13,7 @@
 #include "kx_common.cuh"
 #include "kx_gemm.cuh"
 #include "kx_ops.cuh"
+#include "kx_mega.cuh"
 
 using namespace kx;
 
@@ -58,6 +59,18 @@ struct kx_engine {
     void *comm = nullptr;
     int (*allreduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
     int (*allgather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    // persistent decode kernel (small batches, no tensor parallelism): weight maps / per-layer pointers on the
+    // device, the split-K plan, partial-sum scratch and the grid barrier counter
+    bool mega = false;
+    int mega_grid = 0, mega_max_b = 0;
+    MegaGemm mega_g[4];
+    CUtensorMap *mega_wmaps = nullptr;
+    MegaLayer *mega_layers = nullptr;
+    float *mega_part_qkv = nullptr, *mega_part_o = nullptr, *mega_part_d = nullptr;
+    uint32_t *mega_bar = nullptr;
+    uint64_t *mega_trace = nullptr;                // KX_MEGA_TRACE=1: phase timestamps of CTA 0 (kx_engine_mega_trace)
+    int mega_trace_cap = 0;
+    int64_t mega_launches = 0;
     int64_t device_bytes = 0;
     std::vector<void *> owned;
 };
@@ -232,6 +245,26 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     return KX_OK;
 }
 
+// all layers of one decode step in the persistent kernel (kx_decode_mega.cu)
+int decode_layers_mega(kx_engine *e, int B, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    const int bn = mega_bn(B), bi = bn_index(bn);
+    MegaParams p{};
+    p.wmaps = e->mega_wmaps; p.layers_ptr = e->mega_layers;
+    for (int g = 0; g < 4; ++g) p.g[g] = e->mega_g[g];
+    p.resid = e->resid; p.xn = e->xn; p.attn = e->attn; p.mlp = e->mlp;
+    p.part_qkv = e->mega_part_qkv; p.part_o = e->mega_part_o; p.part_d = e->mega_part_d;
+    p.pos = e->pos; p.block_table = e->block_table; p.rope = reinterpret_cast<const float2 *>(e->rope);
+    p.bar = e->mega_bar;
+    p.trace = e->mega_trace; p.trace_cap = e->mega_trace_cap;
+    p.layers = d.layers; p.B = B; p.hidden = d.hidden; p.qkv_dim = e->qkv_dim; p.q_dim = e->q_dim;
+    p.n_q = d.n_q; p.n_kv = d.n_kv; p.max_pages = e->max_pages;
+    p.eps = d.eps;
+    p.scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
+    ++e->mega_launches;
+    return mega_launch(e->xn_b[bi], e->attn_b[bi], e->mlp_b[bi], p, bn, d.head_dim, e->mega_grid, st);
+}
+
 // greedy token per sequence from e->logits (this rank's vocabulary shard under tensor parallelism)
 int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
     const kx_model_desc &d = e->d;
@@ -353,6 +386,48 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&e->attn_b[j], e->attn, Mx, e->q_dim, e->q_dim, bns[j]));
         KX_E(make_tmap_bf16_2d(&e->mlp_b[j], e->mlp, Mx, d.inter, d.inter, bns[j]));
     }
+    // persistent decode kernel: single GPU replicas only (the tensor-parallel epilogue lives in the cluster GEMM)
+    {
+        // Opt-in (KX_MEGA=1): measured on B200 it does not beat the per-layer kernels yet (decode section)
+        const char *v = getenv("KX_MEGA");
+        const bool want = v && v[0] == '1';
+        if (want && d.tp_size <= 1 && mega_supported(d.head_dim, d.n_q / d.n_kv, d.hidden)) {
+            int dev = 0, sms = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+                return fail(KX_ECUDA);
+            e->mega_grid = sms;
+            e->mega_max_b = d.max_batch < 128 ? d.max_batch : 128;
+            e->mega_g[0] = mega_plan_gemm(e->qkv_dim, d.hidden, sms, true);
+            e->mega_g[1] = mega_plan_gemm(d.hidden, e->q_dim, sms, true);
+            e->mega_g[2] = mega_plan_gemm(2 * d.inter, d.hidden, sms, false);   // SwiGLU in the epilogue needs whole sums
+            e->mega_g[3] = mega_plan_gemm(d.hidden, d.inter, sms, true);
+            const size_t mb = (size_t)e->mega_max_b;
+            KX_E(dev_alloc(e, (void **)&e->mega_part_qkv, (size_t)e->mega_g[0].splits * mb * e->qkv_dim * 4));
+            KX_E(dev_alloc(e, (void **)&e->mega_part_o, (size_t)e->mega_g[1].splits * mb * d.hidden * 4));
+            KX_E(dev_alloc(e, (void **)&e->mega_part_d, (size_t)e->mega_g[3].splits * mb * d.hidden * 4));
+            KX_E(dev_alloc(e, (void **)&e->mega_bar, sizeof(uint32_t) * 7 * (size_t)d.layers + 256));
+            if (const char *t = getenv("KX_MEGA_TRACE")) {
+                if (t[0] == '1') {
+                    e->mega_trace_cap = 16 * d.layers + 16;
+                    KX_E(dev_alloc(e, (void **)&e->mega_trace, sizeof(uint64_t) * 2 * e->mega_trace_cap));
+                    if (cudaMemset(e->mega_trace, 0, sizeof(uint64_t) * 2 * e->mega_trace_cap) != cudaSuccess) return fail(KX_ECUDA);
+                }
+            }
+            KX_E(dev_alloc(e, (void **)&e->mega_wmaps, sizeof(CUtensorMap) * 4 * d.layers));
+            KX_E(dev_alloc(e, (void **)&e->mega_layers, sizeof(MegaLayer) * d.layers));
+            std::vector<CUtensorMap> maps((size_t)4 * d.layers);
+            std::vector<MegaLayer> lp(d.layers);
+            for (int i = 0; i < d.layers; ++i) {
+                const LayerPlan &L = e->layers[i];
+                maps[4 * i + 0] = L.wqkv; maps[4 * i + 1] = L.wo; maps[4 * i + 2] = L.wgu; maps[4 * i + 3] = L.wd;
+                lp[i].ln1 = L.w.ln1; lp[i].ln2 = L.w.ln2; lp[i].bqkv = L.w.bqkv; lp[i].kv_pages = L.kv_pages;
+            }
+            if (cudaMemcpy(e->mega_wmaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice) != cudaSuccess ||
+                cudaMemcpy(e->mega_layers, lp.data(), lp.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice) != cudaSuccess)
+                return fail(KX_ECUDA);
+            e->mega = true;
+        }
+    }
 #undef KX_E
     *out = e;
     return KX_OK;
@@ -456,6 +531,17 @@ extern "C" void kx_engine_destroy(kx_engine *e) {
 
 extern "C" int64_t kx_engine_device_bytes(const kx_engine *e) { return e ? e->device_bytes : 0; }
 
+extern "C" int64_t kx_engine_mega_launches(const kx_engine *e) { return e ? e->mega_launches : 0; }
+
+extern "C" int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max_pairs) {
+    KX_REQUIRE(e && h_pairs, KX_EINVAL, "kx_engine_mega_trace: NULL argument");
+    if (!e->mega_trace) return 0;
+    const int n = max_pairs < e->mega_trace_cap ? max_pairs : e->mega_trace_cap;
+    KX_CUDA(cudaStreamSynchronize(e->stream));
+    KX_CUDA(cudaMemcpy(h_pairs, e->mega_trace, sizeof(uint64_t) * 2 * n, cudaMemcpyDeviceToHost));
+    return n;
+}
+
 extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t B, int32_t S, int32_t n_new,
                                   int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream) {
     KX_REQUIRE(e && h_tokens && h_out, KX_EINVAL, "kx_engine_generate: NULL argument");
@@ -524,7 +610,12 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);
         count_launch();
         KX_TRY(op_embed(e->next_tok, e->embed, e->resid, B, d.hidden, st));
-        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, max_T, st));
+        const bool shared_prefix = e->share_prefix && e->prefix_len >= 64 && B >= 2 && e->prefix_o;
+        if (e->mega && B <= e->mega_max_b && !shared_prefix) {
+            KX_TRY(decode_layers_mega(e, B, st));
+        } else {
+            for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, max_T, st));
+        }
         KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st));
         return KX_OK;
     };

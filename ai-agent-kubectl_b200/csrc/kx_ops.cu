@@ -12,12 +12,13 @@
 #include "kx_common.cuh"
 #include "kx_ops.cuh"
 #include "kx_sm100.cuh"
+#include "kx_attn.cuh"
 
 namespace kx {
 
 namespace {
 
-constexpr int kPage = KX_KV_PAGE;
+using namespace attn;
 
 // Launch with programmatic stream serialization: the grid may start while its predecessor drains;
 // the kernel itself calls griddepcontrol.wait before it touches the predecessor's output.
@@ -171,54 +172,6 @@ __global__ void rope_append_kernel(__nv_bfloat16 *__restrict__ qkv, int qkv_ld, 
 // grid (ceil(S/64), n_q, B), 128 threads; warp w owns query rows 16w .. 16w+15 of the
 // 64-row block.  QK^T and PV run on tensor cores (mma.sync m16n8k16 bf16, fp32 acc) with
 // the online softmax in fp32 registers.
-__device__ __forceinline__ void cp_async16_zfill(uint32_t smem_dst, const void *src, bool valid) {
-    const int n = valid ? 16 : 0;                     // src-size 0: the 16 destination bytes are zero-filled
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(src), "r"(n) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ uint32_t pack2(float a, float b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t *>(&h);
-}
-
-// RoPE on 8 consecutive rotate-half pairs (d, d + half), d = 8 c .. 8 c + 7, of one head: 16-byte loads,
-// the same separately rounded products as rope_append_kernel (no FMA contraction).
-__device__ __forceinline__ void rope8(const __nv_bfloat16 *__restrict__ src, int half, const float2 *__restrict__ cs, int c,
-                                      uint4 &lo, uint4 &hi) {
-    const uint4 a = *reinterpret_cast<const uint4 *>(src + c * 8), b = *reinterpret_cast<const uint4 *>(src + half + c * 8);
-    const __nv_bfloat162 *ah = reinterpret_cast<const __nv_bfloat162 *>(&a), *bh = reinterpret_cast<const __nv_bfloat162 *>(&b);
-    uint32_t o1[4], o2[4];
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-        const float4 cc = *reinterpret_cast<const float4 *>(cs + c * 8 + 2 * t);     // (cos, sin) of two dims
-        const float x1a = __low2float(ah[t]), x1b = __high2float(ah[t]), x2a = __low2float(bh[t]), x2b = __high2float(bh[t]);
-        o1[t] = pack2(__fsub_rn(__fmul_rn(x1a, cc.x), __fmul_rn(x2a, cc.y)), __fsub_rn(__fmul_rn(x1b, cc.z), __fmul_rn(x2b, cc.w)));
-        o2[t] = pack2(__fadd_rn(__fmul_rn(x2a, cc.x), __fmul_rn(x1a, cc.y)), __fadd_rn(__fmul_rn(x2b, cc.z), __fmul_rn(x1b, cc.w)));
-    }
-    lo = make_uint4(o1[0], o1[1], o1[2], o1[3]);
-    hi = make_uint4(o2[0], o2[1], o2[2], o2[3]);
-}
-
-template <int HD>
-__device__ __forceinline__ uint32_t swz(int row, int chunk) {       // byte offset of a 16 B chunk
-    return (uint32_t)(row * HD * 2 + ((chunk ^ (row & 7)) << 4));
-}
-
 template <int HD>
 __global__ void __launch_bounds__(128)
 attn_prefill_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
@@ -368,13 +321,6 @@ attn_prefill_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bflo
 // 256 keys per round; each warp owns a 64-key block of the round with its own online
 // softmax state and the four partial results are merged at the end (flash decoding
 // inside the CTA).
-__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
-}
-
 // NW warps x 64 keys per round: 8 warps hold a whole <= 512-key context in one round (few CTAs, latency
 // matters); 4 warps / 256-key rounds keep three CTAs per SM resident (many CTAs, bandwidth matters)
 
@@ -596,37 +542,21 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
                         int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part, int n_tasks) {
     extern __shared__ __align__(128) uint8_t smem_dw[];
     asm volatile("griddepcontrol.launch_dependents;");
+    using W = WarpAttnSmem<HD, KB, NS>;
     constexpr int CH = HD / 8, HALF = HD / 2;
-    constexpr int QT = 16 * HD * 2, ST = KB * HD * 2, NEWB = 2 * HD * 2;
-    constexpr int WARP_BYTES = QT + NS * 2 * ST + NEWB;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int task = blockIdx.x * 4 + warp;
     const bool live = task < n_tasks;
     const int b = live ? task / n_kv : 0, kvh = live ? task - b * n_kv : 0;
-    uint8_t *Qs = smem_dw + warp * WARP_BYTES;
-    const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ring_u = qs_u + QT;
-    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Qs + QT + NS * 2 * ST), *vnew = knew + HD;
+    uint8_t *Qs = smem_dw + warp * W::BYTES;
+    const uint32_t ring_u = (uint32_t)__cvta_generic_to_shared(Qs) + W::QT;
+    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Qs + W::QT + NS * 2 * W::ST), *vnew = knew + HD;
     const int p = pos[b], T = p + 1;
     const int *bt = block_table + (size_t)b * max_pages;
     const int nblk = live ? (T - key0 + KB - 1) / KB : 0;
-
-    auto fetch = [&](int blk) {                       // keys key0 + blk KB ... into stage blk % NS
-        const uint32_t kdst = ring_u + (uint32_t)(blk % NS) * 2 * ST, vdst = kdst + ST;
-        const int c0 = key0 + blk * KB;
-#pragma unroll
-        for (int i = lane; i < KB * CH; i += 32) {
-            const int r = i / CH, c = i - r * CH;
-            const int t = c0 + r;
-            const bool ok = t < T;
-            const int tt = ok ? t : p;
-            const __nv_bfloat16 *kp = pages + (((size_t)bt[tt / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(tt % kPage) * HD + c * 8;
-            cp_async16_zfill(kdst + swz<HD>(r, c), kp, ok);
-            cp_async16_zfill(vdst + swz<HD>(r, c), kp + (size_t)n_kv * kPage * HD, ok);
-        }
-    };
 #pragma unroll
     for (int i = 0; i < NS - 1; ++i) {                // prologue: NS-1 stages in flight (empty groups keep the count uniform)
-        if (i < nblk) fetch(i);
+        if (i < nblk) warp_attn_fetch<HD, KB, NS>(ring_u, i, key0, T, p, pages, bt, n_kv, kvh, lane);
         cp_async_commit();
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");   // qkv comes from the predecessor
@@ -660,127 +590,9 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
             *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
     }
     __syncwarp();
-    uint32_t qf[HD / 16][4];
-#pragma unroll
-    for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], qs_u + swz<HD>(lane & 15, 2 * ks + (lane >> 4)));
-
-    float o[HD / 8][4];
-#pragma unroll
-    for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
-    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
-    const int g = lane >> 2, tq = lane & 3;
-
-    for (int blk = 0; blk < nblk; ++blk) {
-        if (blk + NS - 1 < nblk) fetch(blk + NS - 1);
-        cp_async_commit();
-        cp_async_wait<NS - 1>();                      // block blk has landed (for this lane)
-        __syncwarp();                                 // ... and for the whole warp
-        const uint32_t ks_u = ring_u + (uint32_t)(blk % NS) * 2 * ST, vs_u = ks_u + ST;
-        const int c0 = key0 + blk * KB;
-        const int n = min(T - c0, KB);
-        if (blk == nblk - 1) {                        // the new token's row comes from this warp, not from the copy
-            if (lane < CH) {
-                uint8_t *ring = Qs + QT + (blk % NS) * 2 * ST;
-                *reinterpret_cast<uint4 *>(ring + swz<HD>(p - c0, lane)) = reinterpret_cast<const uint4 *>(knew)[lane];
-                *reinterpret_cast<uint4 *>(ring + ST + swz<HD>(p - c0, lane)) = reinterpret_cast<const uint4 *>(vnew)[lane];
-            }
-            __syncwarp();
-        }
-        float s[KB / 8][4];
-#pragma unroll
-        for (int j = 0; j < KB / 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
-#pragma unroll
-        for (int ks = 0; ks < HD / 16; ++ks) {
-#pragma unroll
-            for (int jp = 0; jp < KB / 16; ++jp) {
-                uint32_t kf[4];
-                ldsm_x4(kf, ks_u + swz<HD>(jp * 16 + (lane & 7) + ((lane >> 4) << 3), 2 * ks + ((lane >> 3) & 1)));
-                mma_bf16(s[2 * jp], qf[ks], kf[0], kf[1]);
-                mma_bf16(s[2 * jp + 1], qf[ks], kf[2], kf[3]);
-            }
-        }
-        float mx[2] = {mrow[0], mrow[1]};
-#pragma unroll
-        for (int j = 0; j < KB / 8; ++j) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                if (j * 8 + 2 * tq + (e & 1) >= n) s[j][e] = -INFINITY;
-                mx[e >> 1] = fmaxf(mx[e >> 1], s[j][e]);
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
-            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
-        }
-        float corr[2], msc[2];
-#pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            corr[r] = exp2f((mrow[r] - mx[r]) * scale_log2);
-            mrow[r] = mx[r];
-            msc[r] = mx[r] * scale_log2;
-            lrow[r] *= corr[r];
-        }
-#pragma unroll
-        for (int j = 0; j < HD / 8; ++j) { o[j][0] *= corr[0]; o[j][1] *= corr[0]; o[j][2] *= corr[1]; o[j][3] *= corr[1]; }
-        uint32_t pf[KB / 16][4];
-#pragma unroll
-        for (int j = 0; j < KB / 8; ++j) {
-            const float p0 = exp2f(s[j][0] * scale_log2 - msc[0]), p1 = exp2f(s[j][1] * scale_log2 - msc[0]);
-            const float p2 = exp2f(s[j][2] * scale_log2 - msc[1]), p3 = exp2f(s[j][3] * scale_log2 - msc[1]);
-            lrow[0] += p0 + p1;
-            lrow[1] += p2 + p3;
-            pf[j >> 1][(j & 1) * 2] = pack2(p0, p1);
-            pf[j >> 1][(j & 1) * 2 + 1] = pack2(p2, p3);
-        }
-#pragma unroll
-        for (int kk = 0; kk < KB / 16; ++kk) {
-#pragma unroll
-            for (int dp = 0; dp < HD / 16; ++dp) {
-                uint32_t vf[4];
-                ldsm_x4_t(vf, vs_u + swz<HD>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), 2 * dp + (lane >> 4)));
-                mma_bf16(o[2 * dp], pf[kk], vf[0], vf[1]);
-                mma_bf16(o[2 * dp + 1], pf[kk], vf[2], vf[3]);
-            }
-        }
-        __syncwarp();                                 // every lane is done with this stage before it is refilled
-    }
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
-        lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 2);
-    }
-    // merge with the shared-prefix partials (if any), normalise, store the G real rows
-    const size_t part_rows = (size_t)(n_tasks / n_kv) * n_q;
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-        const int h = g + 8 * r;
-        if (h >= G) continue;
-        const size_t prow = (size_t)b * n_q + kvh * G + h;
-        float M = mrow[r];
-        for (int c = 0; c < n_part; ++c) M = fmaxf(M, part_ml[(c * part_rows + prow) * 2]);
-        const float fs = exp2f((mrow[r] - M) * scale_log2);
-        float den = fs * lrow[r];
-        float acc[HD / 8][2];
-#pragma unroll
-        for (int j = 0; j < HD / 8; ++j) { acc[j][0] = fs * o[j][2 * r]; acc[j][1] = fs * o[j][2 * r + 1]; }
-        for (int c = 0; c < n_part; ++c) {
-            const float2 ml = *reinterpret_cast<const float2 *>(part_ml + (c * part_rows + prow) * 2);
-            const float f = exp2f((ml.x - M) * scale_log2);
-            den += f * ml.y;
-            const float *po = part_o + (c * part_rows + prow) * HD + 2 * tq;
-#pragma unroll
-            for (int j = 0; j < HD / 8; ++j) {
-                const float2 v = *reinterpret_cast<const float2 *>(po + j * 8);
-                acc[j][0] += f * v.x; acc[j][1] += f * v.y;
-            }
-        }
-        const float inv = 1.0f / den;
-        __nv_bfloat16 *orow = out + (size_t)b * out_ld + (size_t)(kvh * G + h) * HD + 2 * tq;
-#pragma unroll
-        for (int j = 0; j < HD / 8; ++j)
-            *reinterpret_cast<uint32_t *>(orow + j * 8) = pack2(acc[j][0] * inv, acc[j][1] * inv);
-    }
+    warp_attn_main<HD, G, KB, NS>(Qs, nblk, key0, T, p, pages, bt, n_kv, kvh, lane, scale_log2,
+                                  out + (size_t)b * out_ld + (size_t)kvh * G * HD, part_o, part_ml, n_part,
+                                  (size_t)(n_tasks / n_kv) * n_q, (size_t)b * n_q + kvh * G);
 }
 
 // ---- decode attention over a prefix shared by the whole batch ("read the prefix once") ----

@@ -45,6 +45,8 @@ _lib.declare("kx_engine_set_collectives", ctypes.c_int, [c_void_p, c_void_p, c_v
 _lib.declare("kx_engine_p2p_export", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_import", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_launches", ctypes.c_int64, [c_void_p])
+_lib.declare("kx_engine_mega_launches", ctypes.c_int64, [c_void_p])
+_lib.declare("kx_engine_mega_trace", ctypes.c_int, [c_void_p, c_void_p, ctypes.c_int])
 _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
@@ -184,6 +186,18 @@ class Generator:
 
     def p2p_launches(self) -> int:
         return int(_lib.lib().kx_engine_p2p_launches(self._h))
+
+    def mega_launches(self) -> int:
+        """Decode steps enqueued as the single persistent kernel so far."""
+        return int(_lib.lib().kx_engine_mega_launches(self._h))
+
+    def mega_trace(self, max_pairs: int = 1024):
+        """Diagnostic (KX_MEGA_TRACE=1): [(tag, ns)] recorded by CTA 0 of the persistent kernel in the last step."""
+        buf = np.zeros((max_pairs, 2), np.uint64)
+        n = _lib.lib().kx_engine_mega_trace(self._h, buf.ctypes.data, max_pairs)
+        if n < 0:
+            _lib.check(n)
+        return [(int(t), int(ns)) for t, ns in buf[:n] if ns]
 
     def device_bytes(self) -> int:
         return int(_lib.lib().kx_engine_device_bytes(self._h))

@@ -547,8 +547,11 @@ def run_reference_generate(args):
 
 
 def main():
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: one JSON line only
+    # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) are sent to
+    # stderr by pointing fd 1 at fd 2 for the run, and the line goes out through a saved copy of the real fd 1
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=0, help="0 = workload default")
@@ -573,7 +576,8 @@ def main():
     else:
         line = run_reference(args) if args.impl == "reference" else run_validate_hash(args)
     if line is not None:
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        print(json.dumps(line), file=real_stdout, flush=True)
     _, _, world = dist_env()
     if world > 1 and args.impl != "reference":
         import torch.distributed as dist

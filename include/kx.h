@@ -229,6 +229,20 @@ int kx_engine_p2p_import(kx_engine *e, const void *peer_handles);
 int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the fused all-reduce so far */
 
 /*
+ * Experimental, opt-in with KX_MEGA=1 in the environment when the engine is created: decode steps of
+ * at most 128 sequences on a single-GPU replica run all layers in ONE persistent kernel (weights keep
+ * streaming through the phase barriers; see csrc/kx_decode_mega.cu).  Parity-tested, but on B200 it
+ * is not yet faster than the per-layer kernels, which stay the default.  Returns how many steps were
+ * enqueued that way so far (0: the per-layer kernels were used).
+ */
+int64_t kx_engine_mega_launches(const kx_engine *e);
+/* Diagnostic: with KX_MEGA_TRACE=1 in the environment at creation, CTA 0 of the persistent kernel records
+ * (tag, globaltimer ns) pairs at its phase barriers (tag = 2 * phase on arrival, 2 * phase + 1 when the wait
+ * for that phase returned, 0xffffffff at kernel start); copies up to max_pairs pairs of the LAST step to
+ * h_pairs and returns how many slots were copied (0 when tracing is off). */
+int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max_pairs);
+
+/*
  * kx_engine_set_prefix -- prefill `n` tokens (a multiple of 16; host int32) ONCE and keep their
  * KV pages; every later kx_engine_generate treats its prompts as continuing that prefix
  * (positions start at n, the pages are shared by all sequences through the block table).
