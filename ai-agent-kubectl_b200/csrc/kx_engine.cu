@@ -61,6 +61,13 @@ struct kx_engine {
     int (*allgather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
     // persistent decode kernel (small batches, no tensor parallelism): weight maps / per-layer pointers on the
     // device, the split-K plan, partial-sum scratch and the grid barrier counter
+    // wide decode batches (256 < M <= 512): the row-parallel projections run as split-K token-major GEMMs that
+    // leave per-slice partial sums here; the RMSNorm that follows adds them to the residual (pend_* describe them)
+    float *splitk_part = nullptr;
+    size_t splitk_cap = 0;                         // floats
+    const float *pend_part = nullptr;
+    int pend_splits = 0;
+    size_t pend_stride = 0;
     bool mega = false;
     int mega_grid = 0, mega_max_b = 0;
     MegaGemm mega_g[4];
@@ -124,12 +131,13 @@ struct GemmCall {
     int pair_bn = 0;                               // ... and its tile width (128 or 256)
     const GemmParams *extra = nullptr;             // EPI_QKV_ROPE: the rope / cache fields
     bool tp_fused = false;                         // EPI_RESID + all-reduce over peer memory in the epilogue
+    size_t split_stride = 0;                       // pair kernel with splits > 1: distance between the slices' outputs
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     GemmParams p{};
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
-    p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits;
+    p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits; p.split_stride = c.split_stride;
     if (c.extra) {
         p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
         p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
@@ -178,10 +186,33 @@ int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, co
                         out, ldo, bias}, st);
 }
 
+// RMSNorm of the residual rows; folds in (and clears) split-K partials a preceding projection left pending
+int norm_rows(kx_engine *e, const void *g, int M, const int *row_map, cudaStream_t st) {
+    const int rc = op_rmsnorm(e->resid, g, e->xn, M, e->d.hidden, e->d.eps, row_map, st, e->pend_part, e->pend_splits, e->pend_stride);
+    e->pend_part = nullptr; e->pend_splits = 0; e->pend_stride = 0;
+    return rc;
+}
+
 // Row-parallel linear layer whose result is added to the residual stream.  With tensor
 // parallelism every rank holds a partial sum: it goes to tp_buf, is all-reduced, then added.
-int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st) {
+int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool decode) {
     const kx_model_desc &d = e->d;
+    if (d.tp_size <= 1 && decode && M > 256 && M <= 512 && d.hidden % 256 == 0 && e->splitk_part) {
+        // 2 x (hidden / 256) tiles of 256 x 256 would use a fraction of the SMs: cut k so that ~64 CTA pairs work,
+        // slices land in splitk_part and the next RMSNorm adds them to the residual
+        const int tiles = ((M + 255) / 256) * (d.hidden / 256);
+        int S = 74 / tiles;
+        const int kb = (l.k + 63) / 64;
+        if (S > 8) S = 8;
+        if (S > kb / 4) S = kb / 4;
+        if (S >= 2 && (size_t)S * M * d.hidden <= e->splitk_cap) {
+            GemmCall c{l.x_a, l.w_full, M, l.features, l.k, EPI_F32, 0, S, 128, e->splitk_part, d.hidden, nullptr, l.w_half + 1, 256};
+            c.split_stride = (size_t)M * d.hidden;
+            KX_TRY(run_gemm(e, c, st));
+            e->pend_part = e->splitk_part; e->pend_splits = S; e->pend_stride = c.split_stride;
+            return KX_OK;
+        }
+    }
     if (d.tp_size <= 1) return linear(e, l, M, EPI_RESID, e->resid, d.hidden, nullptr, st);
     if (d.tp_size == 2 && e->p2p_peer_recv && M <= e->p2p_rows && M < 256 && linear_pair_bn(l, M) == 0) {
         // decode: the swap-AB cluster GEMM reduces across the two ranks itself, over NVLink peer memory
@@ -208,7 +239,7 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     const Linear wo{&L.wo, L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim};
     const Linear wgu{&L.wgu, L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
     const Linear wd{&L.wd, L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
-    KX_TRY(op_rmsnorm(e->resid, L.w.ln1, e->xn, M, d.hidden, d.eps, nullptr, st));
+    KX_TRY(norm_rows(e, L.w.ln1, M, nullptr, st));
     const int head_w = d.head_dim;
     const int qkv_pbn = linear_pair_bn(qkv, M);
     const bool fused_rope = !decode && qkv_pbn && qkv_pbn % head_w == 0;   // QKV epilogue also rotates and appends
@@ -238,10 +269,10 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, pos0, d.n_q, d.n_kv, d.head_dim, st));
     }
-    KX_TRY(linear_resid(e, wo, M, st));
-    KX_TRY(op_rmsnorm(e->resid, L.w.ln2, e->xn, M, d.hidden, d.eps, nullptr, st));
+    KX_TRY(linear_resid(e, wo, M, st, decode));
+    KX_TRY(norm_rows(e, L.w.ln2, M, nullptr, st));
     KX_TRY(linear(e, wgu, M, EPI_SWIGLU, e->mlp, d.inter, nullptr, st));
-    KX_TRY(linear_resid(e, wd, M, st));
+    KX_TRY(linear_resid(e, wd, M, st, decode));
     return KX_OK;
 }
 
@@ -279,7 +310,7 @@ int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
 // final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
 int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
     const kx_model_desc &d = e->d;
-    KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, B, d.hidden, d.eps, row_map, st));
+    KX_TRY(norm_rows(e, e->norm, B, row_map, st));
     const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
     KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
     if (d_logits_step)
@@ -385,6 +416,10 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&e->xn_b[j], e->xn, Mx, d.hidden, d.hidden, bns[j]));
         KX_E(make_tmap_bf16_2d(&e->attn_b[j], e->attn, Mx, e->q_dim, e->q_dim, bns[j]));
         KX_E(make_tmap_bf16_2d(&e->mlp_b[j], e->mlp, Mx, d.inter, d.inter, bns[j]));
+    }
+    if (d.tp_size <= 1 && d.max_batch > 256 && d.hidden % 256 == 0) {
+        e->splitk_cap = (size_t)8 * (d.max_batch < 512 ? d.max_batch : 512) * d.hidden;
+        KX_E(dev_alloc(e, (void **)&e->splitk_part, e->splitk_cap * sizeof(float)));
     }
     // persistent decode kernel: single GPU replicas only (the tensor-parallel epilogue lives in the cluster GEMM)
     {

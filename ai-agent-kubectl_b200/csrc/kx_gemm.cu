@@ -343,7 +343,11 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
     asm volatile("griddepcontrol.launch_dependents;");        // launched with programmatic serialization (see launch_pair)
     const int total_kb = (p.k + BK - 1) / BK;
-    const int n_work = m_pairs * n_tiles;
+    // split-K (EPI_F32 only): a work item is (output tile, k slice); slice ks writes its partial tile to
+    // out + ks * split_stride and the consumer (the next RMSNorm) adds the slices up in a fixed order
+    const int S = p.splits > 1 ? p.splits : 1;
+    const int kbp = S > 1 ? p.kb_per_split : total_kb;
+    const int n_work = m_pairs * n_tiles * S;
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmA);
@@ -367,31 +371,35 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             // of weight half-tiles is requested before griddepcontrol.wait, the activation tiles after it.
             int pre = 0;
             if (cluster_id < n_work) {
-                const int mp = cluster_id / n_tiles, nt = cluster_id - mp * n_tiles;
-                const int n0 = nt * BN + (int)rank * (BN / 2);
-                pre = total_kb < C::STAGES ? total_kb : C::STAGES;
+                const int tile = cluster_id / S, ks = cluster_id - tile * S;
+                const int mp = tile / n_tiles, nt = tile - mp * n_tiles;
+                const int n0 = nt * BN + (int)rank * (BN / 2), kb0 = ks * kbp;
+                const int nkb = min(kbp, total_kb - kb0);
+                pre = nkb < C::STAGES ? nkb : C::STAGES;
                 for (int i = 0; i < pre; ++i) {
                     mbar_expect_tx(full + i, C::STAGE_BYTES);
-                    tma_load_2d_mcast(smem + i * C::STAGE_BYTES + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + i, i * BK, n0,
+                    tma_load_2d_mcast(smem + i * C::STAGE_BYTES + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + i, (kb0 + i) * BK, n0,
                                       (uint16_t)3, pol_w);
                 }
             }
             asm volatile("griddepcontrol.wait;" ::: "memory");
             for (int wk = cluster_id; wk < n_work; wk += n_clusters) {
-                const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
-                const int m0 = (2 * mp + (int)rank) * BM, n0 = nt * BN + (int)rank * (BN / 2);
-                for (int i = 0; i < total_kb; ++i, ++it) {
+                const int tile = wk / S, ks = wk - tile * S;
+                const int mp = tile / n_tiles, nt = tile - mp * n_tiles;
+                const int m0 = (2 * mp + (int)rank) * BM, n0 = nt * BN + (int)rank * (BN / 2), kb0 = ks * kbp;
+                const int nkb = min(kbp, total_kb - kb0);
+                for (int i = 0; i < nkb; ++i, ++it) {
                     const int s = it % C::STAGES;
                     uint8_t *sa = smem + s * C::STAGE_BYTES;
                     if (it < pre) {                                      // weights of this stage are already on their way
-                        tma_load_2d_hint(sa, &tmA, full + s, i * BK, m0, pol_act);
+                        tma_load_2d_hint(sa, &tmA, full + s, (kb0 + i) * BK, m0, pol_act);
                         continue;
                     }
                     const uint32_t ph = (it / C::STAGES) & 1;
                     mbar_wait(empty + s, ph ^ 1);                       // both CTAs are done with this stage
                     mbar_expect_tx(full + s, C::STAGE_BYTES);
-                    tma_load_2d_hint(sa, &tmA, full + s, i * BK, m0, pol_act);
-                    tma_load_2d_mcast(sa + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + s, i * BK, n0, (uint16_t)3, pol_w);
+                    tma_load_2d_hint(sa, &tmA, full + s, (kb0 + i) * BK, m0, pol_act);
+                    tma_load_2d_mcast(sa + C::A_BYTES + rank * (C::B_BYTES / 2), &tmBhalf, full + s, (kb0 + i) * BK, n0, (uint16_t)3, pol_w);
                 }
             }
         }
@@ -404,7 +412,8 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 mbar_wait(tmem_empty + ab, ((tile_it >> 1) & 1) ^ 1);   // epilogue drained this accumulator
                 tc_fence_after();
                 const uint32_t acc = tmem + (uint32_t)(ab * BN);
-                for (int i = 0; i < total_kb; ++i, ++it) {
+                const int nkb = min(kbp, total_kb - (wk % S) * kbp);
+                for (int i = 0; i < nkb; ++i, ++it) {
                     const int s = it % C::STAGES;
                     const uint32_t ph = (it / C::STAGES) & 1;
                     mbar_wait(full + s, ph);
@@ -422,10 +431,13 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int q = warp & 3;
         int tile_it = 0;
         asm volatile("griddepcontrol.wait;" ::: "memory");     // the epilogue reads / overwrites buffers earlier kernels used
+        GemmParams ps = p;                                     // per-slice output pointer (split-K)
         for (int wk = cluster_id; wk < n_work; wk += n_clusters, ++tile_it) {
-            const int mp = wk / n_tiles, nt = wk - mp * n_tiles;
+            const int tile = wk / S, ks = wk - tile * S;
+            const int mp = tile / n_tiles, nt = tile - mp * n_tiles;
             const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
             const int ab = tile_it & 1;
+            if (EPI == EPI_F32) ps.out = reinterpret_cast<float *>(p.out) + (size_t)ks * p.split_stride;
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
@@ -459,7 +471,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         __syncwarp();
                         if (lane == 0) mbar_arrive(tmem_empty + ab);
                     }
-                    epilogue_chunk<EPI, false>(p, v, arow, n0 + c, false);
+                    epilogue_chunk<EPI, false>(ps, v, arow, n0 + c, false);
                 }
             }
         }
@@ -484,8 +496,18 @@ int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams 
         attr_set = true;
     }
     const int m_pairs = (p.a_rows + 2 * BM - 1) / (2 * BM), n_tiles = (p.b_rows + BN - 1) / BN;
+    GemmParams pp = p;
+    if (pp.splits > 1) {
+        KX_REQUIRE(EPI == EPI_F32, KX_EINVAL, "kx_gemm: the token-major kernel splits k only with the fp32 epilogue");
+        const int total_kb = (pp.k + BK - 1) / BK;
+        if (pp.splits > total_kb) pp.splits = total_kb;
+        pp.kb_per_split = (total_kb + pp.splits - 1) / pp.splits;
+        pp.splits = (total_kb + pp.kb_per_split - 1) / pp.kb_per_split;
+    } else {
+        pp.splits = 1;
+    }
     int clusters = sms / 2;
-    if (clusters > m_pairs * n_tiles) clusters = m_pairs * n_tiles;
+    if (clusters > m_pairs * n_tiles * pp.splits) clusters = m_pairs * n_tiles * pp.splits;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * clusters);
     cfg.blockDim = dim3(kGemmThreads);
@@ -496,7 +518,7 @@ int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tbh, p, m_pairs, n_tiles));
+    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tbh, pp, m_pairs, n_tiles));
     count_launch();
     return KX_OK;
 }
@@ -881,6 +903,7 @@ extern "C" int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const 
     if (rc != KX_OK) return rc;
     const int pbn = swap ? 0 : gemm_pair_bn(a_rows, b_rows);
     if (pbn) {                                        // prefill: persistent CTA-pair kernel
+        p.splits = 1;                                 // (its split-K mode writes per-slice partials: engine-internal)
         rc = make_tmap_bf16_2d(&tb, d_b, b_rows, k, ldb, pbn / 2);
         if (rc != KX_OK) return rc;
         return gemm_launch_pair(ta, tb, p, pbn, st);

@@ -17,6 +17,7 @@ struct GemmParams {
     int epilogue;
     int splits;              // split-K factor requested (clamped to the number of 64-wide k blocks)
     int kb_per_split;        // filled by gemm_launch
+    size_t split_stride;     // token-major pair kernel with splits > 1 (EPI_F32 only): fp32 elements between the splits' partial outputs
     float *ws;               // split-K scratch, filled by gemm_launch
     uint32_t *tickets;
     // EPI_QKV_ROPE (token-major pair kernel only): bias, bf16 rounding, RoPE on q and k, q -> out,

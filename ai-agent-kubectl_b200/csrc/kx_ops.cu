@@ -95,25 +95,38 @@ __global__ void rmsnorm_kernel(const float *__restrict__ x, const __nv_bfloat16 
 // the GPU idle and is latency bound; here the row is read once into registers.
 template <int PER>   // float4 chunks per thread: H = 512 * PER
 __global__ void __launch_bounds__(128)
-rmsnorm_row_kernel(const float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, __nv_bfloat16 *__restrict__ y,
-                   int H, float eps, const int *__restrict__ row_map) {
+rmsnorm_row_kernel(float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, __nv_bfloat16 *__restrict__ y,
+                   int H, float eps, const int *__restrict__ row_map, const float *__restrict__ part, int splits,
+                   size_t split_stride) {
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int row = blockIdx.x, tid = threadIdx.x;
-    const float *xr = x + (size_t)(row_map ? row_map[row] : row) * H;
+    const size_t src = (size_t)(row_map ? row_map[row] : row) * H;
+    float *xr = x + src;
     float4 v[PER];
     float ss = 0.f;
 #pragma unroll
     for (int u = 0; u < PER; ++u) {
         const int i = (u * 128 + tid) * 4;
         v[u] = i < H ? *reinterpret_cast<const float4 *>(xr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (splits > 0 && i < H) {
+            // pending split-K partial sums of the preceding row-parallel projection: residual += their sum,
+            // slices added in index order (deterministic), and the residual row is written back
+            float4 a = *reinterpret_cast<const float4 *>(part + src + i);
+            for (int s = 1; s < splits; ++s) {
+                const float4 c = *reinterpret_cast<const float4 *>(part + (size_t)s * split_stride + src + i);
+                a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+            }
+            v[u].x += a.x; v[u].y += a.y; v[u].z += a.z; v[u].w += a.w;
+            *reinterpret_cast<float4 *>(xr + i) = v[u];
+        }
         ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
     }
     ss = warp_sum(ss);
-    __shared__ float part[4];
-    if ((tid & 31) == 0) part[tid >> 5] = ss;
+    __shared__ float wsum[4];
+    if ((tid & 31) == 0) wsum[tid >> 5] = ss;
     __syncthreads();
-    const float r = 1.0f / sqrtf((part[0] + part[1] + part[2] + part[3]) / (float)H + eps);
+    const float r = 1.0f / sqrtf((wsum[0] + wsum[1] + wsum[2] + wsum[3]) / (float)H + eps);
     __nv_bfloat16 *yr = y + (size_t)row * H;
 #pragma unroll
     for (int u = 0; u < PER; ++u) {
@@ -892,18 +905,20 @@ int op_embed(const int *tokens, const void *table, float *x, int M, int H, cudaS
     return KX_OK;
 }
 
-int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st) {
+int op_rmsnorm(float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st,
+               const float *part, int splits, size_t split_stride) {
     if (M <= 2048 && H <= 8192) {
         const int per = (H + 511) / 512;
         const __nv_bfloat16 *gg = (const __nv_bfloat16 *)g;
         __nv_bfloat16 *yy = (__nv_bfloat16 *)y;
-        if (per <= 2) KX_CUDA(launch_pdl(rmsnorm_row_kernel<2>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
-        else if (per <= 4) KX_CUDA(launch_pdl(rmsnorm_row_kernel<4>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
-        else if (per <= 8) KX_CUDA(launch_pdl(rmsnorm_row_kernel<8>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
-        else KX_CUDA(launch_pdl(rmsnorm_row_kernel<16>, M, 128, 0, st, x, gg, yy, H, eps, row_map));
+        if (per <= 2) KX_CUDA(launch_pdl(rmsnorm_row_kernel<2>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
+        else if (per <= 4) KX_CUDA(launch_pdl(rmsnorm_row_kernel<4>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
+        else if (per <= 8) KX_CUDA(launch_pdl(rmsnorm_row_kernel<8>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
+        else KX_CUDA(launch_pdl(rmsnorm_row_kernel<16>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
         count_launch();
         return KX_OK;
     }
+    KX_REQUIRE(splits == 0, KX_EINVAL, "rmsnorm: pending split-K partials are only folded in by the row kernel (M <= 2048)");
     rmsnorm_kernel<<<(M + 7) / 8, 256, 0, st>>>(x, (const __nv_bfloat16 *)g, (__nv_bfloat16 *)y, M, H, eps, row_map);
     count_launch();
     KX_CUDA(cudaGetLastError());

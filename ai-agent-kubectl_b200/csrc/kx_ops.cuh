@@ -8,7 +8,10 @@
 namespace kx {
 
 int op_embed(const int *tokens, const void *table, float *x, int M, int H, cudaStream_t st);
-int op_rmsnorm(const float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st);
+// part / splits / split_stride: split-K partial sums of the preceding projection still to be added to the residual
+// rows (x is updated in place before it is normalised); splits = 0: plain RMSNorm
+int op_rmsnorm(float *x, const void *g, void *y, int M, int H, float eps, const int *row_map, cudaStream_t st,
+               const float *part = nullptr, int splits = 0, size_t split_stride = 0);
 int op_rope_append(void *qkv, int qkv_ld, const int *pos, const int *seq, const float *rope, void *pages,
                    const int *block_table, int max_pages, int M, int n_q, int n_kv, int hd, cudaStream_t st);
 // decode attention also applies RoPE to the new token's q/k and appends its k, v to the cache.

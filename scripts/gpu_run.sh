@@ -1,7 +1,5 @@
-timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/t_gpu_all.log 2>&1; echo "pytest rc=$?" >> gpurun_out/t_gpu_all.log
-tail -n 6 gpurun_out/t_gpu_all.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-tail -n 4 gpurun_out/smoke.log
-timeout 900 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"
-cat gpurun_out/bench_default.json | cut -c1-1500
-tail -n 3 gpurun_out/bench_default.err
+timeout 900 python -m pytest tests/test_gemm_gpu.py tests/test_generator_gpu.py -q -x > gpurun_out/t_sk.log 2>&1; echo "pytest rc=$?" >> gpurun_out/t_sk.log
+tail -n 4 gpurun_out/t_sk.log
+timeout 300 python profiles/run_gen.py llama-3.2-1b 512 256 32 3 > gpurun_out/gen512_sk.log 2>&1
+timeout 300 python profiles/run_gen.py llama-3.2-1b 300 256 32 3 > gpurun_out/gen300_sk.log 2>&1
+tail -n 3 gpurun_out/gen512_sk.log gpurun_out/gen300_sk.log
