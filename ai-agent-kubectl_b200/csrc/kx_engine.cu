@@ -63,6 +63,7 @@ struct kx_engine {
     // device, the split-K plan, partial-sum scratch and the grid barrier counter
     // wide decode batches (256 < M <= 512): the row-parallel projections run as split-K token-major GEMMs that
     // leave per-slice partial sums here; the RMSNorm that follows adds them to the residual (pend_* describe them)
+    void *argmax_parts = nullptr;                  // fused lm_head argmax: int2 [parts][max_batch]
     float *splitk_part = nullptr;
     size_t splitk_cap = 0;                         // floats
     const float *pend_part = nullptr;
@@ -197,7 +198,8 @@ int norm_rows(kx_engine *e, const void *g, int M, const int *row_map, cudaStream
 // parallelism every rank holds a partial sum: it goes to tp_buf, is all-reduced, then added.
 int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool decode) {
     const kx_model_desc &d = e->d;
-    if (d.tp_size <= 1 && decode && M > 256 && M <= 512 && d.hidden % 256 == 0 && e->splitk_part) {
+    static const int splitk_min_m = [] { const char *v = getenv("KX_SPLITK_MIN_M"); return v ? atoi(v) : 257; }();
+    if (d.tp_size <= 1 && decode && M >= splitk_min_m && M <= 512 && d.hidden % 256 == 0 && e->splitk_part) {
         // 2 x (hidden / 256) tiles of 256 x 256 would use a fraction of the SMs: cut k so that ~64 CTA pairs work,
         // slices land in splitk_part and the next RMSNorm adds them to the residual
         const int tiles = ((M + 255) / 256) * (d.hidden / 256);
@@ -312,6 +314,32 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
     const kx_model_desc &d = e->d;
     KX_TRY(norm_rows(e, e->norm, B, row_map, st));
     const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+    // Nobody asked for the logits: the lm_head epilogue keeps only (max, index) per token and tile, a small
+    // second kernel finishes the pick; [B, vocab] is never written.  (Small vocabularies take the cluster split-K
+    // GEMM, which has no such epilogue, and B > 512 the single-CTA kernel: both use the logits path.)
+    const int pbn = linear_pair_bn(head, B);
+    const int v_tiles = (d.vocab + 127) / 128;
+    const int sbn = gemm_pick_bn(1, B);
+    static const bool want_fused = [] { const char *v = getenv("KX_FUSED_ARGMAX"); return !(v && v[0] == '0'); }();
+    const bool fused = want_fused && !d_logits_step && e->argmax_parts &&
+                       (pbn || (B <= 512 && pick_splits(d.vocab, d.hidden, (B + sbn - 1) / sbn) == 1));
+    if (fused) {
+        const int n_parts = pbn ? (d.vocab + pbn - 1) / pbn : 4 * v_tiles;
+        KX_TRY(linear(e, head, B, EPI_ARGMAX, e->argmax_parts, d.max_batch, nullptr, st));
+        if (d.tp_size <= 1) {
+            KX_TRY(op_argmax_parts(e->argmax_parts, n_parts, d.max_batch, B, 0, e->next_tok, nullptr, nullptr, st));
+        } else {
+            KX_REQUIRE(e->comm && e->allgather, KX_EINVAL, "engine: tensor parallelism needs kx_engine_set_collectives");
+            KX_TRY(op_argmax_parts(e->argmax_parts, n_parts, d.max_batch, B, d.vocab_offset, nullptr, nullptr, e->tp_pairs, st));
+            const int rc = e->allgather(e->tp_pairs, e->tp_gathered, (size_t)B * 8, /*ncclInt8*/ 0, e->comm, st);
+            KX_REQUIRE(rc == 0, KX_ECUDA, "engine: ncclAllGather failed with %d", rc);
+            KX_TRY(op_pick(e->tp_gathered, d.tp_size, B, e->next_tok, st));
+        }
+        store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
+        count_launch();
+        KX_CUDA(cudaGetLastError());
+        return KX_OK;
+    }
     KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
@@ -417,7 +445,8 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         KX_E(make_tmap_bf16_2d(&e->attn_b[j], e->attn, Mx, e->q_dim, e->q_dim, bns[j]));
         KX_E(make_tmap_bf16_2d(&e->mlp_b[j], e->mlp, Mx, d.inter, d.inter, bns[j]));
     }
-    if (d.tp_size <= 1 && d.max_batch > 256 && d.hidden % 256 == 0) {
+    KX_E(dev_alloc(e, &e->argmax_parts, (size_t)4 * ((d.vocab + 127) / 128) * d.max_batch * 8));
+    if (d.tp_size <= 1 && d.max_batch > 128 && d.hidden % 256 == 0) {
         e->splitk_cap = (size_t)8 * (d.max_batch < 512 ? d.max_batch : 512) * d.hidden;
         KX_E(dev_alloc(e, (void **)&e->splitk_part, e->splitk_cap * sizeof(float)));
     }

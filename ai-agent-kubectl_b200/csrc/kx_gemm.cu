@@ -210,13 +210,40 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_wait(tmem_full, 0);
         tc_fence_after();
         const bool split = gridDim.z > 1;
-        if (!split || EPI == EPI_RESID) {
+        if (EPI == EPI_ARGMAX) {
+            // swap-AB lm_head: rows = vocabulary entries, columns = tokens.  Per token the warp reduces its 32 rows
+            // to (max, lowest index); lane j ends up holding the pair of token column j and writes it.
+            // The 32 x 32 block (rows x token columns) goes through this warp's slice of the drained stage ring
+            // (padded rows: conflict-free both ways); then lane j scans token column j over the 32 rows in order.
+            int2 *parts = reinterpret_cast<int2 *>(p.out) + (size_t)(blockIdx.y * 4 + q) * p.ldo;
+            float *tr = reinterpret_cast<float *>(smem) + q * (32 * 33);
+            const int row0 = m0 + q * 32;
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 float v[32];
                 tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
                 tmem_ld_wait();
-                epilogue_chunk<EPI, SWAP>(p, v, arow, n0 + c, split);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) tr[lane * 33 + j] = v[j];
+                __syncwarp();
+                float bv = -INFINITY;
+                int bi = 0x7fffffff;
+                const int rows = min(32, p.a_rows - row0);
+                for (int r = 0; r < rows; ++r) {
+                    const float x = tr[r * 33 + lane];
+                    if (x > bv) { bv = x; bi = row0 + r; }        // ascending rows: the lowest index wins a tie
+                }
+                __syncwarp();
+                const int tok = n0 + c + lane;
+                if (tok < p.b_rows) parts[tok] = make_int2(__float_as_int(bv), bi);
+            }
+        } else if (!split || EPI == EPI_RESID) {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                tmem_ld_wait();
+                epilogue_chunk<EPI == EPI_ARGMAX ? EPI_F32 : EPI, SWAP>(p, v, arow, n0 + c, split);
             }
         } else {
             // split-K: reduce into scratch laid out [tile][col][row] so a warp's atomics are contiguous
@@ -245,7 +272,7 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         v[j] = 0.f;
                         if (n0 + c + j < p.b_rows) { v[j] = __ldcg(ws + (size_t)(c + j) * BM); __stcg(ws + (size_t)(c + j) * BM, 0.f); }
                     }
-                    epilogue_chunk<EPI, SWAP>(p, v, arow, n0 + c, false);
+                    epilogue_chunk<EPI == EPI_ARGMAX ? EPI_F32 : EPI, SWAP>(p, v, arow, n0 + c, false);
                 }
                 if (etid == 0) p.tickets[tile] = 0;
             }
@@ -460,6 +487,25 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0);
                     }
                 }
+            } else if (EPI == EPI_ARGMAX) {
+                // token-major lm_head: this thread's row is a token; scan the tile's vocabulary columns in order
+                float bv = -INFINITY;
+                int bi = 0x7fffffff;
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    float v[32];
+                    tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                    tmem_ld_wait();
+                    if (c + 32 >= BN) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tmem_empty + ab);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (n0 + c + j < p.b_rows && v[j] > bv) { bv = v[j]; bi = n0 + c + j; }
+                }
+                if (arow < p.a_rows) reinterpret_cast<int2 *>(p.out)[(size_t)nt * p.ldo + arow] = make_int2(__float_as_int(bv), bi);
             } else {
 #pragma unroll 1
                 for (int c = 0; c < BN; c += 32) {
@@ -471,7 +517,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         __syncwarp();
                         if (lane == 0) mbar_arrive(tmem_empty + ab);
                     }
-                    epilogue_chunk<EPI, false>(ps, v, arow, n0 + c, false);
+                    epilogue_chunk<EPI == EPI_ARGMAX ? EPI_F32 : EPI, false>(ps, v, arow, n0 + c, false);
                 }
             }
         }
@@ -531,6 +577,7 @@ int launch_pair_epi(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmPar
         case EPI_SWIGLU: return launch_pair<BN, EPI_SWIGLU>(ta, tbh, p, st);
         case EPI_F32: return launch_pair<BN, EPI_F32>(ta, tbh, p, st);
         case EPI_QKV_ROPE: return launch_pair<BN, EPI_QKV_ROPE>(ta, tbh, p, st);
+        case EPI_ARGMAX: return launch_pair<BN, EPI_ARGMAX>(ta, tbh, p, st);
     }
     set_error("kx_gemm: unknown epilogue %d", p.epilogue);
     return KX_EINVAL;
@@ -795,6 +842,9 @@ int launch_epi(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p
         case EPI_RESID: return launch<BN, EPI_RESID, SWAP>(ta, tb, p, grid, st);
         case EPI_SWIGLU: return launch<BN, EPI_SWIGLU, SWAP>(ta, tb, p, grid, st);
         case EPI_F32: return launch<BN, EPI_F32, SWAP>(ta, tb, p, grid, st);
+        case EPI_ARGMAX:
+            KX_REQUIRE(SWAP && grid.z == 1, KX_EINVAL, "kx_gemm: the argmax epilogue of this kernel needs swap-AB without split-K");
+            return launch<BN, EPI_ARGMAX, SWAP>(ta, tb, p, grid, st);
     }
     set_error("kx_gemm: unknown epilogue %d", p.epilogue);
     return KX_EINVAL;
@@ -892,7 +942,9 @@ extern "C" int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const 
     KX_REQUIRE(d_a && d_b && d_out, KX_EINVAL, "kx_gemm_bf16: NULL operand");
     KX_REQUIRE(a_rows > 0 && b_rows > 0 && k > 0 && k % 8 == 0, KX_EINVAL, "kx_gemm_bf16: bad shape (k must be a multiple of 8)");
     KX_REQUIRE(swap || b_rows % 8 == 0, KX_EINVAL, "kx_gemm_bf16: feature count must be a multiple of 8");
-    KX_REQUIRE(ldo % 8 == 0, KX_EINVAL, "kx_gemm_bf16: ldo must be a multiple of 8 elements");
+    KX_REQUIRE(epilogue == EPI_ARGMAX || ldo % 8 == 0, KX_EINVAL, "kx_gemm_bf16: ldo must be a multiple of 8 elements");
+    KX_REQUIRE(epilogue != EPI_ARGMAX || splits <= 1, KX_EINVAL, "kx_gemm_bf16: the argmax epilogue does not split k");
+    KX_REQUIRE(epilogue != EPI_QKV_ROPE, KX_EINVAL, "kx_gemm_bf16: epilogue %d is engine-internal", epilogue);
     KX_REQUIRE(epilogue != EPI_SWIGLU || (swap ? a_rows : b_rows) % 2 == 0, KX_EINVAL, "kx_gemm_bf16: SwiGLU needs (gate, up) pairs");
     cudaStream_t st = (cudaStream_t)stream;
     GemmParams p{};

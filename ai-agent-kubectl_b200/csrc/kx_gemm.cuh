@@ -6,7 +6,11 @@
 
 namespace kx {
 
-enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3, EPI_QKV_ROPE = 4 };
+// EPI_ARGMAX (lm_head, k8): no [tokens, vocabulary] logits are written; every CTA reduces its tile to one
+// (max logit, lowest feature index attaining it) pair per token and part: out = int2 [parts][ldo] with the
+// value's bits in .x.  Token-major pair kernel: parts = feature tiles.  Swap-AB kernel: parts = 4 per 128-feature
+// tile (one per epilogue warp).  op_argmax_parts finishes the reduction.
+enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3, EPI_QKV_ROPE = 4, EPI_ARGMAX = 5 };
 
 struct GemmParams {
     int a_rows, b_rows, k;   // D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T

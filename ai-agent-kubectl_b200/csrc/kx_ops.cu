@@ -788,6 +788,37 @@ argmax_kernel(const float *__restrict__ logits, int V, int ld, int *__restrict__
     }
 }
 
+// ---- second stage of the fused lm_head argmax: parts[n_parts][ld] (value bits, index) -> one id per token ----
+// block = 32 tokens x 32 part groups; ties -> lowest index (what torch.argmax over the full row returns)
+__global__ void __launch_bounds__(1024)
+argmax_parts_kernel(const int2 *__restrict__ parts, int n_parts, int ld, int B, int id_offset, int *__restrict__ out,
+                    int *__restrict__ out2, int2 *__restrict__ out_pairs) {
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int b = blockIdx.x * 32 + tx;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    if (b < B) {
+        for (int pi = ty; pi < n_parts; pi += 32) {
+            const int2 v = parts[(size_t)pi * ld + b];
+            const float f = __int_as_float(v.x);
+            if (f > best || (f == best && v.y < bi)) { best = f; bi = v.y; }
+        }
+    }
+    __shared__ float sv[32][33];
+    __shared__ int si[32][33];
+    sv[ty][tx] = best; si[ty][tx] = bi;
+    __syncthreads();
+    if (ty == 0 && b < B) {
+        for (int g = 1; g < 32; ++g) {
+            const float f = sv[g][tx];
+            const int i = si[g][tx];
+            if (f > best || (f == best && i < bi)) { best = f; bi = i; }
+        }
+        if (out_pairs) out_pairs[b] = make_int2(__float_as_int(best), bi + id_offset);
+        else { out[b] = bi + id_offset; if (out2) out2[b] = bi + id_offset; }
+    }
+}
+
 // ---- tensor-parallel helpers -----------------------------------------------------
 __global__ void add_inplace_kernel(float *__restrict__ x, const float *__restrict__ d, size_t n4) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1057,6 +1088,14 @@ int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cu
     return KX_OK;
 }
 
+int op_argmax_parts(const void *parts, int n_parts, int ld, int B, int id_offset, int *out, int *out2, void *out_pairs,
+                    cudaStream_t st) {
+    argmax_parts_kernel<<<(B + 31) / 32, 1024, 0, st>>>((const int2 *)parts, n_parts, ld, B, id_offset, out, out2, (int2 *)out_pairs);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
 int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st) {
     const size_t n4 = n / 4;
     add_inplace_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(x, d, n4);
@@ -1115,4 +1154,10 @@ extern "C" int kx_attn_decode(const void *d_qkv, int32_t qkv_ld, void *d_out, in
     }
     return op_attn_decode(d_qkv, qkv_ld, d_out, out_ld, d_pages, d_block_table, max_pages, d_pos, d_rope, B, max_T, n_q, n_kv, hd,
                           key0, part_o, part_ml, n_part, st);
+}
+
+extern "C" int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream) {
+    using namespace kx;
+    KX_REQUIRE(d_parts && d_ids && n_parts >= 1 && B >= 1 && ld >= B, KX_EINVAL, "kx_argmax_parts: bad argument");
+    return op_argmax_parts(d_parts, n_parts, ld, B, 0, d_ids, nullptr, nullptr, (cudaStream_t)stream);
 }

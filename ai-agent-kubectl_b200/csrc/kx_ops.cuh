@@ -26,6 +26,10 @@ int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt
 int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
                     int max_pages, int B, int S, int pos0, int n_q, int n_kv, int hd, cudaStream_t st);
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st);
+// second stage of the GEMM's EPI_ARGMAX epilogue: parts int2 [n_parts][ld] -> ids (out / out2) or, for a
+// vocabulary shard, (value bits, id + id_offset) pairs (out_pairs)
+int op_argmax_parts(const void *parts, int n_parts, int ld, int B, int id_offset, int *out, int *out2, void *out_pairs,
+                    cudaStream_t st);
 int op_advance(int *pos, int n, cudaStream_t st);
 // tensor-parallel helpers
 int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st);

@@ -120,6 +120,10 @@ void kx_release_host_staging(void);
 #define KX_EPI_RESID     1   /* out fp32 += acc   (residual stream)                    */
 #define KX_EPI_SWIGLU    2   /* features are (gate, up) pairs: out bf16[f/2] = silu(g)*u */
 #define KX_EPI_F32       3   /* out fp32 = acc    (logits)                             */
+#define KX_EPI_ARGMAX    5   /* lm_head + greedy pick without materialising the logits: out = int2 [parts][ldo],
+                                (max logit bits, lowest feature index attaining it) per token and part.
+                                swap = 1 (batch < 256): 4 parts per 128-feature tile; swap = 0: 1 part per
+                                256-feature tile.  kx_argmax_parts reduces the parts to one id per token. */
 
 /*
  * kx_gemm_bf16 -- D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T on tcgen05 tensor
@@ -135,6 +139,9 @@ void kx_release_host_staging(void);
 int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, int64_t b_rows, int64_t ldb,
                  int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
                  void *stream);
+
+/* Second stage of KX_EPI_ARGMAX: d_parts int2 [n_parts][ld] -> d_ids int32 [B]; ties go to the lowest id. */
+int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream);
 
 /*
  * kx_attn_decode -- one decode step of attention over the paged KV cache, as the

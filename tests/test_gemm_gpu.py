@@ -84,3 +84,50 @@ def test_strided_operands(gemm):
     out = torch.zeros(300, 128, device="cuda")
     gemm(a, w, 3, 0, out)
     torch.testing.assert_close(out, _ref(a, w), rtol=1e-4, atol=1e-3)
+
+
+def _argmax_rows(ref):
+    """(max, lowest index) per row on the CPU: the tie rule of torch.argmax / the reference decoder."""
+    import numpy as np
+    a = ref.cpu().numpy()
+    return np.argmax(a, axis=1)          # numpy returns the first maximal index
+
+
+@pytest.mark.parametrize("batch,vocab,k", [(5, 1000, 128), (64, 5000, 896), (100, 33000, 256), (200, 2048, 192)])
+def test_lm_head_argmax_epilogue_swap_ab(gemm, batch, vocab, k):
+    """KX_EPI_ARGMAX, decode orientation (weights are the 128-row operand): ids must equal the argmax of the
+    logits the fp32 epilogue of the same kernel writes, without [batch, vocab] ever being stored."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import _lib
+    w, x = _rand(vocab, k, 11), _rand(batch, k, 12)
+    w[vocab // 3] = w[vocab // 2]                                  # an exact tie: the lower index must win
+    logits = torch.zeros(batch, vocab, device="cuda")
+    gemm(w, x, 3, 1, logits)
+    n_parts = 4 * ((vocab + 127) // 128)
+    parts = torch.zeros(n_parts, batch, device="cuda", dtype=torch.int64)      # int2 (value bits, index) per entry
+    gemm(w, x, 5, 1, parts)
+    ids = torch.zeros(batch, device="cuda", dtype=torch.int32)
+    L = _lib.lib()
+    _lib.check(L.kx_argmax_parts(parts.data_ptr(), n_parts, batch, batch, ids.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert (ids.cpu().numpy() == _argmax_rows(logits)).all()
+
+
+@pytest.mark.parametrize("batch,vocab,k", [(256, 4096, 128), (300, 5000, 192), (512, 33000, 256)])
+def test_lm_head_argmax_epilogue_token_major(gemm, batch, vocab, k):
+    """Same through the CTA-pair kernel (wide decode batch): one part per feature tile."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import _lib
+    x, w = _rand(batch, k, 13), _rand(vocab, k, 14)
+    w[vocab // 3] = w[vocab // 2]
+    logits = torch.zeros(batch, vocab, device="cuda")
+    gemm(x, w, 3, 0, logits)
+    bn = 256 if (vocab % 256 == 0 or vocab >= 2048) else 128
+    n_parts = (vocab + bn - 1) // bn
+    parts = torch.zeros(n_parts, batch, device="cuda", dtype=torch.int64)      # int2 (value bits, index) per entry
+    gemm(x, w, 5, 0, parts)
+    ids = torch.zeros(batch, device="cuda", dtype=torch.int32)
+    L = _lib.lib()
+    _lib.check(L.kx_argmax_parts(parts.data_ptr(), n_parts, batch, batch, ids.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert (ids.cpu().numpy() == _argmax_rows(logits)).all()
