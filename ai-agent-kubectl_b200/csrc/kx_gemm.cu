@@ -42,7 +42,10 @@ template <int BN> struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (96 * 1024) / STAGE_BYTES;          // two CTAs per SM
+#ifndef KX_RING_KB
+#define KX_RING_KB 96
+#endif
+    static constexpr int STAGES = (KX_RING_KB * 1024) / STAGE_BYTES;  // 96 KB: two CTAs per SM
     static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };

@@ -139,3 +139,22 @@ def test_full_size_10m_bit_exact(ks):
     idx = np.repeat(off[:100000] - off2[:-1], lens) + np.arange(int(off2[-1]))
     again = ks.validate_hash_host(r2["san"][idx], off2)
     assert np.array_equal(again["hash"], r2["hash"])
+
+
+def test_router_affinity_key_is_the_cache_key_hash(ks):
+    """ReplicaRouter's default key: the k9 hash of the sanitised request inside the prompt, i.e. what the
+    reference's TTLCache lookup hashes (app.py:305,312) -- whitespace variants of a request share a replica."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import chat_model, router
+    head = "You are a Kubernetes CLI specialist.\nUser Request: "
+    variants = ["list all pods in namespace ns7", "list  all\tpods in\nnamespace ns7 ", "\r\nlist all pods in namespace ns7"]
+    others = [f"describe the node n{i}" for i in range(64)]
+    prompts = [head + q + "\nKubectl Command:\n" for q in variants + others]
+    r = router.ReplicaRouter([chat_model.CallableEngine(lambda p: p) for _ in range(8)])
+    where = r.assign(prompts)
+    assert len(set(where[:3])) == 1
+    keys = router.k9_keys(prompts)
+    assert keys[0] == keys[1] == keys[2] == po.spec_hash(po.ref_sanitize_query(variants[0]))   # CPython's str hash, seed 0
+    assert where == [k % 8 for k in keys]
+    assert len(set(where[3:])) > 4                                         # and distinct requests spread out
+    r.close()
