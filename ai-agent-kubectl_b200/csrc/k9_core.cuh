@@ -316,14 +316,48 @@ KX_HD int64_t sip_stream(const uint32_t *W, int lo, int n) {
     return s.finish();
 }
 
+// Length (2 or 3) of the UTF-8 encoding of a non-ASCII whitespace code point that starts at B[p], else 0.
+// Exactly the 19 code points of ws_wide: U+0085 U+00A0 | U+1680 | U+2000..200A U+2028 U+2029 U+202F | U+205F | U+3000.
+KX_HD int uws_at(const uint8_t *B, int p, int hi) {
+    const uint32_t b0 = B[p];
+    if (b0 == 0xC2u) return (p + 1 < hi && (B[p + 1] == 0x85u || B[p + 1] == 0xA0u)) ? 2 : 0;
+    if (b0 < 0xE1u || b0 > 0xE3u || p + 2 >= hi) return 0;
+    const uint32_t b1 = B[p + 1], b2 = B[p + 2];
+    if (b0 == 0xE1u) return (b1 == 0x9Au && b2 == 0x80u) ? 3 : 0;
+    if (b0 == 0xE3u) return (b1 == 0x80u && b2 == 0x80u) ? 3 : 0;
+    if (b1 == 0x80u) return ((b2 >= 0x80u && b2 <= 0x8Au) || b2 == 0xA8u || b2 == 0xA9u || b2 == 0xAFu) ? 3 : 0;
+    return (b1 == 0x81u && b2 == 0x9Fu) ? 3 : 0;
+}
+
 // Returns true if the string must be redone by the general path; otherwise fills r.
+//
+// Non-ASCII whitespace at the two ENDS of the string (str.strip() removes it, app.py:74,97) is stripped here
+// as well, so a padded but otherwise ASCII string stays on this path.  Front: exact encodings, decoded
+// forwards from the string start.  Back: the same encodings matched backwards; that agrees with the general
+// path's forward decoding because what is left in between is pure ASCII (checked by the main loop: any byte
+// >= 0x80 there sends the string to the general path), so the trailing run starts on a code point boundary
+// and each matched unit is one complete encoding.
 template <bool PARSE>
 KX_HD bool fast_string(uint32_t *W, int lo, int hi, const uint8_t *cls_lut, const uint8_t *trans,
                        bool want_hash, uint8_t *san, Result &r) {
     uint8_t *B = (uint8_t *)W;
     int a = lo, b = hi;
-    while (a < hi && ws_ascii(B[a])) ++a;
-    while (b > a && ws_ascii(B[b - 1])) --b;
+    for (;;) {
+        while (a < hi && ws_ascii(B[a])) ++a;
+        if (a >= hi || B[a] < 0x80u) break;
+        const int n = uws_at(B, a, hi);
+        if (n == 0) break;
+        a += n;
+    }
+    for (;;) {
+        while (b > a && ws_ascii(B[b - 1])) --b;
+        if (b <= a || B[b - 1] < 0x80u) break;
+        int n = 0;
+        if (b - 2 >= a && uws_at(B, b - 2, b) == 2) n = 2;
+        else if (b - 3 >= a && uws_at(B, b - 3, b) == 3) n = 3;
+        if (n == 0) break;
+        b -= n;
+    }
     if (PARSE && a < b && B[a] == 0x60) return true;
 
     bool pfx = false;

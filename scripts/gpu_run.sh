@@ -1,5 +1,4 @@
-SPLITS=1,2,4,8,12 timeout 300 python profiles/sweep_decode_gemm.py 1b.qkv 1b.wo 1b.wgu 1b.wd q.wgu q.wd > gpurun_out/sweep_ring72.log 2>&1
-cat gpurun_out/sweep_ring72.log
-timeout 300 python profiles/run_gen.py llama-3.2-1b 64 256 32 4 > gpurun_out/gen64_ring72.log 2>&1
-timeout 300 python profiles/run_gen.py qwen2.5-0.5b 64 256 32 3 > gpurun_out/genq64_ring72.log 2>&1
-tail -n 2 gpurun_out/gen64_ring72.log gpurun_out/genq64_ring72.log
+timeout 900 python -m pytest tests/test_strings_gpu.py tests/test_zz_no_alloc.py tests/test_pipeline.py -q -x -m gpu > gpurun_out/t_k9.log 2>&1; echo "pytest rc=$?" >> gpurun_out/t_k9.log
+tail -n 5 gpurun_out/t_k9.log
+timeout 600 python bench.py --workload validate_hash_10m > gpurun_out/bench_k9_v5.json 2> gpurun_out/bench_k9_v5.err; echo "bench rc=$?"
+cut -c1-700 gpurun_out/bench_k9_v5.json

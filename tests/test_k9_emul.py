@@ -73,3 +73,30 @@ def test_kernel_logic_on_synthetic_and_garbage(emul, flags):
     off[1:] = np.cumsum([len(b) for b in blobs])
     data = np.frombuffer(b"".join(blobs), np.uint8)
     _same(emul(data, off, flags), c_oracle.validate_hash(data, off, flags, True, True), off)
+
+
+@pytest.mark.parametrize("flags", [0, 1])
+def test_unicode_whitespace_at_the_ends_stays_on_the_fast_path(emul, flags):
+    """str.strip() removes non-ASCII whitespace too (app.py:74,97).  The fast path strips it at both ends when
+    the rest is ASCII; pieces of broken UTF-8 next to the padding must still give exactly the oracle's answer
+    (they change where the general path's forward decoder finds code point boundaries)."""
+    rng = random.Random(11)
+    ws = [" ", "\t", "\x85", "\xa0", "\u1680", "\u2000", "\u2005", "\u200a", "\u2028", "\u2029", "\u202f", "\u205f", "\u3000"]
+    ws = [w.encode("utf-8") for w in ws]
+    junk = [b"\xe2\x80", b"\x80", b"\xc2", b"\xf0\xe2\x80\xa8", b"\xe2", b"\xe3\x80", b"\xc2\x84", b"\xe2\x80\x8b", b"\xe1\x9a"]
+    cores = [b"kubectl get pods", b"kubectl get pods -l 'a b'", b"kubectl", b"", b"kubectl get x; y", b"```\nkubectl get ns\n```",
+             b"kubectl get pods \"unclosed", b"k"]
+
+    def pad():
+        out = b""
+        for _ in range(rng.randrange(0, 4)):
+            out += rng.choice(ws) if rng.random() < 0.8 else rng.choice(junk)
+        return out
+    blobs = [pad() + rng.choice(cores) + pad() for _ in range(40000)]
+    off = np.zeros(len(blobs) + 1, np.int64)
+    off[1:] = np.cumsum([len(b) for b in blobs])
+    data = np.frombuffer(b"".join(blobs), np.uint8)
+    got = emul(data, off, flags)
+    _same(got, c_oracle.validate_hash(data, off, flags, True, True), off)
+    clean = sum(1 for b in blobs if not any(j in b for j in junk))
+    assert got["nslow"] <= len(blobs) - 0.9 * clean + (0.2 * len(blobs) if flags else 0)   # padded ASCII strings did not leave it
