@@ -69,6 +69,10 @@ struct kx_engine {
     const float *pend_part = nullptr;
     int pend_splits = 0;
     size_t pend_stride = 0;
+    // instantiated decode-step graphs, reused by later generate calls of the same shape (capture + instantiate
+    // cost about a millisecond of idle GPU per call otherwise); dropped whenever buffers they point to may change
+    struct StepGraph { int B, S, n_new, P; cudaGraphExec_t exec; int64_t launches; };
+    std::vector<StepGraph> step_graphs;
     bool mega = false;
     int mega_grid = 0, mega_max_b = 0;
     MegaGemm mega_g[4];
@@ -84,6 +88,11 @@ struct kx_engine {
 };
 
 namespace {
+
+void drop_step_graphs(kx_engine *e) {
+    for (auto &g : e->step_graphs) cudaGraphExecDestroy(g.exec);
+    e->step_graphs.clear();
+}
 
 int dev_alloc(kx_engine *e, void **p, size_t bytes) {
     KX_CUDA(cudaMalloc(p, bytes));
@@ -522,6 +531,7 @@ extern "C" int64_t kx_engine_p2p_launches(const kx_engine *e) { return e ? e->p2
 
 extern "C" int kx_engine_p2p_import(kx_engine *e, const void *peer_handles /* 2 x 64 bytes */) {
     KX_REQUIRE(e && peer_handles && e->p2p_recv, KX_EINVAL, "kx_engine_p2p_import: export first");
+    drop_step_graphs(e);
     const cudaIpcMemHandle_t *h = reinterpret_cast<const cudaIpcMemHandle_t *>(peer_handles);
     KX_CUDA(cudaIpcOpenMemHandle((void **)&e->p2p_peer_recv, h[0], cudaIpcMemLazyEnablePeerAccess));
     KX_CUDA(cudaIpcOpenMemHandle((void **)&e->p2p_peer_flag, h[1], cudaIpcMemLazyEnablePeerAccess));
@@ -530,6 +540,7 @@ extern "C" int kx_engine_p2p_import(kx_engine *e, const void *peer_handles /* 2 
 
 extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allreduce, void *allgather) {
     KX_REQUIRE(e && comm && allreduce && allgather, KX_EINVAL, "kx_engine_set_collectives: NULL argument");
+    drop_step_graphs(e);
     e->comm = comm;
     e->allreduce = reinterpret_cast<decltype(e->allreduce)>(allreduce);
     e->allgather = reinterpret_cast<decltype(e->allgather)>(allgather);
@@ -542,6 +553,7 @@ extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32
     KX_REQUIRE(n >= 0 && n % KX_KV_PAGE == 0, KX_EINVAL, "kx_engine_set_prefix: length %d is not a multiple of %d", n, KX_KV_PAGE);
     KX_REQUIRE(n < d.max_seq && n <= e->max_tokens, KX_ETOOBIG, "kx_engine_set_prefix: prefix of %d tokens is too long", n);
     KX_REQUIRE(n == 0 || h_tokens, KX_EINVAL, "kx_engine_set_prefix: NULL tokens");
+    drop_step_graphs(e);
     cudaStream_t st = e->stream;
     cudaEvent_t ev;
     KX_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -586,6 +598,8 @@ extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32
 
 extern "C" void kx_engine_destroy(kx_engine *e) {
     if (!e) return;
+    for (auto &g : e->step_graphs) cudaGraphExecDestroy(g.exec);
+    e->step_graphs.clear();
     if (e->p2p_peer_recv) cudaIpcCloseMemHandle(e->p2p_peer_recv);
     if (e->p2p_peer_flag) cudaIpcCloseMemHandle(e->p2p_peer_flag);
     for (void *p : e->owned) cudaFree(p);
@@ -684,28 +698,38 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         return KX_OK;
     };
     int steps_done = 0;
-    if (n_new > 1) {
-        KX_TRY(step_once(d_logits ? d_logits + (size_t)1 * B * d.vocab : nullptr));   // eager: also sets kernel attributes
-        steps_done = 1;
-    }
-    if (n_new > 2) {
-        if (d_logits) {
-            for (int t = 2; t < n_new; ++t) KX_TRY(step_once(d_logits + (size_t)t * B * d.vocab));
+    if (n_new > 1 && d_logits) {
+        for (int t = 1; t < n_new; ++t) KX_TRY(step_once(d_logits + (size_t)t * B * d.vocab));
+        steps_done = n_new - 1;
+    } else if (n_new > 1) {
+        kx_engine::StepGraph *hit = nullptr;
+        for (auto &g : e->step_graphs)
+            if (g.B == B && g.S == S && g.n_new == n_new && g.P == P) hit = &g;
+        if (hit) {                                             // every step replays the cached graph
+            for (int t = 1; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(hit->exec, st));
+            count_launch((int)(hit->launches * (n_new - 1)));
         } else {
-            cudaGraph_t graph = nullptr;
-            cudaGraphExec_t exec = nullptr;
-            const int64_t l0 = kx_launch_count();
-            KX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            int rc = step_once(nullptr);
-            cudaError_t ce = cudaStreamEndCapture(st, &graph);
-            if (rc != KX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
-            KX_CUDA(ce);
-            const int64_t per_step = kx_launch_count() - l0;
-            KX_CUDA(cudaGraphInstantiate(&exec, graph, 0));
-            for (int t = 2; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(exec, st));
-            count_launch((int)(per_step * (n_new - 3)));      // the capture itself was counted once
-            cudaGraphExecDestroy(exec);
-            cudaGraphDestroy(graph);
+            KX_TRY(step_once(nullptr));                        // eager: also sets kernel attributes outside any capture
+            if (n_new > 2) {
+                cudaGraph_t graph = nullptr;
+                cudaGraphExec_t exec = nullptr;
+                const int64_t l0 = kx_launch_count();
+                KX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                int rc = step_once(nullptr);
+                cudaError_t ce = cudaStreamEndCapture(st, &graph);
+                if (rc != KX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+                KX_CUDA(ce);
+                const int64_t per_step = kx_launch_count() - l0;
+                KX_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+                cudaGraphDestroy(graph);
+                for (int t = 2; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(exec, st));
+                count_launch((int)(per_step * (n_new - 3)));  // the capture itself was counted once
+                if (e->step_graphs.size() >= 8) {              // small cache, oldest entry out
+                    cudaGraphExecDestroy(e->step_graphs.front().exec);
+                    e->step_graphs.erase(e->step_graphs.begin());
+                }
+                e->step_graphs.push_back({B, S, n_new, P, exec, per_step});
+            }
         }
         steps_done = n_new - 1;
     }

@@ -18,7 +18,8 @@ def short(n):
     return (m.group(1) + '<' + m.group(2) + '>') if m else n.split('(')[0][-40:]
 
 
-for label, (a, b) in {'prefill': (0, idx[0]), 'decode step': (idx[0], len(data))}.items():
+end = idx[1] if len(idx) > 1 else len(data)            # several steps captured: tabulate the first one
+for label, (a, b) in {'prefill': (0, idx[0]), 'decode step': (idx[0], end)}.items():
     agg = collections.OrderedDict()
     for n, v, g in data[a:b]:
         k = (short(n), g)
