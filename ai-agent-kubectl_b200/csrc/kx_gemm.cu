@@ -468,6 +468,17 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
             const int ab = tile_it & 1;
             if (EPI == EPI_F32) ps.out = reinterpret_cast<float *>(p.out) + (size_t)ks * p.split_stride;
+            // residual epilogue: request the first chunk of residual values before waiting for the accumulator
+            const bool row_ok = arow < p.a_rows;
+            float *orow = reinterpret_cast<float *>(p.out) + (size_t)arow * p.ldo + n0;
+            float4 nxt[8];
+            auto load_chunk = [&](int c) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    nxt[j] = (row_ok && n0 + c + 4 * j < p.b_rows) ? *reinterpret_cast<const float4 *>(orow + c + 4 * j)
+                                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+            };
+            if (EPI == EPI_RESID) load_chunk(0);
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
@@ -488,6 +499,33 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                             if (lane == 0) mbar_arrive(tmem_empty + ab);
                         }
                         if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0);
+                    }
+                }
+            } else if (EPI == EPI_RESID) {
+                // residual accumulate: the fp32 read-modify-write is latency bound (one row segment per thread), so the
+                // residual values of a chunk are requested one chunk ahead -- the first chunk's before the accumulator is
+                // even complete -- and the adds/stores of chunk c overlap the loads of chunk c + 1
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    float v[32];
+                    tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                    tmem_ld_wait();
+                    float4 cur[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
+                    if (c + 32 < BN) load_chunk(c + 32);
+                    else {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tmem_empty + ab);
+                    }
+                    if (row_ok) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (n0 + c + 4 * j >= p.b_rows) break;
+                            cur[j].x += v[4 * j]; cur[j].y += v[4 * j + 1]; cur[j].z += v[4 * j + 2]; cur[j].w += v[4 * j + 3];
+                            *reinterpret_cast<float4 *>(orow + c + 4 * j) = cur[j];
+                        }
                     }
                 }
             } else if (EPI == EPI_ARGMAX) {
