@@ -354,8 +354,10 @@ template <int BN> struct Cfg2 {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 };
 
+constexpr int kPairThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue: two warps per TMEM lane quarter, half of the tile's columns each
+
 template <int BN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBhalf,
                          const GemmParams p, int m_pairs, int n_tiles) {
     using C = Cfg2<BN>;
@@ -383,7 +385,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmBhalf);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 2); }   // empty: both CTAs' MMAs
-        for (int b = 0; b < 2; ++b) { mbar_init(tmem_full + b, 1); mbar_init(tmem_empty + b, 4); }  // 4 epilogue warps
+        for (int b = 0; b < 2; ++b) { mbar_init(tmem_full + b, 1); mbar_init(tmem_empty + b, 8); }  // 8 epilogue warps
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_holder, C::TMEM_COLS);
@@ -459,9 +461,16 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
     } else {
         const int q = warp & 3;
+        const int eg = (warp - 2) >> 2;                        // column half this warp drains: [eg BN/2, (eg + 1) BN/2)
+        const int c_beg = eg * (BN / 2), c_end = c_beg + BN / 2;
         int tile_it = 0;
         asm volatile("griddepcontrol.wait;" ::: "memory");     // the epilogue reads / overwrites buffers earlier kernels used
         GemmParams ps = p;                                     // per-slice output pointer (split-K)
+        auto release_acc = [&](int ab) {                       // this warp has read its last accumulator column of the tile
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + ab);
+        };
         for (int wk = cluster_id; wk < n_work; wk += n_clusters, ++tile_it) {
             const int tile = wk / S, ks = wk - tile * S;
             const int mp = tile / n_tiles, nt = tile - mp * n_tiles;
@@ -478,26 +487,25 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     nxt[j] = (row_ok && n0 + c + 4 * j < p.b_rows) ? *reinterpret_cast<const float4 *>(orow + c + 4 * j)
                                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
             };
-            if (EPI == EPI_RESID) load_chunk(0);
+            if (EPI == EPI_RESID) load_chunk(c_beg);
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
             if (EPI == EPI_QKV_ROPE) {
                 // head by head: the rotate-half partners of a head live hd/2 columns apart in the same row
                 const int hd = p.hd, half = hd >> 1;
+                const int heads = BN / hd, h_mid = (heads + 1) >> 1;        // the two warp groups split the tile's heads
+                const int h_beg = eg ? h_mid * hd : 0, h_end = eg ? BN : h_mid * hd;
+                if (h_beg >= h_end) release_acc(ab);                       // a single head in the tile: nothing for the second group
 #pragma unroll 1
-                for (int h0 = 0; h0 < BN; h0 += hd) {
+                for (int h0 = h_beg; h0 < h_end; h0 += hd) {
 #pragma unroll 1
                     for (int d0 = 0; d0 < half; d0 += 32) {
                         float x1[32], x2[32];
                         tmem_ld_32x32(taddr + h0 + d0, reinterpret_cast<uint32_t(&)[32]>(x1));
                         tmem_ld_32x32(taddr + h0 + half + d0, reinterpret_cast<uint32_t(&)[32]>(x2));
                         tmem_ld_wait();
-                        if (h0 + hd >= BN && d0 + 32 >= half) {            // last read of this accumulator
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(tmem_empty + ab);
-                        }
+                        if (h0 + hd >= h_end && d0 + 32 >= half) release_acc(ab);   // last read of this accumulator
                         if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0);
                     }
                 }
@@ -506,19 +514,15 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 // residual values of a chunk are requested one chunk ahead -- the first chunk's before the accumulator is
                 // even complete -- and the adds/stores of chunk c overlap the loads of chunk c + 1
 #pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+                for (int c = c_beg; c < c_end; c += 32) {
                     float v[32];
                     tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
                     tmem_ld_wait();
                     float4 cur[8];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
-                    if (c + 32 < BN) load_chunk(c + 32);
-                    else {
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(tmem_empty + ab);
-                    }
+                    if (c + 32 < c_end) load_chunk(c + 32);
+                    else release_acc(ab);
                     if (row_ok) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -530,34 +534,28 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 }
             } else if (EPI == EPI_ARGMAX) {
                 // token-major lm_head: this thread's row is a token; scan the tile's vocabulary columns in order
+                // (one part per tile: the first warp group scans all columns, the second only hands the accumulator back)
                 float bv = -INFINITY;
                 int bi = 0x7fffffff;
+                if (eg) release_acc(ab);
 #pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+                for (int c = 0; c < (eg ? 0 : BN); c += 32) {
                     float v[32];
                     tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
                     tmem_ld_wait();
-                    if (c + 32 >= BN) {
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(tmem_empty + ab);
-                    }
+                    if (c + 32 >= BN) release_acc(ab);
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
                         if (n0 + c + j < p.b_rows && v[j] > bv) { bv = v[j]; bi = n0 + c + j; }
                 }
-                if (arow < p.a_rows) reinterpret_cast<int2 *>(p.out)[(size_t)nt * p.ldo + arow] = make_int2(__float_as_int(bv), bi);
+                if (!eg && arow < p.a_rows) reinterpret_cast<int2 *>(p.out)[(size_t)nt * p.ldo + arow] = make_int2(__float_as_int(bv), bi);
             } else {
 #pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+                for (int c = c_beg; c < c_end; c += 32) {
                     float v[32];
                     tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
                     tmem_ld_wait();
-                    if (c + 32 >= BN) {                                     // last read of this accumulator: hand it back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(tmem_empty + ab);
-                    }
+                    if (c + 32 >= c_end) release_acc(ab);                   // last read of this accumulator: hand it back
                     epilogue_chunk<EPI == EPI_ARGMAX ? EPI_F32 : EPI, false>(ps, v, arow, n0 + c, false);
                 }
             }
@@ -597,7 +595,7 @@ int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams 
     if (clusters > m_pairs * n_tiles * pp.splits) clusters = m_pairs * n_tiles * pp.splits;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * clusters);
-    cfg.blockDim = dim3(kGemmThreads);
+    cfg.blockDim = dim3(kPairThreads);
     cfg.dynamicSmemBytes = Cfg2<BN>::SMEM_BYTES;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
