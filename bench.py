@@ -487,7 +487,7 @@ def run_generate(args):
                                f"{total} concurrent requests split over {world} replica(s), {S}-token prompt, "
                                f"{NEW} greedy tokens, byte-level tokenizer",
                    "requests": total, "requests_per_gpu": mine, "prompt_len": S, "new_tokens": NEW,
-                   "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (NCCL all-reduce over NVLink)" if tp > 1 else "") +
+                   "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (decode: all-reduce fused into the GEMM epilogue over NVLink peer memory; prefill: NCCL)" if tp > 1 else "") +
                                    ", no collective between replicas"),
                    "prefix_cached_tokens": PFX,
                    "l2": "weights + KV + activations per step exceed the 126 MB L2 (%.2f GB weights)" % (cfg.decode_weight_bytes() / 1e9),
