@@ -19,6 +19,16 @@ void release_scratch();
 
 inline void count_launch(int k = 1) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
+// Function attributes (dynamic shared memory limit, cluster opt-in) are per device: a process that drives several
+// GPUs (one engine per device behind a ReplicaRouter) has to set them on each.  `first()` is true once per
+// (call site, current device); `done()` records it after the attributes were set.
+struct PerDeviceOnce {
+    std::atomic<uint64_t> mask{0};
+    static int device() { int d = 0; cudaGetDevice(&d); return d & 63; }
+    bool first() const { return !(mask.load(std::memory_order_acquire) & (1ull << device())); }
+    void done() { mask.fetch_or(1ull << device(), std::memory_order_release); }
+};
+
 #define KX_CUDA(call)                                                                        \
     do {                                                                                     \
         cudaError_t e__ = (call);                                                            \

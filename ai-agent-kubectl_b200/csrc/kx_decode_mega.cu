@@ -437,10 +437,10 @@ template <int BN, int HD, int G>
 int launch_mega(const CUtensorMap &xn, const CUtensorMap &at, const CUtensorMap &ml, const MegaParams &p, int grid, cudaStream_t st) {
     using C = MegaCfg<BN, HD>;
     auto kern = kx_decode_mega_kernel<BN, HD, G>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    if (once.first()) {
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        attr_set = true;
+        once.done();
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);

@@ -29,6 +29,7 @@ struct LayerPlan {
 struct kx_engine {
     kx_model_desc d;
     int qkv_dim, q_dim, max_pages, num_pages, max_tokens;
+    int device = 0;                                // the GPU this engine lives on (current device at creation)
     int prefix_len = 0;                            // tokens of shared prefix whose KV is already cached (multiple of 16)
     // decode attention over the shared prefix: per-chunk partial (O, max/sum) of every (sequence, q head)
     float *prefix_o = nullptr, *prefix_ml = nullptr;
@@ -376,6 +377,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     KX_REQUIRE(d.max_seq <= d.max_pos, KX_EINVAL, "kx_engine_create: max_seq exceeds the rope table");
     kx_engine *e = new kx_engine();
     e->d = d;
+    if (cudaGetDevice(&e->device) != cudaSuccess) { delete e; set_error("kx_engine_create: no current CUDA device"); return KX_ECUDA; }
     if (const char *v = getenv("KX_SHARED_PREFIX")) e->share_prefix = v[0] != '0';
     if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
@@ -554,6 +556,7 @@ extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allredu
 
 extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32_t n, void *stream) {
     KX_REQUIRE(e, KX_EINVAL, "kx_engine_set_prefix: NULL engine");
+    KX_CUDA(cudaSetDevice(e->device));
     const kx_model_desc &d = e->d;
     KX_REQUIRE(n >= 0 && n % KX_KV_PAGE == 0, KX_EINVAL, "kx_engine_set_prefix: length %d is not a multiple of %d", n, KX_KV_PAGE);
     KX_REQUIRE(n < d.max_seq && n <= e->max_tokens, KX_ETOOBIG, "kx_engine_set_prefix: prefix of %d tokens is too long", n);
@@ -628,6 +631,7 @@ extern "C" int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max
 extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t B, int32_t S, int32_t n_new,
                                   int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream) {
     KX_REQUIRE(e && h_tokens && h_out, KX_EINVAL, "kx_engine_generate: NULL argument");
+    KX_CUDA(cudaSetDevice(e->device));               // a host thread serving several engines may have another device current
     const kx_model_desc &d = e->d;
     KX_REQUIRE(B >= 1 && B <= d.max_batch, KX_ETOOBIG, "kx_engine_generate: batch %d exceeds max_batch %d", B, d.max_batch);
     const int P = e->prefix_len;

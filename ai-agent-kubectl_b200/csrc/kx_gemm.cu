@@ -571,15 +571,16 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 template <int BN, int EPI>
 int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams &p, cudaStream_t st) {
     auto kern = kx_gemm_bf16_pair_kernel<BN, EPI>;
-    static bool attr_set = false;
-    static int sms = 0;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    static int sms_of[64];
+    if (once.first()) {
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
         int dev = 0;
         KX_CUDA(cudaGetDevice(&dev));
-        KX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        attr_set = true;
+        KX_CUDA(cudaDeviceGetAttribute(&sms_of[dev & 63], cudaDevAttrMultiProcessorCount, dev));
+        once.done();
     }
+    const int sms = sms_of[PerDeviceOnce::device()];
     const int m_pairs = (p.a_rows + 2 * BM - 1) / (2 * BM), n_tiles = (p.b_rows + BN - 1) / BN;
     GemmParams pp = p;
     if (pp.splits > 1) {
@@ -807,11 +808,11 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
 template <int BN, int EPI>
 int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
     auto kern = kx_gemm_bf16_ksplit_kernel<BN, EPI>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce once;
+    if (once.first()) {
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        attr_set = true;
+        once.done();
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
@@ -863,10 +864,10 @@ EncodeTiledFn encode_fn() {
 template <int BN, int EPI, bool SWAP>
 int launch(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams &p, dim3 grid, cudaStream_t st) {
     auto kern = kx_gemm_bf16_kernel<BN, EPI, SWAP>;
-    static bool attr_set = false;   // per instantiation
-    if (!attr_set) {
+    static PerDeviceOnce once;      // per instantiation
+    if (once.first()) {
         KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
-        attr_set = true;
+        once.done();
     }
     kern<<<grid, kGemmThreads, Cfg<BN>::SMEM_BYTES, st>>>(ta, tb, p);
     count_launch();

@@ -885,8 +885,8 @@ int launch_decode_warp(int G, int n_tasks, cudaStream_t st, const __nv_bfloat16 
 #define KX_DECW(GV)                                                                                          \
     case GV: {                                                                                               \
         auto k = attn_decode_warp_kernel<HD, GV, KB, NS>;                                                    \
-        static bool granted = false;   /* first use is the eager decode step, outside any capture */         \
-        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); granted = true; } \
+        static PerDeviceOnce once;     /* first use is the eager decode step, outside any capture */         \
+        if (once.first()) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); once.done(); } \
         KX_CUDA(launch_pdl(k, grid, dim3(128), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, \
                            key0, part_o, part_ml, n_part, n_tasks));                                         \
         break;                                                                                               \
@@ -909,10 +909,11 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
 #define KX_DEC(GV)                                                                                          \
     case GV: {                                                                                              \
         auto k = nw == 8 ? attn_decode_kernel<HD, GV, 8> : attn_decode_kernel<HD, GV, 4>;                   \
-        static size_t granted[2] = {48 * 1024, 48 * 1024};   /* raised outside any capture by the first, eager call */ \
-        if (smem > granted[nw == 8]) {                                                                      \
+        static size_t granted[64][2];  /* per device; raised outside any capture by the first, eager call */    \
+        size_t &have = granted[PerDeviceOnce::device()][nw == 8];                                           \
+        if (smem > 48 * 1024 && smem > have) {                                                              \
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-            granted[nw == 8] = smem;                                                                        \
+            have = smem;                                                                                    \
         }                                                                                                   \
         KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys, key0, part_o, part_ml, n_part)); \
         break;                                                                                              \
@@ -1047,8 +1048,8 @@ int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt
                            (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
     } else if (hd == 128) {
         auto k = attn_prefix_kernel<128>;
-        static bool granted = false;                   // first use is the eager decode step, outside any capture
-        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); granted = true; }
+        static PerDeviceOnce once;                     // first use is the eager decode step, outside any capture
+        if (once.first()) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); once.done(); }
         KX_CUDA(launch_pdl(k, grid, dim3(128), (size_t)5 * 64 * 128 * 2, st, (const __nv_bfloat16 *)qkv, qkv_ld,
                            (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
     } else {
@@ -1068,8 +1069,8 @@ int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const vo
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else if (hd == 128) {
         auto k = attn_prefill_kernel<128>;
-        static bool granted = false;
-        if (!granted) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); granted = true; }
+        static PerDeviceOnce once;
+        if (once.first()) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); once.done(); }
         k<<<grid, 128, 5 * 64 * 128 * 2, st>>>((const __nv_bfloat16 *)qkv, qkv_ld, (__nv_bfloat16 *)out, out_ld,
             (const __nv_bfloat16 *)pages, block_table, max_pages, S, pos0, n_q, n_kv, scale_log2);
     } else {

@@ -66,3 +66,22 @@ def test_tp2_matches_the_oracle(tmp_path, arch):
         err = (logits[t] - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
         assert err <= 1e-2, f"step {t}: logits off by {err:.2e}"
     assert np.array_equal(r[0]["ids"], want_ids.numpy())
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_router_with_two_replicas_in_one_process():
+    """ReplicaRouter over engines on cuda:0 and cuda:1 inside ONE process (kernel attributes are per device, each
+    engine pins its device): the routed result equals what a single replica generates for the same prompts."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine, router
+    head = "You are a Kubernetes CLI specialist. " * 3 + "User Request: "
+    prompts = [head + f"list pods in namespace ns{i % 11}" + "\nKubectl Command:\n" for i in range(24)]
+    single = engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=160, max_new=6, device=0)
+    want = single.generate(prompts)
+    single.close()
+    reps = [engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=160, max_new=6, device=d) for d in (0, 1)]
+    r = router.ReplicaRouter(reps)
+    got = r.generate(prompts)
+    assert got == want
+    assert min(r.routed) > 0 and sum(r.routed) == len(prompts)        # both replicas worked
+    r.close()
