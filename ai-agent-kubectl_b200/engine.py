@@ -292,5 +292,17 @@ class B200Engine(Engine):
 
 
 def default_engine_factory(arch: str) -> Engine:
-    # the service's prompts share the template's instruction text: cache its KV, prefill only the rest
-    return B200Engine(arch, prompt_len=128, auto_prefix=True)
+    """What ``B200ChatModel(...)`` starts when the reference constructs its ``llm`` (app.py:108-117).
+    The service's prompts share the template's instruction text: its KV is cached, only the rest is prefilled.
+    ``KX_DEVICE`` picks the GPU (default 0); ``KX_REPLICAS=n`` starts n engines on GPUs KX_DEVICE .. KX_DEVICE+n-1
+    inside this process behind a ReplicaRouter (hash affinity on the cache key), so one unmodified ``app.py``
+    worker drives the whole box; alternatively run one uvicorn worker per GPU with its own KX_DEVICE."""
+    import os
+    dev0, n = int(os.environ.get("KX_DEVICE", "0")), int(os.environ.get("KX_REPLICAS", "1"))
+
+    def make(device: int) -> Engine:
+        return B200Engine(arch, prompt_len=128, auto_prefix=True, device=device)
+    if n <= 1:
+        return make(dev0)
+    from .router import ReplicaRouter
+    return ReplicaRouter([make(dev0 + i) for i in range(n)])

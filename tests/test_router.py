@@ -85,3 +85,22 @@ def test_bad_arguments():
         router.ReplicaRouter([])
     with pytest.raises(ValueError):
         router.ReplicaRouter([chat_model.CallableEngine(lambda p: p)], policy="random")
+
+
+def test_default_engine_factory_builds_a_router_for_several_replicas(monkeypatch):
+    """KX_REPLICAS / KX_DEVICE steer what the unmodified app.py gets behind ChatOpenAI(...)."""
+    from kubectl_b200 import engine
+    made = []
+
+    class Stub(chat_model.Engine):
+        def __init__(self, arch, **kw):
+            made.append(kw["device"])
+
+    monkeypatch.setattr(engine, "B200Engine", Stub)
+    monkeypatch.setenv("KX_DEVICE", "2")
+    monkeypatch.delenv("KX_REPLICAS", raising=False)
+    assert isinstance(engine.default_engine_factory("qwen2.5-0.5b"), Stub) and made == [2]
+    monkeypatch.setenv("KX_REPLICAS", "3")
+    r = engine.default_engine_factory("qwen2.5-0.5b")
+    assert isinstance(r, router.ReplicaRouter) and made == [2, 2, 3, 4] and len(r.engines) == 3
+    r.close()
