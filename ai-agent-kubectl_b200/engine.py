@@ -262,9 +262,9 @@ class B200Engine(Engine):
         if self.auto_prefix:
             toks = self._with_learned_prefix(prompts)
         else:
-            toks = np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
+            toks = tokenizer.encode_fixed_batch(prompts, self.prompt_len)
         ids, _ = self.gen.generate_ids(toks, self.max_new)
-        return [tokenizer.decode(row) for row in ids]
+        return tokenizer.decode_batch(ids)
 
     def _with_learned_prefix(self, prompts: Sequence[str]) -> np.ndarray:
         """Prefix cache for the service's own template: every prompt the chain renders starts with the
@@ -284,8 +284,8 @@ class B200Engine(Engine):
             self.gen.set_prefix(np.zeros(0, np.int32))
             self._prefix_bytes = b""
         if not n_tok:
-            return np.asarray([tokenizer.encode_fixed(p, self.prompt_len) for p in prompts], np.int32)
-        return np.asarray([tokenizer.encode_suffix(r[len(want):], self.prompt_len) for r in raw], np.int32)
+            return tokenizer.encode_fixed_batch(prompts, self.prompt_len)
+        return tokenizer.encode_suffix_batch([r[len(want):] for r in raw], self.prompt_len)
 
     def close(self):
         self.gen.close()

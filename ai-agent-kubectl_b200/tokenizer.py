@@ -7,6 +7,8 @@ from __future__ import annotations
 
 from typing import List, Sequence
 
+import numpy as np
+
 BOS, EOS = 256, 257
 
 
@@ -43,3 +45,42 @@ def encode_suffix(data: bytes, length: int, pad: int = 32) -> List[int]:
     if len(ids) >= length:
         return ids[len(ids) - length:]
     return [pad] * (length - len(ids)) + ids
+
+
+# ---- batch versions used on the request path (same results as the scalar functions above) ----
+def encode_fixed_batch(texts: Sequence[str], length: int, pad: int = 32) -> np.ndarray:
+    out = np.full((len(texts), length), pad, np.int32)
+    out[:, 0] = BOS
+    for i, t in enumerate(texts):
+        b = np.frombuffer(t.encode("utf-8"), np.uint8)
+        if b.size > length - 1:
+            b = b[b.size - (length - 1):]
+        if b.size:
+            out[i, length - b.size:] = b
+    return out
+
+
+def encode_suffix_batch(datas: Sequence[bytes], length: int, pad: int = 32) -> np.ndarray:
+    out = np.full((len(datas), length), pad, np.int32)
+    for i, d in enumerate(datas):
+        b = np.frombuffer(d, np.uint8)
+        if b.size > length:
+            b = b[b.size - length:]
+        if b.size:
+            out[i, length - b.size:] = b
+    return out
+
+
+def decode_batch(ids: np.ndarray) -> List[str]:
+    ids = np.asarray(ids)
+    is_eos = ids == EOS
+    end = np.where(is_eos.any(axis=1), is_eos.argmax(axis=1), ids.shape[1])
+    low = (ids & 0xFF).astype(np.uint8)
+    bos = ids == BOS
+    out = []
+    for i in range(ids.shape[0]):
+        row = low[i, :end[i]]
+        if bos[i, :end[i]].any():
+            row = row[~bos[i, :end[i]]]
+        out.append(row.tobytes().decode("utf-8", errors="replace"))
+    return out
