@@ -354,17 +354,21 @@ template <int BN> struct Cfg2 {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 };
 
+constexpr int kPairOutStage = 8 * 4096;   // residual epilogue staging (8 epilogue warps x 4 KB), EPI_RESID only
 constexpr int kPairThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue: two warps per TMEM lane quarter, half of the tile's columns each
 
 template <int BN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBhalf,
-                         const GemmParams p, int m_pairs, int n_tiles) {
+                         const __grid_constant__ CUtensorMap tmOut, const GemmParams p, int m_pairs, int n_tiles) {
     using C = Cfg2<BN>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::STAGES * C::STAGE_BYTES);
+    // residual epilogue: one 4 KB staging box (32 rows x 32 fp32, 128 B swizzle) per epilogue warp, after the ring
+    constexpr int kOutStage = EPI == EPI_RESID ? kPairOutStage : 0;
+    uint8_t *out_stage = smem + C::STAGES * C::STAGE_BYTES;
+    uint64_t *full = reinterpret_cast<uint64_t *>(out_stage + kOutStage);
     uint64_t *empty = full + C::STAGES;
     uint64_t *tmem_full = empty + C::STAGES;      // [2]
     uint64_t *tmem_empty = tmem_full + 2;         // [2]
@@ -477,17 +481,6 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
             const int ab = tile_it & 1;
             if (EPI == EPI_F32) ps.out = reinterpret_cast<float *>(p.out) + (size_t)ks * p.split_stride;
-            // residual epilogue: request the first chunk of residual values before waiting for the accumulator
-            const bool row_ok = arow < p.a_rows;
-            float *orow = reinterpret_cast<float *>(p.out) + (size_t)arow * p.ldo + n0;
-            float4 nxt[8];
-            auto load_chunk = [&](int c) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    nxt[j] = (row_ok && n0 + c + 4 * j < p.b_rows) ? *reinterpret_cast<const float4 *>(orow + c + 4 * j)
-                                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-            };
-            if (EPI == EPI_RESID) load_chunk(c_beg);
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
@@ -510,26 +503,29 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     }
                 }
             } else if (EPI == EPI_RESID) {
-                // residual accumulate: the fp32 read-modify-write is latency bound (one row segment per thread), so the
-                // residual values of a chunk are requested one chunk ahead -- the first chunk's before the accumulator is
-                // even complete -- and the adds/stores of chunk c overlap the loads of chunk c + 1
+                // residual accumulate without reading the residual: each warp stages its 32 rows x 32 columns of fp32 in
+                // shared memory (128 B swizzle) and one lane issues a TMA reduce-add of that box; the add happens in the
+                // L2, rows / columns past the matrix edge are clipped by the tensor map.  (A read-modify-write from the
+                // SM -- one row segment per thread -- made K = 2048 tiles epilogue bound: 19 us against 14 us of MMAs.)
+                uint8_t *obuf = out_stage + (warp - 2) * 4096;
+                const int row0 = (2 * mp + (int)rank) * BM + q * 32;
 #pragma unroll 1
                 for (int c = c_beg; c < c_end; c += 32) {
                     float v[32];
                     tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
                     tmem_ld_wait();
-                    float4 cur[8];
+                    if (c + 32 >= c_end) release_acc(ab);
+                    if (lane == 0) bulk_wait_group_read0();               // the previous box has left the staging buffer
+                    __syncwarp();
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
-                    if (c + 32 < c_end) load_chunk(c + 32);
-                    else release_acc(ab);
-                    if (row_ok) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            if (n0 + c + 4 * j >= p.b_rows) break;
-                            cur[j].x += v[4 * j]; cur[j].y += v[4 * j + 1]; cur[j].z += v[4 * j + 2]; cur[j].w += v[4 * j + 3];
-                            *reinterpret_cast<float4 *>(orow + c + 4 * j) = cur[j];
-                        }
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<float4 *>(obuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && row0 < p.a_rows && n0 + c < p.b_rows) {
+                        tma_reduce_add_2d(&tmOut, obuf, n0 + c, row0);
+                        bulk_commit_group();
                     }
                 }
             } else if (EPI == EPI_ARGMAX) {
@@ -562,6 +558,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
     }
 
+    if (EPI == EPI_RESID && warp >= 2 && lane == 0) bulk_wait_group0();   // every reduce-store of this warp has completed
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();                            // nobody leaves while the peer can still reach its smem
@@ -571,10 +568,12 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 template <int BN, int EPI>
 int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams &p, cudaStream_t st) {
     auto kern = kx_gemm_bf16_pair_kernel<BN, EPI>;
+    constexpr int kSmem = Cfg2<BN>::SMEM_BYTES + (EPI == EPI_RESID ? kPairOutStage : 0);
+    static_assert(kSmem <= 232448, "pair kernel shared memory");
     static PerDeviceOnce once;
     static int sms_of[64];
     if (once.first()) {
-        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
+        KX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
         int dev = 0;
         KX_CUDA(cudaGetDevice(&dev));
         KX_CUDA(cudaDeviceGetAttribute(&sms_of[dev & 63], cudaDevAttrMultiProcessorCount, dev));
@@ -597,14 +596,19 @@ int launch_pair(const CUtensorMap &ta, const CUtensorMap &tbh, const GemmParams 
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * clusters);
     cfg.blockDim = dim3(kPairThreads);
-    cfg.dynamicSmemBytes = Cfg2<BN>::SMEM_BYTES;
+    cfg.dynamicSmemBytes = kSmem;
     cfg.stream = st;
+    CUtensorMap tout{};                                 // fp32 view of the residual rows for the TMA reduce-add epilogue
+    if (EPI == EPI_RESID) {
+        const int rc = make_tmap_f32_box32(&tout, pp.out, pp.a_rows, pp.b_rows, pp.ldo);
+        if (rc != KX_OK) return rc;
+    }
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // prologue + first weight tiles overlap the predecessor's tail
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tbh, pp, m_pairs, n_tiles));
+    KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tbh, tout, pp, m_pairs, n_tiles));
     count_launch();
     return KX_OK;
 }
@@ -905,6 +909,24 @@ int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t c
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     KX_REQUIRE(r == CUDA_SUCCESS, KX_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return KX_OK;
+}
+
+// fp32 matrix [rows, cols] (row pitch ld elements) as 32 x 32 boxes with the 128 B swizzle: the residual epilogue's
+// TMA reduce-add destination
+int make_tmap_f32_box32(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    KX_REQUIRE(fn != nullptr, KX_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    KX_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 4) % 16 == 0, KX_EINVAL,
+               "residual matrix must be 16-byte aligned with a row pitch that is a multiple of 16 bytes");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    KX_REQUIRE(r == CUDA_SUCCESS, KX_ECUDA, "cuTensorMapEncodeTiled (fp32) failed with CUresult %d", (int)r);
     return KX_OK;
 }
 
