@@ -303,9 +303,9 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // QKV epilogue with RoPE + KV append for one (row, head, 32-wide half-pair): x1 = columns d0..d0+31 of the
 // head, x2 = columns d0+hd/2.. of the same head (rotate-half partners).  Values are rounded to bf16 after the
 // bias (what the unfused path stores), rotated in fp32 without FMA contraction, rounded again.
-__device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[32], float (&x2)[32], int row, int head, int d0) {
+__device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[32], float (&x2)[32], int row, int head, int d0,
+                                               int pos, int page) {   // position and KV page of the row, looked up by the caller
     const int half = p.hd >> 1;
-    const int pos = __ldg(p.pos + row);
     const int fcol = head * p.hd + d0;
     __nv_bfloat16 *dst1, *dst2;
     const bool is_v = head >= p.n_q + p.n_kv;
@@ -313,7 +313,6 @@ __device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[
         dst1 = reinterpret_cast<__nv_bfloat16 *>(p.out) + (size_t)row * p.ldo + fcol;
     } else {
         const int kvh = head - p.n_q - (is_v ? p.n_kv : 0);
-        const int page = __ldg(p.block_table + (size_t)__ldg(p.seq + row) * p.max_pages + pos / KX_KV_PAGE);
         dst1 = reinterpret_cast<__nv_bfloat16 *>(p.kv_pages) +
                (((size_t)page * 2 + (is_v ? 1 : 0)) * p.n_kv + kvh) * KX_KV_PAGE * p.hd + (size_t)(pos % KX_KV_PAGE) * p.hd + d0;
     }
@@ -323,6 +322,7 @@ __device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[
 #pragma unroll
     for (int j = 0; j < 32; j += 2) {
         float a[2], b[2];
+        const float4 c2 = is_v ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(reinterpret_cast<const float4 *>(cs + j));   // (cos, sin) of two dims
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
             const float bias1 = p.bias ? p.bias[fcol + j + t] : 0.f, bias2 = p.bias ? p.bias[fcol + half + j + t] : 0.f;
@@ -330,9 +330,9 @@ __device__ __forceinline__ void qkv_rope_store(const GemmParams &p, float (&x1)[
             const float v2 = __bfloat162float(__float2bfloat16(x2[j + t] + bias2));
             if (is_v) { a[t] = v1; b[t] = v2; }
             else {
-                const float2 c = __ldg(cs + j + t);
-                a[t] = __fsub_rn(__fmul_rn(v1, c.x), __fmul_rn(v2, c.y));
-                b[t] = __fadd_rn(__fmul_rn(v2, c.x), __fmul_rn(v1, c.y));
+                const float cx = t ? c2.z : c2.x, cy = t ? c2.w : c2.y;
+                a[t] = __fsub_rn(__fmul_rn(v1, cx), __fmul_rn(v2, cy));
+                b[t] = __fadd_rn(__fmul_rn(v2, cx), __fmul_rn(v1, cy));
             }
         }
         o1[j >> 1] = pack_bf16(a[0], a[1]);
@@ -481,6 +481,15 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int arow = (2 * mp + (int)rank) * BM + q * 32 + lane, n0 = nt * BN;
             const int ab = tile_it & 1;
             if (EPI == EPI_F32) ps.out = reinterpret_cast<float *>(p.out) + (size_t)ks * p.split_stride;
+            // QKV epilogue: the row's position, KV page and rope row do not depend on the accumulator -- fetch them (and
+            // pull the cos/sin row towards L1) while the MMAs of this tile are still running
+            int row_pos = 0, row_page = 0;
+            if (EPI == EPI_QKV_ROPE && arow < p.a_rows) {
+                row_pos = __ldg(p.pos + arow);
+                row_page = __ldg(p.block_table + (size_t)__ldg(p.seq + arow) * p.max_pages + row_pos / KX_KV_PAGE);
+                const char *cs_row = reinterpret_cast<const char *>(p.rope) + (size_t)row_pos * (p.hd >> 1) * 8;
+                for (int o = 0; o < (p.hd >> 1) * 8; o += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(cs_row + o));
+            }
             mbar_wait(tmem_full + ab, (tile_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN);
@@ -499,7 +508,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                         tmem_ld_32x32(taddr + h0 + half + d0, reinterpret_cast<uint32_t(&)[32]>(x2));
                         tmem_ld_wait();
                         if (h0 + hd >= h_end && d0 + 32 >= half) release_acc(ab);   // last read of this accumulator
-                        if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0);
+                        if (arow < p.a_rows && n0 + h0 < p.b_rows) qkv_rope_store(p, x1, x2, arow, (n0 + h0) / hd, d0, row_pos, row_page);
                     }
                 }
             } else if (EPI == EPI_RESID) {
