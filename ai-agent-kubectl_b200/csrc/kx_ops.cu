@@ -113,9 +113,14 @@ rmsnorm_row_kernel(float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, _
             // pending split-K partial sums of the preceding row-parallel projection: residual += their sum,
             // slices added in index order (deterministic), and the residual row is written back
             float4 a = *reinterpret_cast<const float4 *>(part + src + i);
-            for (int s = 1; s < splits; ++s) {
-                const float4 c = *reinterpret_cast<const float4 *>(part + (size_t)s * split_stride + src + i);
-                a.x += c.x; a.y += c.y; a.z += c.z; a.w += c.w;
+            for (int s0 = 1; s0 < splits; s0 += 4) {           // four slices' loads in flight, added in slice order
+                float4 c[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (s0 + j < splits) c[j] = *reinterpret_cast<const float4 *>(part + (size_t)(s0 + j) * split_stride + src + i);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (s0 + j < splits) { a.x += c[j].x; a.y += c[j].y; a.z += c[j].z; a.w += c[j].w; }
             }
             v[u].x += a.x; v[u].y += a.y; v[u].z += a.z; v[u].w += a.w;
             *reinterpret_cast<float4 *>(xr + i) = v[u];
