@@ -437,6 +437,11 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         LayerPlan &L = e->layers[i];
         L.w = w->layers[i];
         KX_E(dev_alloc(e, &L.kv_pages, page_bytes * e->num_pages));
+        // the CTA-pair GEMM multicasts weight tiles: they have to live on this GPU
+        KX_E(require_local_device_memory(L.w.wqkv, "kx_engine_create: wqkv"));
+        KX_E(require_local_device_memory(L.w.wo, "kx_engine_create: wo"));
+        KX_E(require_local_device_memory(L.w.wgu, "kx_engine_create: wgu"));
+        KX_E(require_local_device_memory(L.w.wd, "kx_engine_create: wd"));
         KX_E(make_tmap_bf16_2d(&L.wqkv, L.w.wqkv, e->qkv_dim, d.hidden, d.hidden, 128));
         KX_E(make_tmap_bf16_2d(&L.wo, L.w.wo, d.hidden, e->q_dim, e->q_dim, 128));
         KX_E(make_tmap_bf16_2d(&L.wgu, L.w.wgu, 2 * d.inter, d.hidden, d.hidden, 128));
@@ -449,6 +454,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
             KX_E(make_tmap_bf16_2d(&L.wd_h[j], L.w.wd, d.hidden, d.inter, d.inter, box));
         }
     }
+    KX_E(require_local_device_memory(e->lm_head, "kx_engine_create: lm_head"));
     KX_E(make_tmap_bf16_2d(&e->lm_head_map, e->lm_head, d.vocab, d.hidden, d.hidden, 128));
     KX_E(make_tmap_bf16_2d(&e->lm_head_h[0], e->lm_head, d.vocab, d.hidden, d.hidden, 64));
     KX_E(make_tmap_bf16_2d(&e->lm_head_h[1], e->lm_head, d.vocab, d.hidden, d.hidden, 128));

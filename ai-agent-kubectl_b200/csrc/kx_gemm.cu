@@ -939,6 +939,20 @@ int make_tmap_f32_box32(CUtensorMap *out, const void *ptr, int64_t rows, int64_t
     return KX_OK;
 }
 
+// The CTA-pair kernel fetches its B operand (the weights) with TMA multicast.  TMA multicast loads here read only
+// this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU: an operand that is
+// not plain device memory of the current device (a peer allocation, an IPC mapping, managed memory) is refused.
+int require_local_device_memory(const void *ptr, const char *what) {
+    cudaPointerAttributes a{};
+    int dev = -1;
+    KX_CUDA(cudaGetDevice(&dev));
+    const cudaError_t e = cudaPointerGetAttributes(&a, ptr);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    KX_REQUIRE(e == cudaSuccess && a.type == cudaMemoryTypeDevice && a.device == dev, KX_EINVAL,
+               "%s must be device memory allocated on the current GPU (device %d)", what, dev);
+    return KX_OK;
+}
+
 // Prefill tile width: 256-wide pair tiles when the feature count fills them, else 128-wide.
 int gemm_pair_bn(int64_t a_rows, int64_t b_rows) {
     if (a_rows < 256) return 0;                       // too few rows for a CTA pair: single-CTA kernel
@@ -1026,6 +1040,8 @@ extern "C" int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const 
     if (rc != KX_OK) return rc;
     const int pbn = swap ? 0 : gemm_pair_bn(a_rows, b_rows);
     if (pbn) {                                        // prefill: persistent CTA-pair kernel
+        rc = require_local_device_memory(d_b, "kx_gemm_bf16: the B operand of the token-major kernel");
+        if (rc != KX_OK) return rc;
         p.splits = 1;                                 // (its split-K mode writes per-slice partials: engine-internal)
         rc = make_tmap_bf16_2d(&tb, d_b, b_rows, k, ldb, pbn / 2);
         if (rc != KX_OK) return rc;

@@ -45,6 +45,7 @@ struct GemmParams {
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);
 int make_tmap_f32_box32(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld);   // residual rows, TMA reduce-add
+int require_local_device_memory(const void *ptr, const char *what);   // operands that are loaded with TMA multicast
 int gemm_pick_bn(int swap, int64_t b_rows);
 int gemm_pair_bn(int64_t a_rows, int64_t b_rows);   // 0 = use the single-CTA kernel
 int gemm_launch_pair(const CUtensorMap &ta, const CUtensorMap &tb_half, const GemmParams &p, int bn, cudaStream_t st);
