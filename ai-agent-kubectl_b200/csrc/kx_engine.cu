@@ -34,6 +34,8 @@ struct kx_engine {
     // decode attention over the shared prefix: per-chunk partial (O, max/sum) of every (sequence, q head)
     float *prefix_o = nullptr, *prefix_ml = nullptr;
     size_t prefix_rows = 0;                        // capacity in (chunk, sequence, head) rows
+    bool attn_tc = false;                          // KX_ATTN_TC=1: prefill attention on tcgen05 (kx_attn_tc.cu), head_dim 64
+    int64_t attn_tc_launches = 0;
     bool share_prefix = true;                      // KX_SHARED_PREFIX=0: every sequence re-reads the prefix (for A/B timing)
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
@@ -283,6 +285,11 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         if (!fused_rope)
             KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
                                   d.n_q, d.n_kv, d.head_dim, st));
+        if (e->attn_tc && d.head_dim == 64 && pos0 == 0) {
+            ++e->attn_tc_launches;
+            KX_TRY(op_attn_prefill_tc(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->num_pages,
+                                      e->block_table + (size_t)b0 * e->max_pages, e->max_pages, nb, S, d.n_q, d.n_kv, st));
+        } else
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, pos0, d.n_q, d.n_kv, d.head_dim, st));
     }
@@ -379,6 +386,7 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     e->d = d;
     if (cudaGetDevice(&e->device) != cudaSuccess) { delete e; set_error("kx_engine_create: no current CUDA device"); return KX_ECUDA; }
     if (const char *v = getenv("KX_SHARED_PREFIX")) e->share_prefix = v[0] != '0';
+    if (const char *v = getenv("KX_ATTN_TC")) e->attn_tc = v[0] == '1';
     if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
     e->q_dim = d.n_q * d.head_dim;
@@ -624,6 +632,8 @@ extern "C" void kx_engine_destroy(kx_engine *e) {
 extern "C" int64_t kx_engine_device_bytes(const kx_engine *e) { return e ? e->device_bytes : 0; }
 
 extern "C" int64_t kx_engine_mega_launches(const kx_engine *e) { return e ? e->mega_launches : 0; }
+
+extern "C" int64_t kx_engine_attn_tc_launches(const kx_engine *e) { return e ? e->attn_tc_launches : 0; }
 
 extern "C" int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max_pairs) {
     KX_REQUIRE(e && h_pairs, KX_EINVAL, "kx_engine_mega_trace: NULL argument");

@@ -46,6 +46,7 @@ _lib.declare("kx_engine_p2p_export", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_import", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_launches", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_mega_launches", ctypes.c_int64, [c_void_p])
+_lib.declare("kx_engine_attn_tc_launches", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_mega_trace", ctypes.c_int, [c_void_p, c_void_p, ctypes.c_int])
 _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
@@ -190,6 +191,10 @@ class Generator:
     def mega_launches(self) -> int:
         """Decode steps enqueued as the single persistent kernel so far."""
         return int(_lib.lib().kx_engine_mega_launches(self._h))
+
+    def attn_tc_launches(self) -> int:
+        """Prefill attention launches that took the tcgen05 kernel (KX_ATTN_TC=1) so far."""
+        return int(_lib.lib().kx_engine_attn_tc_launches(self._h))
 
     def mega_trace(self, max_pairs: int = 1024):
         """Diagnostic (KX_MEGA_TRACE=1): [(tag, ns)] recorded by CTA 0 of the persistent kernel in the last step."""

@@ -96,6 +96,23 @@ def test_persistent_decode_kernel(arch, B, S, monkeypatch):
     _check(arch, B=B, S=S, n_new=6, expect_mega=True)
 
 
+@pytest.mark.parametrize("B,S", [(64, 256), (3, 300), (5, 70), (2, 128)])
+def test_tcgen05_prefill_attention(B, S, monkeypatch):
+    """KX_ATTN_TC=1: causal prefill attention as tcgen05 MMAs (S = Q K^T and O = P V in TMEM, V consumed MN-major from
+    the paged layout); same parity bar as the mma.sync kernel, prompts that are not a multiple of the 128-row tile."""
+    monkeypatch.setenv("KX_ATTN_TC", "1")
+    cfg, gen, ref_emu, _ = _setup("tiny-qwen2", 3, B, S, 6)
+    toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(21))
+    ids, logits = gen.generate_ids(toks.numpy().astype(np.int32), 6, want_logits=True)
+    assert gen.attn_tc_launches() > 0
+    want_ids, want_logits = ref_emu.generate(toks, 6, return_logits=True)
+    for t in range(6):
+        err = (logits[t].cpu() - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
+        assert err <= 1e-2, f"step {t}: {err:.2e}"
+    assert np.array_equal(ids, want_ids.numpy())
+    gen.close()
+
+
 def test_config3_shape_on_tiny_model():
     _check("tiny-qwen2", B=64, S=256, n_new=32)
 
