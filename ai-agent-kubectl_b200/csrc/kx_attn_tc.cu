@@ -13,7 +13,8 @@
 //
 // Roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer, warps 2-5 = softmax
 // (TMEM lane quarter = warp % 4).  For head_dim 64 without a cached prefix; everything else takes the
-// mma.sync kernel in kx_ops.cu.  Opt-in (KX_ATTN_TC=1): correct, not yet faster.
+// mma.sync kernel in kx_ops.cu (KX_ATTN_TC=0 forces that kernel everywhere).  Persistent: two CTAs per SM walk
+// the (sequence, head, query block) items, barrier parities run on a tile counter that continues across items.
 #include <cuda_bf16.h>
 #include "kx_common.cuh"
 #include "kx_sm100.cuh"
@@ -57,7 +58,7 @@ __device__ __forceinline__ uint32_t pack2bf(float a, float b) {
 __global__ void __launch_bounds__(192, 2)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                        __nv_bfloat16 *__restrict__ out, int out_ld, const int *__restrict__ block_table, int max_pages,
-                       int S, int n_q, int n_kv, float scale_log2) {
+                       int S, int n_q, int n_kv, float scale_log2, int n_qb, int n_items) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
@@ -66,10 +67,15 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(bar + B_COUNT);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qb = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
-    const int kvh = head / (n_q / n_kv);
-    const int n_tiles = qb + 1;                                 // causal: key tiles 0 .. qb
-    const int *bt = block_table + (size_t)b * max_pages;
+    // persistent: CTA c takes work items c, c + gridDim.x, ...; item -> (sequence, head, query block), the long
+    // (late) query blocks first.  Barrier parities run on a tile counter that continues across items, so the
+    // next item's Q and first K tile are fetched while the current item is still in its last softmax.
+    auto item_of = [&](int w, int &b, int &head, int &qb) {
+        qb = n_qb - 1 - w / (n_q * (n_items / (n_q * n_qb)));
+        const int rest = w % (n_q * (n_items / (n_q * n_qb)));
+        b = rest / n_q;
+        head = rest - b * n_q;
+    };
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmQ);
@@ -86,18 +92,26 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_expect_tx(bar + B_QFULL, kTile);
-            tma_load_2d(Qs, &tmQ, bar + B_QFULL, head * kHD, b * S + qb * kQ);
-            for (int j = 0; j < n_tiles; ++j) {
-                // K tile j: free once the S MMAs of tile j-1 have completed; V tile j: once the PV MMAs of j-1 have
-                if (j > 0) mbar_wait(bar + B_SDONE, (j - 1) & 1);
+            int t = 0;                                           // tiles issued so far by this CTA
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+            int b, head, qb;
+            item_of(w, b, head, qb);
+            const int kvh = head / (n_q / n_kv), n_tiles = qb + 1;   // causal: key tiles 0 .. qb
+            const int *bt = block_table + (size_t)b * max_pages;
+            for (int j = 0; j < n_tiles; ++j, ++t) {
+                // K tile (and a new item's Q): free once the S MMAs of the previous tile have completed; V: once its PV MMAs have
+                if (t > 0) mbar_wait(bar + B_SDONE, (t - 1) & 1);
+                if (j == 0) {
+                    mbar_expect_tx(bar + B_QFULL, kTile);
+                    tma_load_2d(Qs, &tmQ, bar + B_QFULL, head * kHD, b * S + qb * kQ);
+                }
                 mbar_expect_tx(bar + B_KFULL, kTile);
                 for (int i = 0; i < kKeys / kPage; ++i) {
                     int pi = (j * kKeys) / kPage + i;
                     if (pi >= max_pages) pi = max_pages - 1;     // keys past the sequence: masked anyway
                     tma_load_2d(Ks + i * kPage * kHD * 2, &tmKV, bar + B_KFULL, 0, ((bt[pi] * 2 + 0) * n_kv + kvh) * kPage);
                 }
-                if (j > 0) mbar_wait(bar + B_ODONE, (j - 1) & 1);
+                if (t > 0) mbar_wait(bar + B_ODONE, (t - 1) & 1);
                 mbar_expect_tx(bar + B_VFULL, kTile);
                 for (int i = 0; i < kKeys / kPage; ++i) {
                     int pi = (j * kKeys) / kPage + i;
@@ -105,23 +119,29 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     tma_load_2d(Vs + i * kPage * kHD * 2, &tmKV, bar + B_VFULL, 0, ((bt[pi] * 2 + 1) * n_kv + kvh) * kPage);
                 }
             }
+            }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc_s = idesc_bf16(kQ, kKeys, false), idesc_o = idesc_bf16(kQ, kHD, true);
             const uint32_t q_u = base, k_u = q_u + kTile, v_u = k_u + kTile, p_u = v_u + kTile;
-            mbar_wait(bar + B_QFULL, 0);
-            for (int j = 0; j < n_tiles; ++j) {
-                mbar_wait(bar + B_KFULL, j & 1);
-                if (j > 0) mbar_wait(bar + B_SFREE, (j - 1) & 1);           // the softmax threads have read S of tile j-1
+            int t = 0, it = 0;
+            for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+            int b, head, qb;
+            item_of(w, b, head, qb);
+            const int n_tiles = qb + 1;
+            mbar_wait(bar + B_QFULL, it & 1);
+            for (int j = 0; j < n_tiles; ++j, ++t) {
+                mbar_wait(bar + B_KFULL, t & 1);
+                if (t > 0) mbar_wait(bar + B_SFREE, (t - 1) & 1);           // the softmax threads have read S of the previous tile
                 tc_fence_after();
                 const uint64_t dq = umma_desc_sw128(q_u), dk = umma_desc_sw128(k_u);
 #pragma unroll
                 for (int k = 0; k < kHD / 16; ++k) umma_bf16(tmem_s, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                 umma_commit(bar + B_SDONE);
-                mbar_wait(bar + B_PFULL, j & 1);                            // P of tile j is in shared memory
-                mbar_wait(bar + B_VFULL, j & 1);
-                if (j > 0) mbar_wait(bar + B_OFREE, (j - 1) & 1);           // O_j-1 has been read out of TMEM
+                mbar_wait(bar + B_PFULL, t & 1);                            // P of this tile is in shared memory
+                mbar_wait(bar + B_VFULL, t & 1);
+                if (t > 0) mbar_wait(bar + B_OFREE, (t - 1) & 1);           // the previous O tile has been read out of TMEM
                 tc_fence_after();
 #pragma unroll
                 for (int k = 0; k < kKeys / 16; ++k) {
@@ -133,18 +153,24 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                 }
                 umma_commit(bar + B_ODONE);
             }
+            }
         }
     } else {
         // ================= softmax: one thread per query row =================
         const int q = warp & 3, r = q * 32 + lane;
-        const int qpos = qb * kQ + r;
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        int t = 0;
+        for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+        int b, head, qb;
+        item_of(w, b, head, qb);
+        const int n_tiles = qb + 1;
+        const int qpos = qb * kQ + r;
         float o[kHD];
 #pragma unroll
         for (int i = 0; i < kHD; ++i) o[i] = 0.f;
         float m = -INFINITY, l = 0.f;
-        for (int j = 0; j < n_tiles; ++j) {
-            mbar_wait(bar + B_SDONE, j & 1);
+        for (int j = 0; j < n_tiles; ++j, ++t) {
+            mbar_wait(bar + B_SDONE, t & 1);
             tc_fence_after();
             const int klim = (j == qb) ? qpos - j * kKeys : kKeys;          // keys 0 .. klim of this tile are visible (causal)
             float mx = m;
@@ -187,7 +213,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             fence_proxy_async_smem();                                       // P: generic-proxy writes -> async-proxy (MMA) reads
             __syncwarp();
             if (lane == 0) mbar_arrive(bar + B_PFULL);
-            mbar_wait(bar + B_ODONE, j & 1);                                // O_j = P V is in TMEM
+            mbar_wait(bar + B_ODONE, t & 1);                                // O_j = P V is in TMEM
             tc_fence_after();
 #pragma unroll
             for (int c = 0; c < kHD; c += 32) {
@@ -208,6 +234,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             for (int i = 0; i < kHD; i += 8)
                 *reinterpret_cast<uint4 *>(orow + i) = make_uint4(pack2bf(o[i] * inv, o[i + 1] * inv), pack2bf(o[i + 2] * inv, o[i + 3] * inv),
                                                                  pack2bf(o[i + 4] * inv, o[i + 5] * inv), pack2bf(o[i + 6] * inv, o[i + 7] * inv));
+        }
         }
     }
     tc_fence_before();
@@ -231,8 +258,14 @@ int op_attn_prefill_tc(const void *qkv, int qkv_ld, void *out, int out_ld, const
         once.done();
     }
     const float scale_log2 = (1.0f / sqrtf((float)kHD)) * 1.4426950408889634f;
-    dim3 grid((S + kQ - 1) / kQ, n_q, B);
-    attn_prefill_tc_kernel<<<grid, 192, kSmem, st>>>(tq, tkv, (__nv_bfloat16 *)out, out_ld, block_table, max_pages, S, n_q, n_kv, scale_log2);
+    const int n_qb = (S + kQ - 1) / kQ, n_items = n_qb * n_q * B;
+    static int sms_of[64];
+    int dev = 0;
+    KX_CUDA(cudaGetDevice(&dev));
+    if (!sms_of[dev & 63]) KX_CUDA(cudaDeviceGetAttribute(&sms_of[dev & 63], cudaDevAttrMultiProcessorCount, dev));
+    const int grid = n_items < 2 * sms_of[dev & 63] ? n_items : 2 * sms_of[dev & 63];     // two CTAs per SM
+    attn_prefill_tc_kernel<<<grid, 192, kSmem, st>>>(tq, tkv, (__nv_bfloat16 *)out, out_ld, block_table, max_pages, S, n_q, n_kv,
+                                                     scale_log2, n_qb, n_items);
     count_launch();
     KX_CUDA(cudaGetLastError());
     return KX_OK;

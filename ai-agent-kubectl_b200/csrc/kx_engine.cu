@@ -34,7 +34,7 @@ struct kx_engine {
     // decode attention over the shared prefix: per-chunk partial (O, max/sum) of every (sequence, q head)
     float *prefix_o = nullptr, *prefix_ml = nullptr;
     size_t prefix_rows = 0;                        // capacity in (chunk, sequence, head) rows
-    bool attn_tc = false;                          // KX_ATTN_TC=1: prefill attention on tcgen05 (kx_attn_tc.cu), head_dim 64
+    bool attn_tc = true;                           // prefill attention on tcgen05 (kx_attn_tc.cu) for head_dim 64; KX_ATTN_TC=0: mma.sync kernel
     int64_t attn_tc_launches = 0;
     bool share_prefix = true;                      // KX_SHARED_PREFIX=0: every sequence re-reads the prefix (for A/B timing)
     std::vector<LayerPlan> layers;
@@ -445,6 +445,9 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         LayerPlan &L = e->layers[i];
         L.w = w->layers[i];
         KX_E(dev_alloc(e, &L.kv_pages, page_bytes * e->num_pages));
+        // Zeroed once: the tcgen05 prefill kernel multiplies whole 128-key V tiles by P, and keys past the end of a
+        // sequence get P = 0 exactly -- which only cancels finite values (0 x NaN from never-written memory is NaN).
+        if (cudaMemset(L.kv_pages, 0, page_bytes * e->num_pages) != cudaSuccess) return fail(KX_ECUDA);
         // the CTA-pair GEMM multicasts weight tiles: they have to live on this GPU
         KX_E(require_local_device_memory(L.w.wqkv, "kx_engine_create: wqkv"));
         KX_E(require_local_device_memory(L.w.wo, "kx_engine_create: wo"));

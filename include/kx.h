@@ -243,9 +243,9 @@ int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the
  * enqueued that way so far (0: the per-layer kernels were used).
  */
 int64_t kx_engine_mega_launches(const kx_engine *e);
-/* Experimental, opt-in with KX_ATTN_TC=1 at engine creation: prefill attention for head_dim 64 without a cached
- * prefix runs on tcgen05 tensor cores (csrc/kx_attn_tc.cu) instead of the mma.sync kernel.  Parity-tested; same
- * speed as the default today.  Returns how many attention launches took that kernel so far. */
+/* Prefill attention for head_dim 64 without a cached prefix runs on tcgen05 tensor cores (csrc/kx_attn_tc.cu);
+ * other shapes, and every shape with KX_ATTN_TC=0 in the environment at engine creation, take the mma.sync
+ * kernel.  Returns how many attention launches took the tcgen05 kernel so far. */
 int64_t kx_engine_attn_tc_launches(const kx_engine *e);
 /* Diagnostic: with KX_MEGA_TRACE=1 in the environment at creation, CTA 0 of the persistent kernel records
  * (tag, globaltimer ns) pairs at its phase barriers (tag = 2 * phase on arrival, 2 * phase + 1 when the wait

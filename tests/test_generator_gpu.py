@@ -98,9 +98,9 @@ def test_persistent_decode_kernel(arch, B, S, monkeypatch):
 
 @pytest.mark.parametrize("B,S", [(64, 256), (3, 300), (5, 70), (2, 128)])
 def test_tcgen05_prefill_attention(B, S, monkeypatch):
-    """KX_ATTN_TC=1: causal prefill attention as tcgen05 MMAs (S = Q K^T and O = P V in TMEM, V consumed MN-major from
+    """Causal prefill attention as tcgen05 MMAs (S = Q K^T and O = P V in TMEM, V consumed MN-major from
     the paged layout); same parity bar as the mma.sync kernel, prompts that are not a multiple of the 128-row tile."""
-    monkeypatch.setenv("KX_ATTN_TC", "1")
+    monkeypatch.delenv("KX_ATTN_TC", raising=False)
     cfg, gen, ref_emu, _ = _setup("tiny-qwen2", 3, B, S, 6)
     toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(21))
     ids, logits = gen.generate_ids(toks.numpy().astype(np.int32), 6, want_logits=True)
