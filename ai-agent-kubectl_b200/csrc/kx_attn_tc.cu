@@ -12,7 +12,7 @@
 // other's MMAs; inside a CTA the K tile of step j+1 is fetched while step j is in its softmax.
 //
 // Roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer, warps 2-5 = softmax
-// (TMEM lane quarter = warp % 4).  For head_dim 64 without a cached prefix; everything else takes the
+// (TMEM lane quarter = warp % 4).  For head_dim 64, with or without a cached prefix; head_dim 128 takes the
 // mma.sync kernel in kx_ops.cu (KX_ATTN_TC=0 forces that kernel everywhere).  Persistent: two CTAs per SM walk
 // the (sequence, head, query block) items, barrier parities run on a tile counter that continues across items.
 #include <cuda_bf16.h>
@@ -58,7 +58,7 @@ __device__ __forceinline__ uint32_t pack2bf(float a, float b) {
 __global__ void __launch_bounds__(192, 2)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                        __nv_bfloat16 *__restrict__ out, int out_ld, const int *__restrict__ block_table, int max_pages,
-                       int S, int n_q, int n_kv, float scale_log2, int n_qb, int n_items) {
+                       int S, int pos0, int n_q, int n_kv, float scale_log2, int n_qb, int n_items) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t *smem = smem_raw + (base - smem_u32(smem_raw));
@@ -96,7 +96,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
             int b, head, qb;
             item_of(w, b, head, qb);
-            const int kvh = head / (n_q / n_kv), n_tiles = qb + 1;   // causal: key tiles 0 .. qb
+            const int kvh = head / (n_q / n_kv), n_tiles = (pos0 + (qb + 1) * kQ + kKeys - 1) / kKeys;   // causal: keys 0 .. pos0 + (qb+1) 128 - 1
             const int *bt = block_table + (size_t)b * max_pages;
             for (int j = 0; j < n_tiles; ++j, ++t) {
                 // K tile (and a new item's Q): free once the S MMAs of the previous tile have completed; V: once its PV MMAs have
@@ -129,7 +129,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
             int b, head, qb;
             item_of(w, b, head, qb);
-            const int n_tiles = qb + 1;
+            const int n_tiles = (pos0 + (qb + 1) * kQ + kKeys - 1) / kKeys;
             mbar_wait(bar + B_QFULL, it & 1);
             for (int j = 0; j < n_tiles; ++j, ++t) {
                 mbar_wait(bar + B_KFULL, t & 1);
@@ -163,8 +163,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
         int b, head, qb;
         item_of(w, b, head, qb);
-        const int n_tiles = qb + 1;
-        const int qpos = qb * kQ + r;
+        const int n_tiles = (pos0 + (qb + 1) * kQ + kKeys - 1) / kKeys;
+        const int qpos = qb * kQ + r;                                   // row inside the sequence's new tokens; absolute position pos0 + qpos
         float o[kHD];
 #pragma unroll
         for (int i = 0; i < kHD; ++i) o[i] = 0.f;
@@ -172,7 +172,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         for (int j = 0; j < n_tiles; ++j, ++t) {
             mbar_wait(bar + B_SDONE, t & 1);
             tc_fence_after();
-            const int klim = (j == qb) ? qpos - j * kKeys : kKeys;          // keys 0 .. klim of this tile are visible (causal)
+            const int klim = pos0 + qpos - j * kKeys;                       // keys 0 .. klim of this tile are visible (causal; >= 127: all)
             float mx = m;
 #pragma unroll 1
             for (int c = 0; c < kKeys; c += 32) {                           // pass 1: row maximum
@@ -244,9 +244,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
 
 }  // namespace
 
-// head_dim 64, no cached prefix (pos0 = 0).  `pages` is one layer's page pool of `num_pages` pages.
+// head_dim 64; the S new tokens of every sequence sit at positions pos0 .. pos0 + S - 1 behind pos0 cached keys.
+// `pages` is one layer's page pool of `num_pages` pages.
 int op_attn_prefill_tc(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, int num_pages,
-                       const int *block_table, int max_pages, int B, int S, int n_q, int n_kv, cudaStream_t st) {
+                       const int *block_table, int max_pages, int B, int S, int pos0, int n_q, int n_kv, cudaStream_t st) {
     CUtensorMap tq, tkv;
     int rc = make_tmap_bf16_2d(&tq, qkv, (int64_t)B * S, qkv_ld, qkv_ld, kQ);
     if (rc != KX_OK) return rc;
@@ -264,7 +265,7 @@ int op_attn_prefill_tc(const void *qkv, int qkv_ld, void *out, int out_ld, const
     KX_CUDA(cudaGetDevice(&dev));
     if (!sms_of[dev & 63]) KX_CUDA(cudaDeviceGetAttribute(&sms_of[dev & 63], cudaDevAttrMultiProcessorCount, dev));
     const int grid = n_items < 2 * sms_of[dev & 63] ? n_items : 2 * sms_of[dev & 63];     // two CTAs per SM
-    attn_prefill_tc_kernel<<<grid, 192, kSmem, st>>>(tq, tkv, (__nv_bfloat16 *)out, out_ld, block_table, max_pages, S, n_q, n_kv,
+    attn_prefill_tc_kernel<<<grid, 192, kSmem, st>>>(tq, tkv, (__nv_bfloat16 *)out, out_ld, block_table, max_pages, S, pos0, n_q, n_kv,
                                                      scale_log2, n_qb, n_items);
     count_launch();
     KX_CUDA(cudaGetLastError());

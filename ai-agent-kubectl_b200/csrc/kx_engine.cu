@@ -285,10 +285,10 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
         if (!fused_rope)
             KX_TRY(op_rope_append(e->qkv, e->qkv_dim, e->pos, e->seq, e->rope, L.kv_pages, e->block_table, e->max_pages, M,
                                   d.n_q, d.n_kv, d.head_dim, st));
-        if (e->attn_tc && d.head_dim == 64 && pos0 == 0) {
+        if (e->attn_tc && d.head_dim == 64) {
             ++e->attn_tc_launches;
             KX_TRY(op_attn_prefill_tc(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->num_pages,
-                                      e->block_table + (size_t)b0 * e->max_pages, e->max_pages, nb, S, d.n_q, d.n_kv, st));
+                                      e->block_table + (size_t)b0 * e->max_pages, e->max_pages, nb, S, pos0, d.n_q, d.n_kv, st));
         } else
         KX_TRY(op_attn_prefill(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table + (size_t)b0 * e->max_pages,
                                e->max_pages, nb, S, pos0, d.n_q, d.n_kv, d.head_dim, st));

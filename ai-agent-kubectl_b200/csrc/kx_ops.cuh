@@ -25,9 +25,9 @@ int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt
                    int B, int n_q, int n_kv, int hd, int P, float *part_o, float *part_ml, int *n_part, cudaStream_t st);
 int op_attn_prefill(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, const int *block_table,
                     int max_pages, int B, int S, int pos0, int n_q, int n_kv, int hd, cudaStream_t st);
-// tcgen05 version (kx_attn_tc.cu): head_dim 64, no cached prefix
+// tcgen05 version (kx_attn_tc.cu): head_dim 64
 int op_attn_prefill_tc(const void *qkv, int qkv_ld, void *out, int out_ld, const void *pages, int num_pages,
-                       const int *block_table, int max_pages, int B, int S, int n_q, int n_kv, cudaStream_t st);
+                       const int *block_table, int max_pages, int B, int S, int pos0, int n_q, int n_kv, cudaStream_t st);
 int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cudaStream_t st);
 // second stage of the GEMM's EPI_ARGMAX epilogue: parts int2 [n_parts][ld] -> ids (out / out2) or, for a
 // vocabulary shard, (value bits, id + id_offset) pairs (out_pairs)

@@ -243,7 +243,7 @@ int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the
  * enqueued that way so far (0: the per-layer kernels were used).
  */
 int64_t kx_engine_mega_launches(const kx_engine *e);
-/* Prefill attention for head_dim 64 without a cached prefix runs on tcgen05 tensor cores (csrc/kx_attn_tc.cu);
+/* Prefill attention for head_dim 64 (with or without a cached prefix) runs on tcgen05 tensor cores (csrc/kx_attn_tc.cu);
  * other shapes, and every shape with KX_ATTN_TC=0 in the environment at engine creation, take the mma.sync
  * kernel.  Returns how many attention launches took the tcgen05 kernel so far. */
 int64_t kx_engine_attn_tc_launches(const kx_engine *e);
