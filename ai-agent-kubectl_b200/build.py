@@ -38,10 +38,22 @@ def stale() -> bool:
 def build_lib(force: bool = False, verbose: bool = False, extra=()) -> str:
     if not force and not stale():
         return LIB_PATH
-    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-o", LIB_PATH] + sources() + ["-lcuda"]
-    if verbose:
-        print(" ".join(cmd))
-    subprocess.check_call(cmd)
+    # several ranks of one job may get here at once (torchrun): one of them builds, into a temporary file that
+    # replaces the library atomically; the others wait on the lock and then find it up to date
+    import fcntl
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if force or stale():
+            tmp = LIB_PATH + f".tmp{os.getpid()}"
+            cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-o", tmp] + sources() + ["-lcuda"]
+            if verbose:
+                print(" ".join(cmd))
+            try:
+                subprocess.check_call(cmd)
+                os.replace(tmp, LIB_PATH)
+            finally:
+                if os.path.exists(tmp):
+                    os.remove(tmp)
     return LIB_PATH
 
 
