@@ -38,11 +38,6 @@ __device__ __forceinline__ float warp_sum(float v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-}
 
 // ---- embedding gather: x[m, :] = float(table[tokens[m], :]) -----------------
 __global__ void embed_kernel(const int *__restrict__ tokens, const __nv_bfloat16 *__restrict__ table,

@@ -1,5 +1,4 @@
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/t_gpu_all.log 2>&1; echo "pytest rc=$?" >> gpurun_out/t_gpu_all.log
-tail -n 4 gpurun_out/t_gpu_all.log | cut -c1-200
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-tail -n 3 gpurun_out/smoke.log
-timeout 600 python bench.py --impl reference > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cut -c1-200 gpurun_out/bench_ref.json
+timeout 600 python -m pytest tests/test_generator_gpu.py -q -x > gpurun_out/t_tc.log 2>&1; echo "pytest rc=$?" >> gpurun_out/t_tc.log
+tail -n 3 gpurun_out/t_tc.log | cut -c1-220
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:attn_prefill -c 2 --csv --log-file gpurun_out/l3.csv python profiles/run_gen.py llama-3.2-1b 128 256 2 1 > /dev/null 2>&1
+grep -v "^==" gpurun_out/l3.csv | tail -n 2 | cut -d, -f5,15 | cut -c1-120
