@@ -1,4 +1,4 @@
-// Device-side building blocks of the decode attention kernels (kx_ops.cu, kx_decode_mega.cu):
+// Device-side building blocks of the decode attention kernels (kx_ops.cu):
 // cp.async / ldmatrix / mma.sync wrappers, the XOR-swizzled K/V tile layout, 16-byte RoPE, and the
 // one-warp-per-(sequence, kv head) key loop.
 #pragma once

@@ -8,6 +8,7 @@
 namespace kx {
 static thread_local char t_err[512] = "";
 std::atomic<int64_t> g_launches{0};
+thread_local TraceCtx *t_trace = nullptr;
 
 void set_error(const char *fmt, ...) {
     va_list ap;

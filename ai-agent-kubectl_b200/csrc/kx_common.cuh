@@ -29,6 +29,32 @@ struct PerDeviceOnce {
     void done() { mask.fetch_or(1ull << device(), std::memory_order_release); }
 };
 
+// ---- optional kernel timeline (diagnostic, KX_TRACE=1 at engine creation) -----------------------------
+// A slot is four u64 globaltimer values of one launch: [0] earliest CTA start, [1] earliest return from
+// griddepcontrol.wait (the predecessor's results are visible), [2] latest "main loop done" mark, [3] latest
+// CTA end.  The host hands every instrumented launch its slot (or NULL when tracing is off).
+struct TraceCtx {
+    unsigned long long *buf = nullptr;     // device, cap slots of 4 u64
+    int cap = 0, n = 0;
+    const char *names[2048];
+};
+extern thread_local TraceCtx *t_trace;
+inline unsigned long long *trace_slot(const char *name) {
+    TraceCtx *t = t_trace;
+    if (!t || t->n >= t->cap || t->n >= 2048) return nullptr;
+    t->names[t->n] = name;
+    return t->buf + 4 * (size_t)(t->n++);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned long long trace_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_min(unsigned long long *slot, int i) { if (slot) atomicMin(slot + i, trace_now()); }
+__device__ __forceinline__ void trace_max(unsigned long long *slot, int i) { if (slot) atomicMax(slot + i, trace_now()); }
+#endif
+
 #define KX_CUDA(call)                                                                        \
     do {                                                                                     \
         cudaError_t e__ = (call);                                                            \

@@ -13,7 +13,6 @@
 #include "kx_common.cuh"
 #include "kx_gemm.cuh"
 #include "kx_ops.cuh"
-#include "kx_mega.cuh"
 
 using namespace kx;
 
@@ -62,8 +61,6 @@ struct kx_engine {
     void *comm = nullptr;
     int (*allreduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
     int (*allgather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
-    // persistent decode kernel (small batches, no tensor parallelism): weight maps / per-layer pointers on the
-    // device, the split-K plan, partial-sum scratch and the grid barrier counter
     // wide decode batches (256 < M <= 512): the row-parallel projections run as split-K token-major GEMMs that
     // leave per-slice partial sums here; the RMSNorm that follows adds them to the residual (pend_* describe them)
     void *argmax_parts = nullptr;                  // fused lm_head argmax: int2 [parts][max_batch]
@@ -76,18 +73,9 @@ struct kx_engine {
     // cost about a millisecond of idle GPU per call otherwise); dropped whenever buffers they point to may change
     struct StepGraph { int B, S, n_new, P; cudaGraphExec_t exec; int64_t launches; };
     std::vector<StepGraph> step_graphs;
-    bool mega = false;
-    int mega_grid = 0, mega_max_b = 0;
-    MegaGemm mega_g[4];
-    CUtensorMap *mega_wmaps = nullptr;
-    MegaLayer *mega_layers = nullptr;
-    float *mega_part_qkv = nullptr, *mega_part_o = nullptr, *mega_part_d = nullptr;
-    uint32_t *mega_bar = nullptr;
-    uint64_t *mega_trace = nullptr;                // KX_MEGA_TRACE=1: phase timestamps of CTA 0 (kx_engine_mega_trace)
-    int mega_trace_cap = 0;
-    int64_t mega_launches = 0;
     int64_t device_bytes = 0;
     std::vector<void *> owned;
+    TraceCtx *trace = nullptr;                     // KX_TRACE=1: per-launch timeline of the last decode step
 };
 
 namespace {
@@ -125,6 +113,11 @@ int pick_splits(int features, int k, int b_tiles) {
     return s;
 }
 
+__global__ void trace_reset_kernel(unsigned long long *buf, int slots) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < slots) { buf[4 * i] = ~0ull; buf[4 * i + 1] = ~0ull; buf[4 * i + 2] = 0; buf[4 * i + 3] = 0; }
+}
+
 __global__ void advance_step_kernel(int *pos, int *step, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) pos[i] += 1;
@@ -145,12 +138,14 @@ struct GemmCall {
     const GemmParams *extra = nullptr;             // EPI_QKV_ROPE: the rope / cache fields
     bool tp_fused = false;                         // EPI_RESID + all-reduce over peer memory in the epilogue
     size_t split_stride = 0;                       // pair kernel with splits > 1: distance between the slices' outputs
+    const char *label = "gemm";                    // name in the diagnostic timeline
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     GemmParams p{};
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
     p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits; p.split_stride = c.split_stride;
+    p.trace = trace_slot(c.label);
     if (c.extra) {
         p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
         p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
@@ -174,6 +169,7 @@ struct Linear {
     const CUtensorMap *x_a;                        // activation as A operand (128-row box)
     const CUtensorMap *x_b;                        // activation as B operand, indexed by bn_index
     int features, k;
+    const char *label = "gemm";
 };
 
 // tile width the CTA-pair kernel would use for this layer at M rows (0: another kernel is chosen)
@@ -194,14 +190,21 @@ int linear_pair_bn(const Linear &l, int M) {
 
 int linear(kx_engine *e, const Linear &l, int M, int epi, void *out, int ldo, const float *bias, cudaStream_t st,
            const GemmParams *extra = nullptr) {
-    if (const int pbn = linear_pair_bn(l, M))
-        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + (pbn == 256), pbn, extra}, st);
-    if (M > 512)   // tall but very narrow: the single-CTA token-major kernel (128 x 128 tiles)
-        return run_gemm(e, {l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias}, st);
+    if (const int pbn = linear_pair_bn(l, M)) {
+        GemmCall c{l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias, l.w_half + (pbn == 256), pbn, extra};
+        c.label = l.label;
+        return run_gemm(e, c, st);
+    }
+    if (M > 512) {   // tall but very narrow: the single-CTA token-major kernel (128 x 128 tiles)
+        GemmCall c{l.x_a, l.w_full, M, l.features, l.k, epi, 0, 1, 128, out, ldo, bias};
+        c.label = l.label;
+        return run_gemm(e, c, st);
+    }
     const int bn = gemm_pick_bn(1, M), bi = bn_index(bn);
     const int b_tiles = (M + bn - 1) / bn;
-    return run_gemm(e, {l.w_full, l.x_b + bi, l.features, M, l.k, epi, 1, pick_splits(l.features, l.k, b_tiles), bn,
-                        out, ldo, bias}, st);
+    GemmCall c{l.w_full, l.x_b + bi, l.features, M, l.k, epi, 1, pick_splits(l.features, l.k, b_tiles), bn, out, ldo, bias};
+    c.label = l.label;
+    return run_gemm(e, c, st);
 }
 
 // RMSNorm of the residual rows; folds in (and clears) split-K partials a preceding projection left pending
@@ -227,6 +230,7 @@ int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool dec
         if (S >= 2 && (size_t)S * M * d.hidden <= e->splitk_cap) {
             GemmCall c{l.x_a, l.w_full, M, l.features, l.k, EPI_F32, 0, S, 128, e->splitk_part, d.hidden, nullptr, l.w_half + 1, 256};
             c.split_stride = (size_t)M * d.hidden;
+            c.label = l.label;
             KX_TRY(run_gemm(e, c, st));
             e->pend_part = e->splitk_part; e->pend_splits = S; e->pend_stride = c.split_stride;
             return KX_OK;
@@ -240,6 +244,7 @@ int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool dec
         GemmCall c{l.w_full, l.x_b + bi, l.features, M, l.k, EPI_RESID, 1, pick_splits(l.features, l.k, b_tiles), bn,
                    e->resid, d.hidden, nullptr};
         c.tp_fused = true;
+        c.label = l.label;
         ++e->p2p_launches;
         return run_gemm(e, c, st);
     }
@@ -254,10 +259,10 @@ int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool dec
 int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b0, int max_T, cudaStream_t st, int pos0 = 0) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
-    const Linear qkv{&L.wqkv, L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden};
-    const Linear wo{&L.wo, L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim};
-    const Linear wgu{&L.wgu, L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden};
-    const Linear wd{&L.wd, L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter};
+    const Linear qkv{&L.wqkv, L.wqkv_h, &e->xn_a, e->xn_b, e->qkv_dim, d.hidden, "qkv"};
+    const Linear wo{&L.wo, L.wo_h, &e->attn_a, e->attn_b, d.hidden, e->q_dim, "wo"};
+    const Linear wgu{&L.wgu, L.wgu_h, &e->xn_a, e->xn_b, 2 * d.inter, d.hidden, "gate_up"};
+    const Linear wd{&L.wd, L.wd_h, &e->mlp_a, e->mlp_b, d.hidden, d.inter, "down"};
     KX_TRY(norm_rows(e, L.w.ln1, M, nullptr, st));
     const int head_w = d.head_dim;
     const int qkv_pbn = linear_pair_bn(qkv, M);
@@ -300,26 +305,6 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     return KX_OK;
 }
 
-// all layers of one decode step in the persistent kernel (kx_decode_mega.cu)
-int decode_layers_mega(kx_engine *e, int B, cudaStream_t st) {
-    const kx_model_desc &d = e->d;
-    const int bn = mega_bn(B), bi = bn_index(bn);
-    MegaParams p{};
-    p.wmaps = e->mega_wmaps; p.layers_ptr = e->mega_layers;
-    for (int g = 0; g < 4; ++g) p.g[g] = e->mega_g[g];
-    p.resid = e->resid; p.xn = e->xn; p.attn = e->attn; p.mlp = e->mlp;
-    p.part_qkv = e->mega_part_qkv; p.part_o = e->mega_part_o; p.part_d = e->mega_part_d;
-    p.pos = e->pos; p.block_table = e->block_table; p.rope = reinterpret_cast<const float2 *>(e->rope);
-    p.bar = e->mega_bar;
-    p.trace = e->mega_trace; p.trace_cap = e->mega_trace_cap;
-    p.layers = d.layers; p.B = B; p.hidden = d.hidden; p.qkv_dim = e->qkv_dim; p.q_dim = e->q_dim;
-    p.n_q = d.n_q; p.n_kv = d.n_kv; p.max_pages = e->max_pages;
-    p.eps = d.eps;
-    p.scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
-    ++e->mega_launches;
-    return mega_launch(e->xn_b[bi], e->attn_b[bi], e->mlp_b[bi], p, bn, d.head_dim, e->mega_grid, st);
-}
-
 // greedy token per sequence from e->logits (this rank's vocabulary shard under tensor parallelism)
 int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
     const kx_model_desc &d = e->d;
@@ -335,7 +320,7 @@ int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
 int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     KX_TRY(norm_rows(e, e->norm, B, row_map, st));
-    const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+    const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden, "lm_head"};
     // Nobody asked for the logits: the lm_head epilogue keeps only (max, index) per token and tile, a small
     // second kernel finishes the pick; [B, vocab] is never written.  (Small vocabularies take the cluster split-K
     // GEMM, which has no such epilogue, and B > 512 the single-CTA kernel: both use the logits path.)
@@ -483,46 +468,11 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         e->splitk_cap = (size_t)8 * (d.max_batch < 512 ? d.max_batch : 512) * d.hidden;
         KX_E(dev_alloc(e, (void **)&e->splitk_part, e->splitk_cap * sizeof(float)));
     }
-    // persistent decode kernel: single GPU replicas only (the tensor-parallel epilogue lives in the cluster GEMM)
-    {
-        // Opt-in (KX_MEGA=1): measured on B200 it does not beat the per-layer kernels yet (decode section)
-        const char *v = getenv("KX_MEGA");
-        const bool want = v && v[0] == '1';
-        if (want && d.tp_size <= 1 && mega_supported(d.head_dim, d.n_q / d.n_kv, d.hidden)) {
-            int dev = 0, sms = 0;
-            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-                return fail(KX_ECUDA);
-            e->mega_grid = sms;
-            e->mega_max_b = d.max_batch < 128 ? d.max_batch : 128;
-            e->mega_g[0] = mega_plan_gemm(e->qkv_dim, d.hidden, sms, true);
-            e->mega_g[1] = mega_plan_gemm(d.hidden, e->q_dim, sms, true);
-            e->mega_g[2] = mega_plan_gemm(2 * d.inter, d.hidden, sms, false);   // SwiGLU in the epilogue needs whole sums
-            e->mega_g[3] = mega_plan_gemm(d.hidden, d.inter, sms, true);
-            const size_t mb = (size_t)e->mega_max_b;
-            KX_E(dev_alloc(e, (void **)&e->mega_part_qkv, (size_t)e->mega_g[0].splits * mb * e->qkv_dim * 4));
-            KX_E(dev_alloc(e, (void **)&e->mega_part_o, (size_t)e->mega_g[1].splits * mb * d.hidden * 4));
-            KX_E(dev_alloc(e, (void **)&e->mega_part_d, (size_t)e->mega_g[3].splits * mb * d.hidden * 4));
-            KX_E(dev_alloc(e, (void **)&e->mega_bar, sizeof(uint32_t) * 7 * (size_t)d.layers + 256));
-            if (const char *t = getenv("KX_MEGA_TRACE")) {
-                if (t[0] == '1') {
-                    e->mega_trace_cap = 16 * d.layers + 16;
-                    KX_E(dev_alloc(e, (void **)&e->mega_trace, sizeof(uint64_t) * 2 * e->mega_trace_cap));
-                    if (cudaMemset(e->mega_trace, 0, sizeof(uint64_t) * 2 * e->mega_trace_cap) != cudaSuccess) return fail(KX_ECUDA);
-                }
-            }
-            KX_E(dev_alloc(e, (void **)&e->mega_wmaps, sizeof(CUtensorMap) * 4 * d.layers));
-            KX_E(dev_alloc(e, (void **)&e->mega_layers, sizeof(MegaLayer) * d.layers));
-            std::vector<CUtensorMap> maps((size_t)4 * d.layers);
-            std::vector<MegaLayer> lp(d.layers);
-            for (int i = 0; i < d.layers; ++i) {
-                const LayerPlan &L = e->layers[i];
-                maps[4 * i + 0] = L.wqkv; maps[4 * i + 1] = L.wo; maps[4 * i + 2] = L.wgu; maps[4 * i + 3] = L.wd;
-                lp[i].ln1 = L.w.ln1; lp[i].ln2 = L.w.ln2; lp[i].bqkv = L.w.bqkv; lp[i].kv_pages = L.kv_pages;
-            }
-            if (cudaMemcpy(e->mega_wmaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice) != cudaSuccess ||
-                cudaMemcpy(e->mega_layers, lp.data(), lp.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice) != cudaSuccess)
-                return fail(KX_ECUDA);
-            e->mega = true;
+    if (const char *v = getenv("KX_TRACE")) {
+        if (v[0] == '1') {
+            e->trace = new TraceCtx();
+            e->trace->cap = 2048;
+            KX_E(dev_alloc(e, (void **)&e->trace->buf, sizeof(unsigned long long) * 4 * e->trace->cap));
         }
     }
 #undef KX_E
@@ -629,23 +579,26 @@ extern "C" void kx_engine_destroy(kx_engine *e) {
     if (e->p2p_peer_flag) cudaIpcCloseMemHandle(e->p2p_peer_flag);
     for (void *p : e->owned) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);
+    delete e->trace;
     delete e;
 }
 
 extern "C" int64_t kx_engine_device_bytes(const kx_engine *e) { return e ? e->device_bytes : 0; }
 
-extern "C" int64_t kx_engine_mega_launches(const kx_engine *e) { return e ? e->mega_launches : 0; }
-
-extern "C" int64_t kx_engine_attn_tc_launches(const kx_engine *e) { return e ? e->attn_tc_launches : 0; }
-
-extern "C" int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max_pairs) {
-    KX_REQUIRE(e && h_pairs, KX_EINVAL, "kx_engine_mega_trace: NULL argument");
-    if (!e->mega_trace) return 0;
-    const int n = max_pairs < e->mega_trace_cap ? max_pairs : e->mega_trace_cap;
+extern "C" int kx_engine_trace(kx_engine *e, uint64_t *h_slots, int32_t max_slots) {
+    KX_REQUIRE(e && h_slots, KX_EINVAL, "kx_engine_trace: NULL argument");
+    if (!e->trace) return 0;
+    const int n = max_slots < e->trace->n ? max_slots : e->trace->n;
     KX_CUDA(cudaStreamSynchronize(e->stream));
-    KX_CUDA(cudaMemcpy(h_pairs, e->mega_trace, sizeof(uint64_t) * 2 * n, cudaMemcpyDeviceToHost));
+    KX_CUDA(cudaMemcpy(h_slots, e->trace->buf, sizeof(uint64_t) * 4 * n, cudaMemcpyDeviceToHost));
     return n;
 }
+
+extern "C" const char *kx_engine_trace_name(const kx_engine *e, int32_t i) {
+    return (e && e->trace && i >= 0 && i < e->trace->n) ? e->trace->names[i] : "";
+}
+
+extern "C" int64_t kx_engine_attn_tc_launches(const kx_engine *e) { return e ? e->attn_tc_launches : 0; }
 
 extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t B, int32_t S, int32_t n_new,
                                   int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream) {
@@ -712,16 +665,17 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     }
     const int max_T = P + S + n_new;
     auto step_once = [&](float *logits_dst) -> int {
+        if (e->trace) {                                // timeline of this step: slots handed out from 0 again
+            e->trace->n = 0;
+            trace_reset_kernel<<<(e->trace->cap + 255) / 256, 256, 0, st>>>(e->trace->buf, e->trace->cap);
+            t_trace = e->trace;
+        }
+        struct Untrace { ~Untrace() { t_trace = nullptr; } } untrace;
         // pos[b] currently holds the previous token's position
         advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);
         count_launch();
         KX_TRY(op_embed(e->next_tok, e->embed, e->resid, B, d.hidden, st));
-        const bool shared_prefix = e->share_prefix && e->prefix_len >= 64 && B >= 2 && e->prefix_o;
-        if (e->mega && B <= e->mega_max_b && !shared_prefix) {
-            KX_TRY(decode_layers_mega(e, B, st));
-        } else {
-            for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, max_T, st));
-        }
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, max_T, st));
         KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st));
         return KX_OK;
     };

@@ -160,6 +160,8 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int nkb = min(total_kb - kb0, p.kb_per_split);
 
     if (threadIdx.x == 0) {
+        trace_min(p.trace, 0);
+        trace_min(p.trace, 1);
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
@@ -212,6 +214,7 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int etid = threadIdx.x - 64;
         mbar_wait(tmem_full, 0);
         tc_fence_after();
+        if (etid == 0) trace_max(p.trace, 2);
         const bool split = gridDim.z > 1;
         if (EPI == EPI_ARGMAX) {
             // swap-AB lm_head: rows = vocabulary entries, columns = tokens.  Per token the warp reduces its 32 rows
@@ -285,6 +288,7 @@ kx_gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+    if (threadIdx.x == 0) trace_max(p.trace, 3);
 }
 
 
@@ -378,6 +382,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t rank = cluster_ctarank();
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
     asm volatile("griddepcontrol.launch_dependents;");        // launched with programmatic serialization (see launch_pair)
+    if (threadIdx.x == 0) trace_min(p.trace, 0);
     const int total_kb = (p.k + BK - 1) / BK;
     // split-K (EPI_F32 only): a work item is (output tile, k slice); slice ks writes its partial tile to
     // out + ks * split_stride and the consumer (the next RMSNorm) adds the slices up in a fixed order
@@ -419,6 +424,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 }
             }
             asm volatile("griddepcontrol.wait;" ::: "memory");
+            trace_min(p.trace, 1);
             for (int wk = cluster_id; wk < n_work; wk += n_clusters) {
                 const int tile = wk / S, ks = wk - tile * S;
                 const int mp = tile / n_tiles, nt = tile - mp * n_tiles;
@@ -462,6 +468,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 }
                 umma_commit(tmem_full + ab);
             }
+            trace_max(p.trace, 2);
         }
     } else {
         const int q = warp & 3;
@@ -572,6 +579,7 @@ kx_gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     __syncthreads();
     cluster_sync_all();                            // nobody leaves while the peer can still reach its smem
     if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+    if (threadIdx.x == 0) trace_max(p.trace, 3);
 }
 
 template <int BN, int EPI>
@@ -683,6 +691,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
     asm volatile("griddepcontrol.launch_dependents;");        // our own dependents may begin their prologue
+    if (threadIdx.x == 0) trace_min(p.trace, 0);
     const int S = gridDim.z, z = blockIdx.z;                  // cluster = the z column; rank == z
     const int total_kb = (p.k + BK - 1) / BK;
     const int kb0 = z * p.kb_per_split;
@@ -713,6 +722,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 tma_load_2d_hint(smem + i * C::STAGE_BYTES, &tmA, full + i, (kb0 + i) * BK, m0, pol_w);
             }
             asm volatile("griddepcontrol.wait;" ::: "memory");
+            trace_min(p.trace, 1);
             for (int i = 0; i < pre; ++i)
                 tma_load_2d_hint(smem + i * C::STAGE_BYTES + C::A_BYTES, &tmB, full + i, (kb0 + i) * BK, n0, pol_x);
             for (int i = pre; i < nkb; ++i) {
@@ -744,6 +754,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         asm volatile("griddepcontrol.wait;" ::: "memory");     // outputs (and the residual read) follow the predecessor
         mbar_wait(tmem_full, 0);                               // all MMAs retired: the stage ring is free
         tc_fence_after();
+        if (threadIdx.x == 64) trace_max(p.trace, 2);
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
         for (int c = 0; c < BN; c += 32) {
@@ -816,6 +827,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     }
     cluster_sync_all();                                        // peers may still be reading this CTA's partial
     if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
+    if (threadIdx.x == 0) trace_max(p.trace, 3);
 }
 
 template <int BN, int EPI>

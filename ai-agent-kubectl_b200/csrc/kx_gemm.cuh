@@ -41,6 +41,7 @@ struct GemmParams {
     const uint32_t *tp_flag;
     uint32_t *tp_epoch;      // this GPU:  uint32 [tiles], launches seen so far per tile slot
     int tp_rows;             // rows of one receive buffer (max decode batch)
+    unsigned long long *trace;   // diagnostic timeline slot (kx_common.cuh) or NULL
 };
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);

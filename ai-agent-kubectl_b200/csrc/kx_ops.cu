@@ -92,9 +92,11 @@ template <int PER>   // float4 chunks per thread: H = 512 * PER
 __global__ void __launch_bounds__(128)
 rmsnorm_row_kernel(float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, __nv_bfloat16 *__restrict__ y,
                    int H, float eps, const int *__restrict__ row_map, const float *__restrict__ part, int splits,
-                   size_t split_stride) {
+                   size_t split_stride, unsigned long long *trace) {
     asm volatile("griddepcontrol.launch_dependents;");
+    if (threadIdx.x == 0) trace_min(trace, 0);
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0) trace_min(trace, 1);
     const int row = blockIdx.x, tid = threadIdx.x;
     const size_t src = (size_t)(row_map ? row_map[row] : row) * H;
     float *xr = x + src;
@@ -143,6 +145,7 @@ rmsnorm_row_kernel(float *__restrict__ x, const __nv_bfloat16 *__restrict__ g, _
         out.y = *reinterpret_cast<uint32_t *>(&o1);
         *reinterpret_cast<uint2 *>(yr + i) = out;
     }
+    if (tid == 0) trace_max(trace, 3);
 }
 
 // ---- RoPE (rotate-half pairs i, i + hd/2) on q and k, then append k, v to the cache ----
@@ -342,10 +345,13 @@ __global__ void __launch_bounds__(NW * 32)
 attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
                    __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
                    const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
-                   int round_keys, int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part) {
+                   int round_keys, int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part,
+                   unsigned long long *trace) {
     extern __shared__ __align__(128) uint8_t smem_dec[];
     asm volatile("griddepcontrol.launch_dependents;");   // let a dependent GEMM start prefetching its weights
+    if (threadIdx.x == 0) trace_min(trace, 0);
     asm volatile("griddepcontrol.wait;" ::: "memory");   // launched with programmatic serialization: qkv comes from the predecessor
+    if (threadIdx.x == 0) trace_min(trace, 1);
     constexpr int CH = HD / 8;                        // 16 B chunks per row
     constexpr int HALF = HD / 2;
     const int ROUND = round_keys;                     // keys staged per round: a multiple of 64, at most 64 per warp
@@ -538,6 +544,7 @@ attn_decode_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloa
         }
         out[(size_t)b * out_ld + (size_t)(kvh * G + h) * HD + d] = __float2bfloat16(num / den);
     }
+    if (tid == 0) trace_max(trace, 3);
 }
 
 // ---- decode attention, one WARP per (sequence, kv head) -------------------------------------
@@ -552,9 +559,11 @@ __global__ void __launch_bounds__(128)
 attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
                         __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
                         const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
-                        int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part, int n_tasks) {
+                        int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part, int n_tasks,
+                        unsigned long long *trace) {
     extern __shared__ __align__(128) uint8_t smem_dw[];
     asm volatile("griddepcontrol.launch_dependents;");
+    if (threadIdx.x == 0) trace_min(trace, 0);
     using W = WarpAttnSmem<HD, KB, NS>;
     constexpr int CH = HD / 8, HALF = HD / 2;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -573,6 +582,7 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
         cp_async_commit();
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");   // qkv comes from the predecessor
+    if (threadIdx.x == 0) trace_min(trace, 1);
     if (!live) return;
 
     // RoPE: q heads -> Q tile rows 0..G-1, k -> cache and knew, v -> cache and vnew
@@ -606,6 +616,7 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
     warp_attn_main<HD, G, KB, NS>(Qs, nblk, key0, T, p, pages, bt, n_kv, kvh, lane, scale_log2,
                                   out + (size_t)b * out_ld + (size_t)kvh * G * HD, part_o, part_ml, n_part,
                                   (size_t)(n_tasks / n_kv) * n_q, (size_t)b * n_q + kvh * G);
+    if (lane == 0) trace_max(trace, 3);
 }
 
 // ---- decode attention over a prefix shared by the whole batch ("read the prefix once") ----
@@ -620,9 +631,10 @@ __global__ void __launch_bounds__(128)
 attn_prefix_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, const __nv_bfloat16 *__restrict__ pages,
                    const int *__restrict__ bt, const int *__restrict__ pos, const float2 *__restrict__ rope,
                    int B, int G, int n_q, int n_kv, int P, int chunk_keys, float scale_log2,
-                   float *__restrict__ part_o, float *__restrict__ part_ml) {
+                   float *__restrict__ part_o, float *__restrict__ part_ml, unsigned long long *trace) {
     extern __shared__ __align__(128) uint8_t smem_attn[];
     asm volatile("griddepcontrol.launch_dependents;");
+    if (threadIdx.x == 0) trace_min(trace, 0);
     constexpr int CH = HD / 8, HALF = HD / 2;
     constexpr int TILE = 64 * HD * 2;
     const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(smem_attn);
@@ -647,6 +659,7 @@ attn_prefix_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, const __nv
     fetch_kv(0);
     cp_async_commit();
     asm volatile("griddepcontrol.wait;" ::: "memory");   // q comes from the QKV GEMM
+    if (tid == 0) trace_min(trace, 1);
     for (int i = tid; i < 64 * (HALF / 8); i += 128) {    // rotated q rows -> Q tile (rows past B G are zero)
         const int r = i / (HALF / 8), c = i - r * (HALF / 8);
         const int row = rt * 64 + r;
@@ -754,6 +767,7 @@ attn_prefix_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, const __nv
         for (int j = 0; j < HD / 8; ++j)
             *reinterpret_cast<float2 *>(po + j * 8) = make_float2(o[j][2 * r], o[j][2 * r + 1]);
     }
+    if (tid == 0) trace_max(trace, 3);
 }
 
 // ---- greedy argmax over fp32 logits; ties -> lowest index (torch.argmax) ------------
@@ -869,6 +883,11 @@ __global__ void pick_kernel(const int2 *__restrict__ gathered, int tp, int B, in
     out[b] = bi;
 }
 
+// L2 prefetch of a byte range as a kernel of its own (microbenchmarks; the decode kernels issue their own)
+__global__ void l2_prefetch_kernel(const char *p, size_t bytes) {
+    if (threadIdx.x == 0) sm100::l2_prefetch_share(p, bytes, blockIdx.x, gridDim.x);
+}
+
 // positions / bookkeeping for the decode loop, kept on the device so a step can be a CUDA graph
 __global__ void advance_kernel(int *pos, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -888,7 +907,7 @@ int launch_decode_warp(int G, int n_tasks, cudaStream_t st, const __nv_bfloat16 
         static PerDeviceOnce once;     /* first use is the eager decode step, outside any capture */         \
         if (once.first()) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); once.done(); } \
         KX_CUDA(launch_pdl(k, grid, dim3(128), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, \
-                           key0, part_o, part_ml, n_part, n_tasks));                                         \
+                           key0, part_o, part_ml, n_part, n_tasks, trace_slot("attn.warp")));                \
         break;                                                                                               \
     }
     switch (G) {
@@ -915,7 +934,7 @@ int launch_decode_g(int G, dim3 grid, size_t smem, cudaStream_t st, const __nv_b
             KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
             have = smem;                                                                                    \
         }                                                                                                   \
-        KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys, key0, part_o, part_ml, n_part)); \
+        KX_CUDA(launch_pdl(k, grid, dim3(nw * 32), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, round_keys, key0, part_o, part_ml, n_part, trace_slot("attn.cta"))); \
         break;                                                                                              \
     }
     switch (G) {
@@ -943,10 +962,11 @@ int op_rmsnorm(float *x, const void *g, void *y, int M, int H, float eps, const 
         const int per = (H + 511) / 512;
         const __nv_bfloat16 *gg = (const __nv_bfloat16 *)g;
         __nv_bfloat16 *yy = (__nv_bfloat16 *)y;
-        if (per <= 2) KX_CUDA(launch_pdl(rmsnorm_row_kernel<2>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
-        else if (per <= 4) KX_CUDA(launch_pdl(rmsnorm_row_kernel<4>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
-        else if (per <= 8) KX_CUDA(launch_pdl(rmsnorm_row_kernel<8>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
-        else KX_CUDA(launch_pdl(rmsnorm_row_kernel<16>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride));
+        unsigned long long *tr = trace_slot("rmsnorm");
+        if (per <= 2) KX_CUDA(launch_pdl(rmsnorm_row_kernel<2>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride, tr));
+        else if (per <= 4) KX_CUDA(launch_pdl(rmsnorm_row_kernel<4>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride, tr));
+        else if (per <= 8) KX_CUDA(launch_pdl(rmsnorm_row_kernel<8>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride, tr));
+        else KX_CUDA(launch_pdl(rmsnorm_row_kernel<16>, M, 128, 0, st, x, gg, yy, H, eps, row_map, part, splits, split_stride, tr));
         count_launch();
         return KX_OK;
     }
@@ -1045,13 +1065,13 @@ int op_attn_prefix(const void *qkv, int qkv_ld, const void *pages, const int *bt
     dim3 grid(n_kv, (B * G + 63) / 64, nc);
     if (hd == 64) {
         KX_CUDA(launch_pdl(attn_prefix_kernel<64>, grid, dim3(128), (size_t)5 * 64 * 64 * 2, st, (const __nv_bfloat16 *)qkv, qkv_ld,
-                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
+                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml, trace_slot("attn.prefix")));
     } else if (hd == 128) {
         auto k = attn_prefix_kernel<128>;
         static PerDeviceOnce once;                     // first use is the eager decode step, outside any capture
         if (once.first()) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * 64 * 128 * 2)); once.done(); }
         KX_CUDA(launch_pdl(k, grid, dim3(128), (size_t)5 * 64 * 128 * 2, st, (const __nv_bfloat16 *)qkv, qkv_ld,
-                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml));
+                           (const __nv_bfloat16 *)pages, bt_prefix, pos, (const float2 *)rope, B, G, n_q, n_kv, P, ck, scale_log2, part_o, part_ml, trace_slot("attn.prefix")));
     } else {
         set_error("attention: head_dim %d not supported (64 or 128)", hd);
         return KX_EINVAL;
@@ -1155,6 +1175,16 @@ extern "C" int kx_attn_decode(const void *d_qkv, int32_t qkv_ld, void *d_out, in
     }
     return op_attn_decode(d_qkv, qkv_ld, d_out, out_ld, d_pages, d_block_table, max_pages, d_pos, d_rope, B, max_T, n_q, n_kv, hd,
                           key0, part_o, part_ml, n_part, st);
+}
+
+extern "C" int kx_l2_prefetch(const void *d_ptr, int64_t bytes, void *stream) {
+    using namespace kx;
+    KX_REQUIRE(d_ptr && bytes >= 0 && ((uintptr_t)d_ptr & 15) == 0, KX_EINVAL, "kx_l2_prefetch: pointer must be 16-byte aligned");
+    if (bytes < 16) return KX_OK;
+    l2_prefetch_kernel<<<148, 32, 0, (cudaStream_t)stream>>>((const char *)d_ptr, (size_t)bytes);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
 }
 
 extern "C" int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream) {

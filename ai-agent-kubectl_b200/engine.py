@@ -45,9 +45,9 @@ _lib.declare("kx_engine_set_collectives", ctypes.c_int, [c_void_p, c_void_p, c_v
 _lib.declare("kx_engine_p2p_export", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_import", ctypes.c_int, [c_void_p, c_void_p])
 _lib.declare("kx_engine_p2p_launches", ctypes.c_int64, [c_void_p])
-_lib.declare("kx_engine_mega_launches", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_attn_tc_launches", ctypes.c_int64, [c_void_p])
-_lib.declare("kx_engine_mega_trace", ctypes.c_int, [c_void_p, c_void_p, ctypes.c_int])
+_lib.declare("kx_engine_trace", ctypes.c_int, [c_void_p, c_void_p, ctypes.c_int])
+_lib.declare("kx_engine_trace_name", ctypes.c_char_p, [c_void_p, ctypes.c_int])
 _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
@@ -135,14 +135,14 @@ class Generator:
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, max_seq: int = 320, device: int = 0,
                  weights: Optional[Dict] = None, prefill_chunk: int = 32768, tp_rank: int = 0, tp_size: int = 1,
-                 nccl: Optional["NcclComm"] = None, p2p: bool = True):
+                 nccl: Optional["NcclComm"] = None, p2p: bool = True, embed_std: Optional[float] = None):
         import torch
         if not torch.cuda.is_available():
             raise RuntimeError("the generator needs a CUDA device; there is no CPU fallback")
         self.cfg = get_config(arch)
         self.device = torch.device("cuda", device)
         self.max_batch, self.max_seq = max_batch, max_seq
-        self.logical = weights if weights is not None else weights_mod.make_weights(self.cfg, seed)
+        self.logical = weights if weights is not None else weights_mod.make_weights(self.cfg, seed, embed_std)
         with torch.cuda.device(self.device):
             self.packed = pack_weights(self.cfg, self.logical, self.device, tp_rank, tp_size)
             self.rope = weights_mod.rope_table(self.cfg, self.cfg.max_pos).to(self.device)
@@ -188,21 +188,18 @@ class Generator:
     def p2p_launches(self) -> int:
         return int(_lib.lib().kx_engine_p2p_launches(self._h))
 
-    def mega_launches(self) -> int:
-        """Decode steps enqueued as the single persistent kernel so far."""
-        return int(_lib.lib().kx_engine_mega_launches(self._h))
-
     def attn_tc_launches(self) -> int:
         """Prefill attention launches that took the tcgen05 kernel (KX_ATTN_TC=1) so far."""
         return int(_lib.lib().kx_engine_attn_tc_launches(self._h))
 
-    def mega_trace(self, max_pairs: int = 1024):
-        """Diagnostic (KX_MEGA_TRACE=1): [(tag, ns)] recorded by CTA 0 of the persistent kernel in the last step."""
-        buf = np.zeros((max_pairs, 2), np.uint64)
-        n = _lib.lib().kx_engine_mega_trace(self._h, buf.ctypes.data, max_pairs)
+    def trace(self, max_slots: int = 2048):
+        """Diagnostic (KX_TRACE=1): [(label, start, deps_ready, main_done, end)] in ns for every instrumented
+        launch of the last decode step, in launch order."""
+        buf = np.zeros((max_slots, 4), np.uint64)
+        n = _lib.lib().kx_engine_trace(self._h, buf.ctypes.data, max_slots)
         if n < 0:
             _lib.check(n)
-        return [(int(t), int(ns)) for t, ns in buf[:n] if ns]
+        return [(_lib.lib().kx_engine_trace_name(self._h, i).decode(),) + tuple(int(x) for x in buf[i]) for i in range(n)]
 
     def device_bytes(self) -> int:
         return int(_lib.lib().kx_engine_device_bytes(self._h))
@@ -249,14 +246,16 @@ class B200Engine(Engine):
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
                  device: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl: Optional[NcclComm] = None,
-                 prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512):
+                 prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512,
+                 parity_init: bool = False):
         self.auto_prefix, self.max_prefix = auto_prefix, (max_prefix // 16) * 16
         self._prefix_bytes, self.prefix_sets = b"", 0
         if auto_prefix:
             prefix_len = self.max_prefix
         self.gen = Generator(arch, seed=seed, max_batch=max_batch, max_seq=prefix_len + prompt_len + max_new, device=device,
                              tp_rank=tp_rank, tp_size=tp_size, nccl=nccl,
-                             prefill_chunk=max(32768, prefix_len))
+                             prefill_chunk=max(32768, prefix_len),
+                             embed_std=get_config(arch).parity_embed_std if parity_init else None)
         self.max_batch, self.prompt_len, self.max_new = max_batch, prompt_len, max_new
         if prefix_len and not auto_prefix:
             # constant instruction prefix (app.py:50-57 in the service; a system prompt in BASELINE config 5),

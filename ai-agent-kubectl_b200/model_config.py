@@ -24,6 +24,10 @@ class ModelConfig:
     eps: float
     rope_scaling: Optional[Tuple[float, float, float, int]] = None   # llama3: (factor, low, high, original_max_pos)
     max_pos: int = 2048
+    # std of the embedding table under the parity init (weights.py): large enough that the token's own embedding
+    # stays visible in the final hidden state (top-1 logit ~10 sigma above the bulk), small enough that the layers
+    # still carry most of the residual's energy.  None: the architecture is only used with the iid init.
+    parity_embed_std: Optional[float] = None
 
     @property
     def q_dim(self) -> int:
@@ -53,11 +57,12 @@ class ModelConfig:
 
 
 CONFIGS = {
-    "qwen2.5-0.5b": ModelConfig("qwen2.5-0.5b", "qwen2", 896, 24, 14, 2, 64, 4864, 151_936, True, True, 1e6, 1e-6),
+    "qwen2.5-0.5b": ModelConfig("qwen2.5-0.5b", "qwen2", 896, 24, 14, 2, 64, 4864, 151_936, True, True, 1e6, 1e-6,
+                                parity_embed_std=0.5),
     "llama-3.2-1b": ModelConfig("llama-3.2-1b", "llama", 2048, 16, 32, 8, 64, 8192, 128_256, True, False, 5e5, 1e-5,
-                                (32.0, 1.0, 4.0, 8192)),
+                                (32.0, 1.0, 4.0, 8192), parity_embed_std=1.0),
     "llama-3.1-8b": ModelConfig("llama-3.1-8b", "llama", 4096, 32, 32, 8, 128, 14_336, 128_256, False, False, 5e5, 1e-5,
-                                (8.0, 1.0, 4.0, 8192)),
+                                (8.0, 1.0, 4.0, 8192), parity_embed_std=3.0),
     # small shapes for parity tests (same code paths: GQA, bias / llama3 rope, tied / untied)
     "tiny-qwen2": ModelConfig("tiny-qwen2", "qwen2", 128, 2, 4, 2, 64, 256, 1024, True, True, 1e6, 1e-6),
     "tiny-llama": ModelConfig("tiny-llama", "llama", 256, 2, 4, 2, 64, 512, 2048, False, False, 5e5, 1e-5,

@@ -140,6 +140,11 @@ int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, 
                  int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
                  void *stream);
 
+/* Asks the L2 to fetch [d_ptr, d_ptr + bytes) (16-byte aligned) from HBM ahead of the kernels that will read it
+ * (cp.async.bulk.prefetch.L2); the decode kernels do this themselves for the weights of their successor.
+ * No reference counterpart. */
+int kx_l2_prefetch(const void *d_ptr, int64_t bytes, void *stream);
+
 /* Second stage of KX_EPI_ARGMAX: d_parts int2 [n_parts][ld] -> d_ids int32 [B]; ties go to the lowest id. */
 int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream);
 
@@ -235,23 +240,16 @@ int kx_engine_p2p_export(kx_engine *e, void *handles);
 int kx_engine_p2p_import(kx_engine *e, const void *peer_handles);
 int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the fused all-reduce so far */
 
-/*
- * Experimental, opt-in with KX_MEGA=1 in the environment when the engine is created: decode steps of
- * at most 128 sequences on a single-GPU replica run all layers in ONE persistent kernel (weights keep
- * streaming through the phase barriers; see csrc/kx_decode_mega.cu).  Parity-tested, but on B200 it
- * is not yet faster than the per-layer kernels, which stay the default.  Returns how many steps were
- * enqueued that way so far (0: the per-layer kernels were used).
- */
-int64_t kx_engine_mega_launches(const kx_engine *e);
 /* Prefill attention for head_dim 64 (with or without a cached prefix) runs on tcgen05 tensor cores (csrc/kx_attn_tc.cu);
  * other shapes, and every shape with KX_ATTN_TC=0 in the environment at engine creation, take the mma.sync
  * kernel.  Returns how many attention launches took the tcgen05 kernel so far. */
 int64_t kx_engine_attn_tc_launches(const kx_engine *e);
-/* Diagnostic: with KX_MEGA_TRACE=1 in the environment at creation, CTA 0 of the persistent kernel records
- * (tag, globaltimer ns) pairs at its phase barriers (tag = 2 * phase on arrival, 2 * phase + 1 when the wait
- * for that phase returned, 0xffffffff at kernel start); copies up to max_pairs pairs of the LAST step to
- * h_pairs and returns how many slots were copied (0 when tracing is off). */
-int kx_engine_mega_trace(kx_engine *e, uint64_t *h_pairs, int32_t max_pairs);
+/* Diagnostic: with KX_TRACE=1 in the environment at creation every instrumented kernel of a decode step records
+ * globaltimer values into its slot: [0] earliest CTA start, [1] earliest return from griddepcontrol.wait,
+ * [2] latest end of the main loop, [3] latest CTA end (ns).  Copies the slots of the LAST step (launch order) to
+ * h_slots (4 x uint64 each) and returns how many; kx_engine_trace_name gives the launch's label. */
+int kx_engine_trace(kx_engine *e, uint64_t *h_slots, int32_t max_slots);
+const char *kx_engine_trace_name(const kx_engine *e, int32_t i);
 
 /*
  * kx_engine_set_prefix -- prefill `n` tokens (a multiple of 16; host int32) ONCE and keep their

@@ -30,10 +30,24 @@ def _r(x: torch.Tensor, on: bool) -> torch.Tensor:
     return x.to(torch.bfloat16).to(torch.float32) if on else x
 
 
+class StreamedWeights:
+    """Weights that are regenerated from their seed each time they are read and never kept:
+    ``w[name]`` -> fp32 tensor (kubectl_b200.weights.make_tensor).  A forward pass reads every
+    layer tensor exactly once, so an 8B-parameter fp32 model needs one layer (< 1 GB) of memory
+    instead of 32 GB.  Meant for ONE teacher-forced forward over prompt + generated tokens."""
+
+    def __init__(self, cfg, seed: int, embed_std: float):
+        self.cfg, self.seed, self.embed_std = cfg, seed, embed_std
+
+    def __getitem__(self, name: str) -> torch.Tensor:
+        from kubectl_b200 import weights as wm
+        return wm.make_tensor(self.cfg, self.seed, name, self.embed_std).to(torch.float32)
+
+
 class RefModel:
-    def __init__(self, cfg, weights: Dict[str, torch.Tensor], rope: torch.Tensor, emulate_bf16: bool = False):
+    def __init__(self, cfg, weights, rope: torch.Tensor, emulate_bf16: bool = False):
         self.cfg, self.emu = cfg, emulate_bf16
-        self.w = {k: v.to(torch.float32) for k, v in weights.items()}
+        self.w = weights if isinstance(weights, StreamedWeights) else {k: v.to(torch.float32) for k, v in weights.items()}
         self.rope = rope  # [max_pos, hd/2, 2]
 
     # -- pieces ---------------------------------------------------------------
@@ -80,8 +94,9 @@ class RefModel:
         return x + m @ w[f"wd.{i}"].T
 
     def forward(self, tokens: torch.Tensor, pos0: int = 0, cache: Optional[list] = None,
-                last_only: bool = True) -> torch.Tensor:
-        """tokens [B,S] int64 at positions pos0..pos0+S-1 -> logits [B,V] (last) or [B,S,V]."""
+                last_only: bool = True, last_n: Optional[int] = None) -> torch.Tensor:
+        """tokens [B,S] int64 at positions pos0..pos0+S-1 -> logits [B,V] (last), [B,S,V], or
+        (last_only=False, last_n=n) only the last n positions [B,n,V]."""
         B, S = tokens.shape
         x = self.w["embed"][tokens]
         pos = torch.arange(pos0, pos0 + S)[None, :].expand(B, S)
@@ -93,6 +108,8 @@ class RefModel:
             x = self._layer(i, x, pos, cache, mask)
         if last_only:
             x = x[:, -1:, :]
+        elif last_n is not None:
+            x = x[:, -last_n:, :]
         h = _r(self._norm(x, self.w["norm"]), self.emu)
         head = self.w["embed"] if self.cfg.tied else self.w["lm_head"]
         logits = h @ head.T
