@@ -96,11 +96,12 @@ __device__ __forceinline__ void warp_attn_fetch(uint32_t ring_u, int blk, int ke
 // knew / vnew (the new token's k, v) are in the warp's shared memory and the first NS-1 stages have been
 // requested (one committed cp.async group each).  Streams the keys key0 .. T-1, merges with n_part
 // shared-prefix partials (rows prow0 + h of part_o / part_ml) and stores the G normalised rows at out_pair.
+// The loop alone: keys key0 .. T-1 in nblk blocks (the first NS-1 already requested); leaves the unnormalised
+// accumulator rows o (rows g and g + 8 of the 16-row tile), their running maxima and (quad-reduced) sums.
 template <int HD, int G, int KB, int NS>
-__device__ __forceinline__ void warp_attn_main(uint8_t *Qs, int nblk, int key0, int T, int p, const __nv_bfloat16 *__restrict__ pages,
+__device__ __forceinline__ void warp_attn_loop(uint8_t *Qs, int nblk, int key0, int T, int p, const __nv_bfloat16 *__restrict__ pages,
                                                const int *__restrict__ bt, int n_kv, int kvh, int lane, float scale_log2,
-                                               __nv_bfloat16 *__restrict__ out_pair, const float *__restrict__ part_o,
-                                               const float *__restrict__ part_ml, int n_part, size_t part_rows, size_t prow0) {
+                                               float (&o)[HD / 8][4], float (&mrow)[2], float (&lrow)[2], bool has_new = true) {
     constexpr int CH = HD / 8;
     constexpr int QT = 16 * HD * 2, ST = KB * HD * 2;
     const uint32_t qs_u = (uint32_t)__cvta_generic_to_shared(Qs), ring_u = qs_u + QT;
@@ -109,11 +110,11 @@ __device__ __forceinline__ void warp_attn_main(uint8_t *Qs, int nblk, int key0, 
 #pragma unroll
     for (int ks = 0; ks < HD / 16; ++ks) ldsm_x4(qf[ks], qs_u + swz<HD>(lane & 15, 2 * ks + (lane >> 4)));
 
-    float o[HD / 8][4];
 #pragma unroll
     for (int j = 0; j < HD / 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
-    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
-    const int g = lane >> 2, tq = lane & 3;
+    mrow[0] = mrow[1] = -INFINITY;
+    lrow[0] = lrow[1] = 0.f;
+    const int tq = lane & 3;
 
     for (int blk = 0; blk < nblk; ++blk) {
         if (blk + NS - 1 < nblk) warp_attn_fetch<HD, KB, NS>(ring_u, blk + NS - 1, key0, T, p, pages, bt, n_kv, kvh, lane);
@@ -123,7 +124,7 @@ __device__ __forceinline__ void warp_attn_main(uint8_t *Qs, int nblk, int key0, 
         const uint32_t ks_u = ring_u + (uint32_t)(blk % NS) * 2 * ST, vs_u = ks_u + ST;
         const int c0 = key0 + blk * KB;
         const int n = min(T - c0, KB);
-        if (blk == nblk - 1) {                        // the new token's row comes from this warp, not from the copy
+        if (has_new && p >= c0 && p < c0 + KB) {      // the new token's row comes from this warp, not from the copy
             if (lane < CH) {
                 uint8_t *ring = Qs + QT + (blk % NS) * 2 * ST;
                 *reinterpret_cast<uint4 *>(ring + swz<HD>(p - c0, lane)) = reinterpret_cast<const uint4 *>(knew)[lane];
@@ -195,6 +196,16 @@ __device__ __forceinline__ void warp_attn_main(uint8_t *Qs, int nblk, int key0, 
         lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 1);
         lrow[r] += __shfl_xor_sync(0xffffffffu, lrow[r], 2);
     }
+}
+
+template <int HD, int G, int KB, int NS>
+__device__ __forceinline__ void warp_attn_main(uint8_t *Qs, int nblk, int key0, int T, int p, const __nv_bfloat16 *__restrict__ pages,
+                                               const int *__restrict__ bt, int n_kv, int kvh, int lane, float scale_log2,
+                                               __nv_bfloat16 *__restrict__ out_pair, const float *__restrict__ part_o,
+                                               const float *__restrict__ part_ml, int n_part, size_t part_rows, size_t prow0) {
+    float o[HD / 8][4], mrow[2], lrow[2];
+    warp_attn_loop<HD, G, KB, NS>(Qs, nblk, key0, T, p, pages, bt, n_kv, kvh, lane, scale_log2, o, mrow, lrow);
+    const int g = lane >> 2, tq = lane & 3;
     // merge with the shared-prefix partials (if any), normalise, store the G real rows
 #pragma unroll
     for (int r = 0; r < 2; ++r) {

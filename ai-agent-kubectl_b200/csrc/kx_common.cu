@@ -1,5 +1,7 @@
 #include "kx_common.cuh"
 #include <stdarg.h>
+#include <stdlib.h>
+#include <string>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -15,6 +17,12 @@ void set_error(const char *fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(t_err, sizeof t_err, fmt, ap);
     va_end(ap);
+}
+
+bool debug_flag(const char *name) {
+    const char *v = getenv("KX_DEBUG");              // read when an engine is created, not on the request path
+    const std::string flags = std::string(",") + (v ? v : "") + ",";
+    return flags.find(std::string(",") + name + ",") != std::string::npos;
 }
 
 namespace {

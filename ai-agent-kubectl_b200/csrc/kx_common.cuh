@@ -17,6 +17,16 @@ enum ScratchTag { SCRATCH_K9_QUEUE = 0, SCRATCH_GEMM = 1, SCRATCH_ATTN = 2, SCRA
 int stream_scratch(cudaStream_t stream, int tag, size_t bytes, void **out, bool zero_on_alloc = false);
 void release_scratch();
 
+// Development switches, all in ONE environment variable read when an engine is created: KX_DEBUG is a comma-separated list of
+//   trace            per-launch timeline of the decode step (kx_engine_trace)
+//   no-fused-norm    decode keeps separate RMSNorm launches (A/B against the deferred-norm epilogues)
+//   no-attn-tc       prefill attention on the mma.sync kernel
+//   no-shared-prefix every sequence re-reads a cached prefix in decode attention
+//   no-fused-argmax  lm_head writes logits, a second kernel picks the token
+//   prefetch         decode GEMMs ask the L2 for the weights of a later launch (experiment: slower on B200)
+// Nothing in the product path depends on it being set.
+bool debug_flag(const char *name);
+
 inline void count_launch(int k = 1) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
 // Function attributes (dynamic shared memory limit, cluster opt-in) are per device: a process that drives several
@@ -30,11 +40,12 @@ struct PerDeviceOnce {
 };
 
 // ---- optional kernel timeline (diagnostic, KX_TRACE=1 at engine creation) -----------------------------
-// A slot is four u64 globaltimer values of one launch: [0] earliest CTA start, [1] earliest return from
+// A slot is eight u64 globaltimer values of one launch: [0] earliest CTA start, [1] earliest return from
 // griddepcontrol.wait (the predecessor's results are visible), [2] latest "main loop done" mark, [3] latest
-// CTA end.  The host hands every instrumented launch its slot (or NULL when tracing is off).
+// CTA end, [4] latest "split-K slices exchanged" mark, [5..7] spare.  The host hands every instrumented launch its
+// slot (or NULL when tracing is off).
 struct TraceCtx {
-    unsigned long long *buf = nullptr;     // device, cap slots of 4 u64
+    unsigned long long *buf = nullptr;     // device, cap slots of 8 u64
     int cap = 0, n = 0;
     const char *names[2048];
 };
@@ -43,7 +54,7 @@ inline unsigned long long *trace_slot(const char *name) {
     TraceCtx *t = t_trace;
     if (!t || t->n >= t->cap || t->n >= 2048) return nullptr;
     t->names[t->n] = name;
-    return t->buf + 4 * (size_t)(t->n++);
+    return t->buf + 8 * (size_t)(t->n++);
 }
 #ifdef __CUDACC__
 __device__ __forceinline__ unsigned long long trace_now() {

@@ -33,9 +33,13 @@ struct kx_engine {
     // decode attention over the shared prefix: per-chunk partial (O, max/sum) of every (sequence, q head)
     float *prefix_o = nullptr, *prefix_ml = nullptr;
     size_t prefix_rows = 0;                        // capacity in (chunk, sequence, head) rows
-    bool attn_tc = true;                           // prefill attention on tcgen05 (kx_attn_tc.cu) for head_dim 64; KX_ATTN_TC=0: mma.sync kernel
+    bool attn_tc = true;                           // prefill attention on tcgen05 (kx_attn_tc.cu) for head_dim 64
     int64_t attn_tc_launches = 0;
-    bool share_prefix = true;                      // KX_SHARED_PREFIX=0: every sequence re-reads the prefix (for A/B timing)
+    bool share_prefix = true;                      // decode attention reads a cached prefix once per 64 query rows
+    bool fused_norm = true;                        // decode (batch < 256, no TP): RMSNorm deferred into the GEMM epilogues
+    float *ssq = nullptr, *col_rinv = nullptr;     // ... per-tile sums of squares [hidden / 128][max_batch]; 1 / rms per column
+    bool prefetch = false;                         // KX_DEBUG=prefetch: kernels ask the L2 for a later launch's weights (measured: no gain)
+    bool fused_argmax = true;                      // lm_head keeps (max, index) per tile instead of writing logits
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
     const float *rope;
@@ -80,6 +84,8 @@ struct kx_engine {
 
 namespace {
 
+constexpr int kP2pSlots = 8192;                    // flag / epoch slots of the fused tensor-parallel all-reduce
+
 void drop_step_graphs(kx_engine *e) {
     for (auto &g : e->step_graphs) cudaGraphExecDestroy(g.exec);
     e->step_graphs.clear();
@@ -115,7 +121,10 @@ int pick_splits(int features, int k, int b_tiles) {
 
 __global__ void trace_reset_kernel(unsigned long long *buf, int slots) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < slots) { buf[4 * i] = ~0ull; buf[4 * i + 1] = ~0ull; buf[4 * i + 2] = 0; buf[4 * i + 3] = 0; }
+    if (i < slots) {
+        buf[8 * i] = ~0ull; buf[8 * i + 1] = ~0ull;
+        for (int k = 2; k < 8; ++k) buf[8 * i + k] = 0;
+    }
 }
 
 __global__ void advance_step_kernel(int *pos, int *step, int n) {
@@ -139,6 +148,11 @@ struct GemmCall {
     bool tp_fused = false;                         // EPI_RESID + all-reduce over peer memory in the epilogue
     size_t split_stride = 0;                       // pair kernel with splits > 1: distance between the slices' outputs
     const char *label = "gemm";                    // name in the diagnostic timeline
+    bool ssq_in = false;                           // deferred RMSNorm: scale the accumulator columns by 1 / rms (from e->ssq)
+    const void *norm_g = nullptr;                  // EPI_RESID_NORM: gain of the next norm
+    const float *col_scale = nullptr;
+    const void *pf_ptr = nullptr;                  // weights of a later launch to pull into the L2
+    size_t pf_bytes = 0;
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
@@ -146,6 +160,11 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     p.a_rows = c.a_rows; p.b_rows = c.b_rows; p.k = c.k; p.out = c.out; p.ldo = c.ldo; p.bias = c.bias;
     p.swap = c.swap; p.epilogue = c.epi; p.splits = c.splits; p.split_stride = c.split_stride;
     p.trace = trace_slot(c.label);
+    p.ssq_ld = e->d.max_batch; p.ssq_tiles = e->d.hidden / 128; p.norm_eps = e->d.eps; p.norm_inv_n = 1.0f / (float)e->d.hidden;
+    if (c.ssq_in) p.ssq_in = e->ssq;
+    if (c.epi == EPI_RESID_NORM) { p.norm_g = c.norm_g; p.norm_out = e->xn; p.ssq_out = e->ssq; }
+    p.col_scale = c.col_scale;
+    if (e->prefetch) { p.pf_ptr = c.pf_ptr; p.pf_bytes = c.pf_bytes; }
     if (c.extra) {
         p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
         p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
@@ -154,6 +173,9 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     if (c.tp_fused) {
         p.tp_peer_recv = e->p2p_peer_recv; p.tp_peer_flag = e->p2p_peer_flag; p.tp_recv = e->p2p_recv;
         p.tp_flag = e->p2p_flag; p.tp_epoch = e->p2p_epoch; p.tp_rows = e->p2p_rows;
+        p.tp_seq = (int)(e->p2p_launches & 0x7fffffff);
+        const int64_t slots = (int64_t)((c.a_rows + 127) / 128) * ((c.b_rows + c.bn - 1) / c.bn) * (c.splits < 1 ? 1 : c.splits);
+        KX_REQUIRE(slots <= kP2pSlots, KX_ETOOBIG, "engine: fused all-reduce would use %lld flag slots, %d exist", (long long)slots, kP2pSlots);
     }
     if (!c.swap && c.b_half) return gemm_launch_pair(*c.a, *c.b_half, p, c.pair_bn, st);
     KX_REQUIRE(gemm_scratch_bytes(p, c.bn) <= e->scratch_bytes, KX_ENOMEM, "engine: split-K scratch too small");
@@ -179,12 +201,12 @@ int linear_pair_bn(const Linear &l, int M) {
     const int t256 = m_pairs * ((l.features + 255) / 256), t128 = m_pairs * ((l.features + 127) / 128);
     // 256-wide tiles halve the operand bytes per flop; a partial last tile is worth it up to ~15 % padding
     // (Qwen2.5-0.5B: 896 and 1152 features -> prefill 17.2 -> 16.7 ms)
-    static const int waste_pct = [] { const char *v = getenv("KX_PAIR256_MAX_WASTE"); return v ? atoi(v) : 15; }();
+    constexpr int waste_pct = 15;
     const int padded = ((l.features + 255) / 256) * 256;
     const bool little_waste = (padded - l.features) * 100 <= waste_pct * l.features;   // partial last tile is cheap enough
     if ((l.features % 256 == 0 || l.features >= 2048 || little_waste) && t256 >= 64) return 256;
     // fewer 128-wide tiles than this leave most SMs idle: the weight-streaming kernel with split-K covers them
-    static const int min128 = [] { const char *v = getenv("KX_PAIR128_MIN_TILES"); return v ? atoi(v) : 24; }();
+    constexpr int min128 = 24;
     return t128 >= min128 ? 128 : 0;
 }
 
@@ -218,7 +240,7 @@ int norm_rows(kx_engine *e, const void *g, int M, const int *row_map, cudaStream
 // parallelism every rank holds a partial sum: it goes to tp_buf, is all-reduced, then added.
 int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool decode) {
     const kx_model_desc &d = e->d;
-    static const int splitk_min_m = [] { const char *v = getenv("KX_SPLITK_MIN_M"); return v ? atoi(v) : 257; }();
+    constexpr int splitk_min_m = 257;
     if (d.tp_size <= 1 && decode && M >= splitk_min_m && M <= 512 && d.hidden % 256 == 0 && e->splitk_part) {
         // 2 x (hidden / 256) tiles of 256 x 256 would use a fraction of the SMs: cut k so that ~64 CTA pairs work,
         // slices land in splitk_part and the next RMSNorm adds them to the residual
@@ -245,8 +267,9 @@ int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool dec
                    e->resid, d.hidden, nullptr};
         c.tp_fused = true;
         c.label = l.label;
+        const int rc = run_gemm(e, c, st);             // its receive half-buffer is picked by the parity of p2p_launches
         ++e->p2p_launches;
-        return run_gemm(e, c, st);
+        return rc;
     }
     KX_REQUIRE(e->comm && e->allreduce, KX_EINVAL, "engine: tensor parallelism needs kx_engine_set_collectives");
     KX_TRY(linear(e, l, M, EPI_F32, e->tp_buf, d.hidden, nullptr, st));
@@ -305,6 +328,51 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     return KX_OK;
 }
 
+// Decode on the deferred-RMSNorm path (single GPU replica, batch < 256: every projection is a swap-AB cluster GEMM).
+bool fused_norm_decode(const kx_engine *e, int B) { return e->fused_norm && e->d.tp_size <= 1 && B < 256; }
+
+// One layer of a decode step with the RMSNorms folded into the projections (kx_gemm.cuh): five launches --
+// QKV (scaled by 1 / rms), attention, wo (+ residual, prepares norm 2), gate/up (scaled, SwiGLU), down (+ residual,
+// prepares the next layer's norm 1 or the final norm).  e->xn holds bf16(residual * g) of the pending norm, e->ssq
+// its per-tile sums of squares.  Each GEMM also asks the L2 for the weights of the launch after next.
+int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    LayerPlan &L = e->layers[li];
+    const int bn = gemm_pick_bn(1, B), bi = bn_index(bn);
+    const int b_tiles = (B + bn - 1) / bn;
+    const bool last = li + 1 == d.layers;
+    const size_t w_qkv = (size_t)e->qkv_dim * d.hidden * 2, w_o = (size_t)d.hidden * e->q_dim * 2,
+                 w_gu = (size_t)2 * d.inter * d.hidden * 2, w_d = (size_t)d.hidden * d.inter * 2;
+    auto gemm = [&](const CUtensorMap *w, const CUtensorMap *x, int features, int k, int epi, void *out, int ldo, const float *bias,
+                    const char *label, bool ssq_in, const void *norm_g, const void *pf, size_t pf_bytes) {
+        GemmCall c{w, x + bi, features, B, k, epi, 1, pick_splits(features, k, b_tiles), bn, out, ldo, bias};
+        c.label = label; c.ssq_in = ssq_in; c.norm_g = norm_g; c.pf_ptr = pf; c.pf_bytes = pf_bytes;
+        return run_gemm(e, c, st);
+    };
+    // Prefetch plan.  QKV, attention and wo are latency bound (their weights sit in the stage rings before their
+    // inputs exist) and leave HBM idle; gate/up is the one projection that has to stream (67 MB for Llama-3.2-1B).
+    // So the QKV launch asks the L2 for the part of gate/up's weights the rings will not already hold, and gate/up
+    // does the same for the down projection.
+    const size_t gu_skip = (size_t)32 << 20 < w_gu ? (size_t)16 << 20 : w_gu;   // the first 16 MB arrive through the rings anyway
+    KX_TRY(gemm(&L.wqkv, e->xn_b, e->qkv_dim, d.hidden, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, "qkv", true, nullptr,
+                (const char *)L.w.wgu + gu_skip, w_gu - gu_skip));
+    int key0 = 0, n_part = 0;
+    if (e->share_prefix && e->prefix_len >= 64 && B >= 2 && e->prefix_o &&
+        (size_t)attn_prefix_parts(B, d.n_q, d.n_kv, e->prefix_len, nullptr) * B * d.n_q <= e->prefix_rows) {
+        KX_TRY(op_attn_prefix(e->qkv, e->qkv_dim, L.kv_pages, e->block_table + (size_t)d.max_batch * e->max_pages, e->pos,
+                              e->rope, B, d.n_q, d.n_kv, d.head_dim, e->prefix_len, e->prefix_o, e->prefix_ml, &n_part, st));
+        key0 = e->prefix_len;
+    }
+    KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos,
+                          e->rope, B, max_T, d.n_q, d.n_kv, d.head_dim, key0, e->prefix_o, e->prefix_ml, n_part, st));
+    KX_TRY(gemm(&L.wo, e->attn_b, d.hidden, e->q_dim, EPI_RESID_NORM, e->resid, d.hidden, nullptr, "wo", false, L.w.ln2, nullptr, 0));
+    KX_TRY(gemm(&L.wgu, e->xn_b, 2 * d.inter, d.hidden, EPI_SWIGLU, e->mlp, d.inter, nullptr, "gate_up", true, nullptr, L.w.wd, w_d));
+    KX_TRY(gemm(&L.wd, e->mlp_b, d.hidden, d.inter, EPI_RESID_NORM, e->resid, d.hidden, nullptr, "down", false,
+                last ? e->norm : e->layers[li + 1].w.ln1, nullptr, 0));
+    (void)w_qkv; (void)w_o;
+    return KX_OK;
+}
+
 // greedy token per sequence from e->logits (this rank's vocabulary shard under tensor parallelism)
 int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
     const kx_model_desc &d = e->d;
@@ -317,9 +385,11 @@ int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
 }
 
 // final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
-int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st) {
+// deferred: e->xn already holds bf16(residual * g_final) and e->ssq its sums of squares (decode on the fused-norm path);
+// the caller's tail kernel then stores the token instead of store_token_kernel
+int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st, bool deferred = false) {
     const kx_model_desc &d = e->d;
-    KX_TRY(norm_rows(e, e->norm, B, row_map, st));
+    if (!deferred) KX_TRY(norm_rows(e, e->norm, B, row_map, st));
     const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden, "lm_head"};
     // Nobody asked for the logits: the lm_head epilogue keeps only (max, index) per token and tile, a small
     // second kernel finishes the pick; [B, vocab] is never written.  (Small vocabularies take the cluster split-K
@@ -327,7 +397,7 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
     const int pbn = linear_pair_bn(head, B);
     const int v_tiles = (d.vocab + 127) / 128;
     const int sbn = gemm_pick_bn(1, B);
-    static const bool want_fused = [] { const char *v = getenv("KX_FUSED_ARGMAX"); return !(v && v[0] == '0'); }();
+    const bool want_fused = e->fused_argmax;
     const bool fused = want_fused && !d_logits_step && e->argmax_parts &&
                        (pbn || (B <= 512 && pick_splits(d.vocab, d.hidden, (B + sbn - 1) / sbn) == 1));
     if (fused) {
@@ -342,15 +412,25 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
             KX_REQUIRE(rc == 0, KX_ECUDA, "engine: ncclAllGather failed with %d", rc);
             KX_TRY(op_pick(e->tp_gathered, d.tp_size, B, e->next_tok, st));
         }
+        if (deferred) return KX_OK;                    // argmax is unchanged by the positive per-token factor 1 / rms
         store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
         count_launch();
         KX_CUDA(cudaGetLastError());
         return KX_OK;
     }
-    KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
+    if (deferred) {                                    // the logits themselves are wanted: scale column b by 1 / rms_b
+        KX_TRY(op_col_rinv(e->ssq, d.hidden / 128, d.max_batch, B, d.hidden, d.eps, e->col_rinv, st));
+        const int bn = gemm_pick_bn(1, B), bi = bn_index(bn);
+        GemmCall c{&e->lm_head_map, e->xn_b + bi, d.vocab, B, d.hidden, EPI_F32, 1, 1, bn, e->logits, d.vocab, nullptr};
+        c.label = "lm_head"; c.col_scale = e->col_rinv;
+        KX_TRY(run_gemm(e, c, st));
+    } else {
+        KX_TRY(linear(e, head, B, EPI_F32, e->logits, d.vocab, nullptr, st));
+    }
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
     KX_TRY(greedy_pick(e, B, st));
+    if (deferred) return KX_OK;
     store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
     count_launch();
     KX_CUDA(cudaGetLastError());
@@ -370,8 +450,11 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     kx_engine *e = new kx_engine();
     e->d = d;
     if (cudaGetDevice(&e->device) != cudaSuccess) { delete e; set_error("kx_engine_create: no current CUDA device"); return KX_ECUDA; }
-    if (const char *v = getenv("KX_SHARED_PREFIX")) e->share_prefix = v[0] != '0';
-    if (const char *v = getenv("KX_ATTN_TC")) e->attn_tc = v[0] == '1';
+    e->share_prefix = !debug_flag("no-shared-prefix");
+    e->attn_tc = !debug_flag("no-attn-tc");
+    e->fused_norm = !debug_flag("no-fused-norm");
+    e->prefetch = debug_flag("prefetch");
+    e->fused_argmax = !debug_flag("no-fused-argmax");
     if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
     e->q_dim = d.n_q * d.head_dim;
@@ -468,20 +551,19 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
         e->splitk_cap = (size_t)8 * (d.max_batch < 512 ? d.max_batch : 512) * d.hidden;
         KX_E(dev_alloc(e, (void **)&e->splitk_part, e->splitk_cap * sizeof(float)));
     }
-    if (const char *v = getenv("KX_TRACE")) {
-        if (v[0] == '1') {
-            e->trace = new TraceCtx();
-            e->trace->cap = 2048;
-            KX_E(dev_alloc(e, (void **)&e->trace->buf, sizeof(unsigned long long) * 4 * e->trace->cap));
-        }
+    if (debug_flag("trace")) {
+        e->trace = new TraceCtx();
+        e->trace->cap = 2048;
+        KX_E(dev_alloc(e, (void **)&e->trace->buf, sizeof(unsigned long long) * 8 * e->trace->cap));
     }
+    KX_E(dev_alloc(e, (void **)&e->ssq, sizeof(float) * (size_t)(d.hidden / 128) * d.max_batch));
+    KX_E(dev_alloc(e, (void **)&e->col_rinv, sizeof(float) * (size_t)d.max_batch));
 #undef KX_E
     *out = e;
     return KX_OK;
 }
 
 // ---- fused P2P all-reduce set-up: export this rank's buffers, import the peer's (CUDA IPC) ----
-namespace { constexpr int kP2pSlots = 8192; }
 
 extern "C" int kx_engine_p2p_export(kx_engine *e, void *handles /* 2 x 64 bytes */) {
     KX_REQUIRE(e && handles, KX_EINVAL, "kx_engine_p2p_export: NULL argument");
@@ -590,7 +672,7 @@ extern "C" int kx_engine_trace(kx_engine *e, uint64_t *h_slots, int32_t max_slot
     if (!e->trace) return 0;
     const int n = max_slots < e->trace->n ? max_slots : e->trace->n;
     KX_CUDA(cudaStreamSynchronize(e->stream));
-    KX_CUDA(cudaMemcpy(h_slots, e->trace->buf, sizeof(uint64_t) * 4 * n, cudaMemcpyDeviceToHost));
+    KX_CUDA(cudaMemcpy(h_slots, e->trace->buf, sizeof(uint64_t) * 8 * n, cudaMemcpyDeviceToHost));
     return n;
 }
 
@@ -664,6 +746,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_CUDA(cudaStreamSynchronize(st));
     }
     const int max_T = P + S + n_new;
+    const bool fused = fused_norm_decode(e, B);
     auto step_once = [&](float *logits_dst) -> int {
         if (e->trace) {                                // timeline of this step: slots handed out from 0 again
             e->trace->n = 0;
@@ -671,6 +754,13 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
             t_trace = e->trace;
         }
         struct Untrace { ~Untrace() { t_trace = nullptr; } } untrace;
+        if (fused) {
+            // the previous tail kernel (or `begin` below) left this step's input in resid / xn / ssq and advanced pos
+            for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward_fused(e, li, B, max_T, st));
+            KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st, true));
+            return op_decode_tail(e->next_tok, e->out_ids, n_new, P + S - 1, e->pos, e->embed, e->layers[0].w.ln1, e->resid, e->xn,
+                                  e->ssq, d.max_batch, B, d.hidden, 1, st);
+        }
         // pos[b] currently holds the previous token's position
         advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);
         count_launch();
@@ -679,6 +769,9 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st));
         return KX_OK;
     };
+    if (fused && n_new > 1)      // first decode step's input: embedding of the token prefill chose, pos -> P + S
+        KX_TRY(op_decode_tail(e->next_tok, e->out_ids, n_new, P + S - 1, e->pos, e->embed, e->layers[0].w.ln1, e->resid, e->xn,
+                              e->ssq, d.max_batch, B, d.hidden, 0, st));
     int steps_done = 0;
     if (n_new > 1 && d_logits) {
         for (int t = 1; t < n_new; ++t) KX_TRY(step_once(d_logits + (size_t)t * B * d.vocab));

@@ -50,7 +50,10 @@ template <int BN> struct Cfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
-__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+// x * sigmoid(x) with the hardware reciprocal (MUFU.RCP, 1 ulp, no slow path): a full fp32 division is ~40 dependent
+// instructions plus a call for the denormal case, which the decode epilogues (one warp per scheduler) feel.  The
+// result is rounded to bf16 right away, so the last fp32 bit does not matter.
+__device__ __forceinline__ float silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
@@ -134,7 +137,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams &p, float (&v)[3
                 float *o = reinterpret_cast<float *>(p.out) + (size_t)b * p.ldo + arow;
                 if (atomic_resid) atomicAdd(o, v[j]); else *o += v[j];
             } else {
-                reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] = v[j];
+                reinterpret_cast<float *>(p.out)[(size_t)b * p.ldo + arow] = p.col_scale ? __fmul_rn(v[j], p.col_scale[b]) : v[j];
             }
         }
     }
@@ -674,6 +677,26 @@ __device__ __forceinline__ void epilogue_swap_elem(const GemmParams &p, float v,
 
 constexpr int kMaxSplits = 16;   // cluster size: 8 is the portable limit, 16 needs the non-portable opt-in (see max_cluster_splits)
 
+// bulk copy from this CTA's shared memory into a cluster CTA's shared memory; completes `bytes` on an mbarrier of the
+// DESTINATION CTA when the data has landed (both addresses 16-byte aligned, bytes a multiple of 16)
+__device__ __forceinline__ void dsmem_bulk_copy(uint32_t dst_cluster_addr, uint32_t src_cta_addr, uint32_t bytes, uint32_t dst_cluster_mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_cluster_addr), "r"(src_cta_addr), "r"(bytes), "r"(dst_cluster_mbar) : "memory");
+}
+// execution barrier over the cluster without memory ordering (nothing is handed over through memory)
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_plain() { asm volatile("barrier.cluster.wait.aligned;" ::: "memory"); }
+
+// Split-K reduction, push model.  Batch column j of the tile is owned by cluster rank j / cols_per.  Once every CTA
+// of the cluster has finished its MMAs (one cluster barrier, execution only: nobody's stage ring is in use any more),
+// each CTA stages its accumulator (TMEM -> registers -> shared memory, 32 columns at a time, column-major so that a
+// rank's columns are contiguous) and sends every owner its columns with ONE bulk shared-to-shared copy per (chunk,
+// owner) into the owner's slot [source rank]; the copy engine completes the bytes on the owner's `xchg` mbarrier,
+// which the owner armed with the byte count it expects.  An owner whose slices have landed adds them from its OWN
+// shared memory in rank order (deterministic) and applies the epilogue -- no second barrier, no fence, CTAs leave
+// independently.  (Per-element st.async stores cost 2-3 us per launch: 8,192 four-byte transactions per CTA.)  (The first version pulled: every owner loaded the other CTAs' partials over DSMEM column by
+// column, a full round trip each, between two release/acquire cluster barriers -- 5 us per launch, 13 us for the
+// 32 columns of a gate/up CTA, more than the weight streaming itself.)
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 2)
 kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
@@ -684,31 +707,57 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::STAGES * C::STAGE_BYTES);
     uint64_t *empty = full + C::STAGES;
     uint64_t *tmem_full = empty + C::STAGES;
-    uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(tmem_full + 1);
-    float *partial = reinterpret_cast<float *>(smem);          // [BN][128] fp32, reuses the drained stage ring
-    static_assert(BN * BM * 4 <= C::STAGES * C::STAGE_BYTES, "partial tile must fit in the stage ring");
+    uint64_t *xchg = tmem_full + 1;                            // split-K slices of this CTA's columns have landed
+    uint32_t *tmem_holder = reinterpret_cast<uint32_t *>(xchg + 1);
+    float *recv = reinterpret_cast<float *>(smem);             // [S][cols_per][128] fp32, reuses the drained stage ring
+    constexpr int kRecvBytes = (BN + kMaxSplits) * BM * 4;     // S * cols_per <= BN + S - 1 columns of 512 bytes
+    constexpr int kStageBufs = BN <= 64 ? (BN / 32 < 2 ? 1 : 2) : 1;   // send staging: 32 columns x 128 rows fp32 each
+    float *stage = reinterpret_cast<float *>(smem + kRecvBytes);
+    static_assert(kRecvBytes + kStageBufs * 32 * BM * 4 <= C::STAGES * C::STAGE_BYTES, "exchange buffers must fit in the stage ring");
+    __shared__ float rinv_s[BN];                               // deferred RMSNorm: 1 / rms of every batch column of this tile
+    __shared__ float sq_s[EPI == EPI_RESID_NORM ? 4 * BN : 1]; // EPI_RESID_NORM: per-warp sums of squares
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
     asm volatile("griddepcontrol.launch_dependents;");        // our own dependents may begin their prologue
-    if (threadIdx.x == 0) trace_min(p.trace, 0);
+    if (threadIdx.x == 0) {
+        trace_min(p.trace, 0);
+        if (p.pf_ptr)     // weights of a later launch: ask the L2 for them now
+            l2_prefetch_share(p.pf_ptr, p.pf_bytes, (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z,
+                              gridDim.x * gridDim.y * gridDim.z);
+    }
     const int S = gridDim.z, z = blockIdx.z;                  // cluster = the z column; rank == z
     const int total_kb = (p.k + BK - 1) / BK;
     const int kb0 = z * p.kb_per_split;
     const int nkb = min(total_kb - kb0, p.kb_per_split);
+    const int cols_per = (BN + S - 1) / S;
+    const int j0 = z * cols_per, j1 = min(min(BN, j0 + cols_per), p.b_rows - n0);   // batch columns this CTA owns
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
         mbar_init(tmem_full, 1);
+        mbar_init(xchg, 1);
         fence_barrier_init();
+        if (S > 1) mbar_expect_tx(xchg, (uint32_t)(max(j1 - j0, 0) * S * BM * 4));   // every rank sends 128 floats per owned column
     }
     if (warp == 1) tmem_alloc(tmem_holder, C::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_holder;
+    const int q = warp & 3, r = q * 32 + lane;                // epilogue warps: TMEM lane quarter, accumulator row
+    const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+    if (EPI == EPI_RESID_NORM && warp >= 2 && m0 + r < p.a_rows) {
+        // The residual rows this thread will update were written two launches ago and ~100 MB of weights have
+        // streamed through the L2 since: pull their lines (and the gain) back in now, while the predecessor still
+        // runs -- a demand miss in the epilogue queues behind the weight tiles of the next two launches (8 us).
+        // Only the L2 is warmed, so data that is still being produced is not a problem.
+        for (int j = j0; j < j1; ++j)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float *>(p.out) + (size_t)(n0 + j) * p.ldo + m0 + r));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const __nv_bfloat16 *>(p.norm_g) + m0 + r));
+    }
 
     if (warp == 0) {
         if (lane == 0) {
@@ -750,82 +799,227 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             umma_commit(tmem_full);
         }
     } else {
-        const int q = warp & 3, r = q * 32 + lane;
         asm volatile("griddepcontrol.wait;" ::: "memory");     // outputs (and the residual read) follow the predecessor
+        if (p.ssq_in && r < BN) {                              // deferred RMSNorm: 1 / rms of batch column n0 + r, tiles added in order
+            float ss = 0.f;
+            if (n0 + r < p.b_rows)
+                for (int t = 0; t < p.ssq_tiles; ++t) ss += p.ssq_in[(size_t)t * p.ssq_ld + n0 + r];
+            rinv_s[r] = 1.0f / sqrtf(ss * p.norm_inv_n + p.norm_eps);
+        }
         mbar_wait(tmem_full, 0);                               // all MMAs retired: the stage ring is free
         tc_fence_after();
         if (threadIdx.x == 64) trace_max(p.trace, 2);
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-#pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-            float v[32];
-            tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
-            tmem_ld_wait();
+    }
+
+    const bool probe = p.trace && threadIdx.x == 64 && blockIdx.y == 0 && blockIdx.z == 0 && blockIdx.x == 0;
+    long long ckb = 0, ckp = 0, ckw = 0, ck0 = 0, ck1 = 0;
+    if (probe) ckb = clock64();
+    // EPI_RESID_NORM: the residual values of the first group of owned columns, requested now so that their latency
+    // hides behind the split-K exchange (the predecessor is complete: the epilogue warps are past griddepcontrol.wait)
+    float xres[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (EPI == EPI_RESID_NORM && warp >= 2 && m0 + r < p.a_rows) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) partial[(c + j) * BM + r] = v[j];
+        for (int c = 0; c < 8; ++c)
+            if (j0 + c < j1) xres[c] = reinterpret_cast<const float *>(p.out)[(size_t)(n0 + j0 + c) * p.ldo + m0 + r];
+    }
+    if (S > 1) {
+        __syncthreads();
+        cluster_arrive_relaxed();                              // this CTA no longer reads its stage ring ...
+        cluster_wait_plain();                                  // ... and neither does any other: slices may be stored into it
+        if (probe) ckp = clock64();
+        if (warp >= 2) {
+            const uint32_t local = smem_u32(recv), bar_local = smem_u32(xchg);
+            const int valid = min(BN, p.b_rows - n0);          // columns past the batch are never sent
+            int chunk = 0;
+#pragma unroll 1
+            for (int c = 0; c < valid; c += 32, ++chunk) {
+                float *buf = stage + (chunk % kStageBufs) * (32 * BM);
+                if (chunk >= kStageBufs) {                     // the copies that read this buffer have finished reading it
+                    if (warp == 2) bulk_wait_group_read0();       // (bulk groups are per thread: every sending lane waits for its own)
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+                float v[32];
+                tmem_ld_32x32(taddr + c, reinterpret_cast<uint32_t(&)[32]>(v));
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) buf[j * BM + r] = v[j];
+                fence_proxy_async_smem();                      // generic-proxy writes before the copy engine reads them
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (warp == 2) {                               // lane l sends the l-th owner that has columns in this chunk
+                    const int c_end = min(c + 32, valid);
+                    const int first = c / cols_per, owner = first + lane;
+                    const int a = max(owner * cols_per, c), e = min((owner + 1) * cols_per, c_end);
+                    if (owner < S && e > a)
+                        dsmem_bulk_copy(dsmem_addr(local, (uint32_t)owner) + (uint32_t)((z * cols_per + (a - owner * cols_per)) * BM * 4),
+                                        smem_u32(buf) + (uint32_t)((a - c) * BM * 4), (uint32_t)((e - a) * BM * 4),
+                                        dsmem_addr(bar_local, (uint32_t)owner));
+                    bulk_commit_group();
+                }
+            }
+            if (probe) ckw = clock64();
+            mbar_wait(xchg, 0);                                // all S slices of this CTA's columns have landed
+            if (threadIdx.x == 64) trace_max(p.trace, 4);
         }
     }
-    tc_fence_before();
-    __syncthreads();
-    cluster_sync_all();                                        // every partial of the cluster is in place
+    if (probe) ck0 = clock64();
 
     if (warp >= 2) {
-        const int r = (warp & 3) * 32 + lane, arow = m0 + r;
+        const int arow = m0 + r;
         const bool ok = arow < p.a_rows;
         const float bias = (ok && p.bias) ? p.bias[arow] : 0.0f;   // plain load: ld.global.nc may be hoisted above the null test
-        const int cols_per = (BN + S - 1) / S;
-        const int j0 = z * cols_per, j1 = min(BN, j0 + cols_per);
-        const uint32_t local = smem_u32(partial);
-        uint32_t peer[kMaxSplits];
+        // sums of kCG owned columns at a time; slices added in ascending rank order: deterministic.
+        // A single-CTA cluster has nothing to add: its columns come straight from TMEM.
+        constexpr int kCG = 8;
+        auto column_sums = [&](int jg, float (&acc)[kCG]) {
+            if (S == 1) {
+                uint32_t t[8];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                             : "=r"(t[0]), "=r"(t[1]), "=r"(t[2]), "=r"(t[3]), "=r"(t[4]), "=r"(t[5]), "=r"(t[6]), "=r"(t[7])
+                             : "r"(taddr + jg) : "memory");
+                tmem_ld_wait();
 #pragma unroll
-        for (int src = 0; src < kMaxSplits; ++src) peer[src] = dsmem_addr(local, (uint32_t)(src < S ? src : 0));
-        auto column_sum = [&](int j) -> float {
-            float part[kMaxSplits];
+                for (int c = 0; c < kCG; ++c) acc[c] = __uint_as_float(t[c]);
+                return;
+            }
 #pragma unroll
-            for (int src = 0; src < kMaxSplits; ++src)         // all remote loads in flight together
-                part[src] = src < S ? dsmem_ld_f32(peer[src] + (uint32_t)((j * BM + r) * 4)) : 0.f;
-            float v = 0.f;
+            for (int c = 0; c < kCG; ++c) acc[c] = 0.f;
+            // (columns past j1 read slots nobody wrote; their sums are discarded by the callers' predicates)
+            const float *src = recv + (jg - j0) * BM + r;
+#pragma unroll 4
+            for (int s = 0; s < S; ++s, src += cols_per * BM) {
 #pragma unroll
-            for (int src = 0; src < kMaxSplits; ++src) v += part[src];   // fixed order: deterministic sum
-            return v;
+                for (int c = 0; c < kCG; ++c) acc[c] += src[c * BM];
+            }
         };
         if (EPI == EPI_RESID && p.tp_peer_recv) {
             // ---- fused tensor-parallel all-reduce (2 ranks) over peer memory ----
             const uint32_t slot = (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z;
             const uint32_t epoch = p.tp_epoch[slot] + 1;       // same count on both ranks: they run the same launches
-            const size_t buf = (size_t)(epoch & 1) * (size_t)p.tp_rows * p.ldo;
-            for (int j = j0; j < j1; ++j) {
-                if (n0 + j >= p.b_rows) break;
-                const float v = column_sum(j);
-                if (ok) p.tp_peer_recv[buf + (size_t)(n0 + j) * p.ldo + arow] = v;      // NVLink store
+            const size_t buf = (size_t)(p.tp_seq & 1) * (size_t)p.tp_rows * p.ldo;   // receive half-buffer of this launch
+            for (int jg = j0; jg < j1; jg += kCG) {
+                float v[kCG];
+                column_sums(jg, v);
+#pragma unroll
+                for (int c = 0; c < kCG; ++c)
+                    if (ok && jg + c < j1) p.tp_peer_recv[buf + (size_t)(n0 + jg + c) * p.ldo + arow] = v[c];      // NVLink store
             }
             __threadfence_system();
             asm volatile("bar.sync 1, 128;" ::: "memory");
             if (threadIdx.x == 64) {
                 asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.tp_peer_flag + slot), "r"(epoch) : "memory");
                 uint32_t seen;
+                long long polls = 0;
                 do {
                     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.tp_flag + slot) : "memory");
+                    // the peer runs the same launch: if its flag does not arrive within seconds the ranks have lost step
+                    // (or the peer died); trap instead of hanging both GPUs
+                    if (++polls > (1ll << 24)) { printf("kx_gemm: peer rank did not publish its partial sums (slot %u)\n", slot); __trap(); }
                 } while ((int32_t)(seen - epoch) < 0);
                 p.tp_epoch[slot] = epoch;
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            for (int j = j0; j < j1; ++j) {
-                if (n0 + j >= p.b_rows) break;
-                const float v = column_sum(j);                 // this rank's partial again (still in shared memory)
-                if (ok) {
-                    const float other = __ldcv(p.tp_recv + buf + (size_t)(n0 + j) * p.ldo + arow);   // the peer's partial
-                    reinterpret_cast<float *>(p.out)[(size_t)(n0 + j) * p.ldo + arow] += v + other;
+            for (int jg = j0; jg < j1; jg += kCG) {
+                float v[kCG];
+                column_sums(jg, v);                            // this rank's partial again (still in shared memory / TMEM)
+#pragma unroll
+                for (int c = 0; c < kCG; ++c) {
+                    if (ok && jg + c < j1) {
+                        const float other = __ldcv(p.tp_recv + buf + (size_t)(n0 + jg + c) * p.ldo + arow);   // the peer's partial
+                        reinterpret_cast<float *>(p.out)[(size_t)(n0 + jg + c) * p.ldo + arow] += v[c] + other;
+                    }
+                }
+            }
+        } else if (EPI == EPI_RESID_NORM) {
+            // residual update + preparation of the next RMSNorm (deferred: see kx_gemm.cuh)
+            const float g = ok ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(p.norm_g)[arow]) : 0.f;
+            for (int jg = j0; jg < j1; jg += kCG) {
+                float x[kCG];
+                if (jg == j0) {
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c) x[c] = xres[c];   // requested before the exchange
+                } else {
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c) {
+                        x[c] = 0.f;
+                        if (ok && jg + c < j1) x[c] = reinterpret_cast<float *>(p.out)[(size_t)(n0 + jg + c) * p.ldo + arow];
+                    }
+                }
+                float v[kCG];
+                column_sums(jg, v);
+                if (probe && jg == j0) ck1 = clock64();
+                float sq[kCG];
+#pragma unroll
+                for (int c = 0; c < kCG; ++c) {
+                    x[c] += v[c];
+                    sq[c] = ok ? __fmul_rn(x[c], x[c]) : 0.f;
+                }
+#pragma unroll
+                for (int c = 0; c < kCG; ++c) {
+                    if (ok && jg + c < j1) {
+                        reinterpret_cast<float *>(p.out)[(size_t)(n0 + jg + c) * p.ldo + arow] = x[c];
+                        reinterpret_cast<__nv_bfloat16 *>(p.norm_out)[(size_t)(n0 + jg + c) * p.ldo + arow] = __float2bfloat16(__fmul_rn(x[c], g));
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)               // the kCG columns' butterflies side by side
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c) sq[c] += __shfl_xor_sync(0xffffffffu, sq[c], o);
+                if (lane == 0) {
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c)
+                        if (jg + c < j1) sq_s[q * BN + jg + c] = sq[c];
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            for (int j = j0 + (int)threadIdx.x - 64; j < j1; j += 128)     // the four warps' sums, fixed order
+                p.ssq_out[(size_t)blockIdx.y * p.ssq_ld + n0 + j] = (sq_s[j] + sq_s[BN + j]) + (sq_s[2 * BN + j] + sq_s[3 * BN + j]);
+        } else if (EPI == EPI_SWIGLU && S > 1) {
+            // The slices are in shared memory, so a thread need not keep to "its" TMEM lane: thread t takes the
+            // (gate, up) pair t % 64 of the tile (two adjacent floats: one 8-byte load per slice) for every second
+            // owned column -- no shuffle, no lane computing a SiLU that is thrown away, 128-byte stores per column.
+            const int pr = (int)threadIdx.x & 63, half = ((int)threadIdx.x - 64) >> 6;
+            const bool pok = m0 + 2 * pr < p.a_rows;
+            __nv_bfloat16 *orow = reinterpret_cast<__nv_bfloat16 *>(p.out) + ((m0 >> 1) + pr);
+            for (int jg = j0 + half; jg < j1; jg += 2 * kCG) {
+                float2 acc[kCG];
+#pragma unroll
+                for (int c = 0; c < kCG; ++c) acc[c] = make_float2(0.f, 0.f);
+                const float *src = recv + (jg - j0) * BM + 2 * pr;
+#pragma unroll 2
+                for (int s = 0; s < S; ++s, src += cols_per * BM) {
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c) {
+                        const float2 t = *reinterpret_cast<const float2 *>(src + 2 * c * BM);
+                        acc[c].x += t.x; acc[c].y += t.y;
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < kCG; ++c) {
+                    const int j = jg + 2 * c;
+                    const float sc = p.ssq_in ? rinv_s[min(j, BN - 1)] : 1.0f;
+                    const float gte = __fmul_rn(acc[c].x, sc), up = __fmul_rn(acc[c].y, sc);
+                    if (pok && j < j1) orow[(size_t)(n0 + j) * p.ldo] = __float2bfloat16(silu(gte) * up);
                 }
             }
         } else {
-            for (int j = j0; j < j1; ++j) {
-                if (n0 + j >= p.b_rows) break;                 // warp-uniform
-                epilogue_swap_elem<EPI>(p, column_sum(j), arow, n0 + j, ok, bias);
+            for (int jg = j0; jg < j1; jg += kCG) {
+                float v[kCG];
+                column_sums(jg, v);
+#pragma unroll
+                for (int c = 0; c < kCG; ++c)                  // (no early exit: the columns' dependency chains interleave)
+                    epilogue_swap_elem<EPI>(p, p.ssq_in ? __fmul_rn(v[c], rinv_s[min(jg + c, BN - 1)]) : v[c], arow, n0 + jg + c,
+                                            ok && jg + c < j1, bias);
             }
         }
     }
-    cluster_sync_all();                                        // peers may still be reading this CTA's partial
+    if (probe) {       // cycles: [5] = barrier | push loop, [6] = wait for the slices | first column sums, [7] = whole epilogue
+        p.trace[5] = ((unsigned long long)(ckp - ckb) << 32) | (unsigned long long)(unsigned)(ckw - ckp);
+        p.trace[6] = ((unsigned long long)(ck0 - ckw) << 32) | (unsigned long long)(unsigned)(ck1 - ck0);
+        p.trace[7] = (unsigned long long)(clock64() - ck0);
+    }
+    if (S > 1 && warp == 2) bulk_wait_group_read0();           // the copy engine has read this CTA's staging buffers
+    tc_fence_before();
+    __syncthreads();
     if (warp == 1) tmem_dealloc(tmem, C::TMEM_COLS);
     if (threadIdx.x == 0) trace_max(p.trace, 3);
 }
@@ -851,6 +1045,14 @@ int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
+    if (p.tp_peer_recv) {
+        // every CTA spins on a flag the SAME tile's CTA on the peer GPU publishes: that only terminates if all clusters
+        // of the grid are resident at once on both GPUs
+        int max_clusters = 0;
+        KX_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
+        KX_REQUIRE((int)(grid.x * grid.y) <= max_clusters, KX_EINVAL,
+                   "kx_gemm: fused all-reduce needs all %u clusters of %u CTAs co-resident, the GPU holds %d", grid.x * grid.y, grid.z, max_clusters);
+    }
     KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     count_launch();
     return KX_OK;
@@ -863,6 +1065,7 @@ int launch_ksplit_epi(const CUtensorMap &ta, const CUtensorMap &tb, const GemmPa
         case EPI_RESID: return launch_ksplit<BN, EPI_RESID>(ta, tb, p, grid, st);
         case EPI_SWIGLU: return launch_ksplit<BN, EPI_SWIGLU>(ta, tb, p, grid, st);
         case EPI_F32: return launch_ksplit<BN, EPI_F32>(ta, tb, p, grid, st);
+        case EPI_RESID_NORM: return launch_ksplit<BN, EPI_RESID_NORM>(ta, tb, p, grid, st);
     }
     set_error("kx_gemm: unknown epilogue %d", p.epilogue);
     return KX_EINVAL;
@@ -984,7 +1187,7 @@ int gemm_pick_bn(int swap, int64_t b_rows) {
 }
 
 size_t gemm_scratch_bytes(const GemmParams &p, int bn) {
-    if (p.splits <= 1 || p.epilogue == EPI_RESID || p.swap) return 0;   // swap-AB splits reduce over DSMEM
+    if (p.splits <= 1 || p.epilogue == EPI_RESID || p.epilogue == EPI_RESID_NORM || p.swap) return 0;   // swap-AB splits reduce over DSMEM
     const size_t tiles = (size_t)((p.a_rows + BM - 1) / BM) * (size_t)((p.b_rows + bn - 1) / bn);
     return tiles * (size_t)(BM * bn) * sizeof(float) + tiles * sizeof(uint32_t);
 }
@@ -996,7 +1199,9 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;      // no empty slice
     p.splits = splits;
-    if (p.swap && (splits > 1 || p.tp_peer_recv)) {
+    KX_REQUIRE(p.epilogue != EPI_RESID_NORM || (p.swap && p.norm_g && p.norm_out && p.ssq_out && !p.tp_peer_recv), KX_EINVAL,
+               "kx_gemm: EPI_RESID_NORM needs the swap-AB kernel and its norm arguments");
+    if (p.swap && (splits > 1 || p.tp_peer_recv || p.ssq_in || p.epilogue == EPI_RESID_NORM || p.pf_ptr)) {
         // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory
         if (splits > kMaxSplits) splits = kMaxSplits;
         p.kb_per_split = (total_kb + splits - 1) / splits;

@@ -10,7 +10,15 @@ namespace kx {
 // (max logit, lowest feature index attaining it) pair per token and part: out = int2 [parts][ldo] with the
 // value's bits in .x.  Token-major pair kernel: parts = feature tiles.  Swap-AB kernel: parts = 4 per 128-feature
 // tile (one per epilogue warp).  op_argmax_parts finishes the reduction.
-enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3, EPI_QKV_ROPE = 4, EPI_ARGMAX = 5 };
+//
+// Deferred RMSNorm (decode, swap-AB cluster kernel): the row-parallel projections (wo, wd) own whole residual
+// elements after their split-K reduction, so their epilogue (EPI_RESID_NORM) also prepares the NEXT norm:
+// it writes bf16(resid * g) -- the next GEMM's input, not yet divided by the row's rms -- and, per 128-feature
+// tile and batch column, the sum of squares of the updated residual (ssq_out[tile][column]).  The consuming GEMM
+// (ssq_in set) adds the tiles' sums in a fixed order and multiplies its accumulator columns by
+// 1 / sqrt(sum / hidden + eps) before bias / SwiGLU: W (x g / rms) == (W (x g)) / rms.  No RMSNorm launch.
+enum GemmEpilogue { EPI_BF16 = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_F32 = 3, EPI_QKV_ROPE = 4, EPI_ARGMAX = 5,
+                    EPI_RESID_NORM = 6 };
 
 struct GemmParams {
     int a_rows, b_rows, k;   // D[a_rows, b_rows] = A[a_rows, k] * B[b_rows, k]^T
@@ -34,14 +42,27 @@ struct GemmParams {
     // Tensor-parallel residual epilogue fused with the all-reduce (decode, 2 ranks, swap-AB cluster kernel):
     // each CTA pushes its slice of this rank's partial sum straight into the PEER GPU's receive buffer over
     // NVLink, publishes an epoch flag there, waits for the peer CTA of the same tile to do the same here, and
-    // adds both partials to the residual.  Buffers are double-buffered by epoch parity.
+    // adds both partials to the residual.  The receive buffer has two halves used by alternate launches: a rank can only
+    // reach launch n + 1 after the peer published launch n, i.e. after the peer finished reading launch n - 1's half.
     float *tp_peer_recv;     // peer GPU:  float [2][tp_rows * ldo]   (written by this rank)
     uint32_t *tp_peer_flag;  // peer GPU:  uint32 [tiles]             (epoch published by this rank)
     const float *tp_recv;    // this GPU:  the same two arrays, written by the peer
     const uint32_t *tp_flag;
     uint32_t *tp_epoch;      // this GPU:  uint32 [tiles], launches seen so far per tile slot
     int tp_rows;             // rows of one receive buffer (max decode batch)
+    int tp_seq;              // sequence number of this fused launch (same on both ranks); its parity picks the receive half-buffer
     unsigned long long *trace;   // diagnostic timeline slot (kx_common.cuh) or NULL
+    // deferred RMSNorm (see above)
+    const void *norm_g;      // EPI_RESID_NORM: bf16 gain of the next norm [features]
+    void *norm_out;          // EPI_RESID_NORM: bf16 [batch][ldo] = bf16(resid * g)
+    float *ssq_out;          // EPI_RESID_NORM: fp32 [features / 128][ssq_ld]
+    const float *ssq_in;     // consumer: fp32 [ssq_tiles][ssq_ld] (NULL: input is already normalised)
+    int ssq_ld, ssq_tiles;
+    float norm_eps, norm_inv_n;   // eps and 1 / hidden of the norm being applied
+    const float *col_scale;  // single-CTA swap-AB kernel, EPI_F32: logits column b is multiplied by col_scale[b] (or NULL)
+    // L2 prefetch of the weights a later kernel will stream (issued at kernel start, spread over the CTAs)
+    const void *pf_ptr;
+    size_t pf_bytes;
 };
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);

@@ -619,6 +619,128 @@ attn_decode_warp_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_
     if (lane == 0) trace_max(trace, 3);
 }
 
+// ---- decode attention, WPP (2 or 4) warps per (sequence, kv head) --------------------------------------
+// Medium batches (a few hundred pairs): one warp per pair leaves most SMs with four resident warps, each walking its
+// pair's key blocks one after the other (9 dependent softmax steps at 272 keys: 12 us per layer at batch 64).  Here
+// the WPP warps of a pair take 1 / WPP of its key blocks each -- same private cp.async rings, same prefetch before
+// griddepcontrol.wait -- and their (max, sum, O) partials are merged through shared memory.  A CTA of four warps
+// holds 4 / WPP pairs; WPP is chosen so that the grid is one resident wave.
+template <int HD, int G, int KB, int NS, int WPP>
+__global__ void __launch_bounds__(128)
+attn_decode_split_kernel(const __nv_bfloat16 *__restrict__ qkv, int qkv_ld, __nv_bfloat16 *__restrict__ out, int out_ld,
+                         __nv_bfloat16 *__restrict__ pages, const int *__restrict__ block_table, int max_pages,
+                         const int *__restrict__ pos, const float2 *__restrict__ rope, int n_q, int n_kv, float scale_log2,
+                         int key0, const float *__restrict__ part_o, const float *__restrict__ part_ml, int n_part, int n_tasks,
+                         unsigned long long *trace) {
+    extern __shared__ __align__(128) uint8_t smem_dw[];
+    asm volatile("griddepcontrol.launch_dependents;");
+    if (threadIdx.x == 0) trace_min(trace, 0);
+    using W = WarpAttnSmem<HD, KB, NS>;
+    constexpr int CH = HD / 8, HALF = HD / 2, PP = 4 / WPP;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+    const int pl = warp / WPP, sub = warp - pl * WPP;                       // pair inside the CTA, slice of its keys
+    const int task = blockIdx.x * PP + pl;
+    const bool live = task < n_tasks;
+    const int b = live ? task / n_kv : 0, kvh = live ? task - b * n_kv : 0;
+    uint8_t *Qs = smem_dw + warp * W::BYTES;
+    const uint32_t ring_u = (uint32_t)__cvta_generic_to_shared(Qs) + W::QT;
+    __nv_bfloat16 *knew = reinterpret_cast<__nv_bfloat16 *>(Qs + W::QT + NS * 2 * W::ST), *vnew = knew + HD;
+    float *comb_m = reinterpret_cast<float *>(smem_dw + 4 * W::BYTES);     // [4 warps][16] max, [4][16] sum, [4][G][HD] O
+    float *comb_l = comb_m + 4 * 16, *comb_o = comb_l + 4 * 16;
+    const int p = pos[b], T = p + 1;
+    const int *bt = block_table + (size_t)b * max_pages;
+    const int nblk_all = live ? (T - key0 + KB - 1) / KB : 0;
+    const int blk0 = sub * nblk_all / WPP, blk1 = (sub + 1) * nblk_all / WPP;   // this warp's blocks
+    const int k0 = key0 + blk0 * KB, Tw = min(T, key0 + blk1 * KB), nblk = blk1 - blk0;
+    const bool owner = sub == WPP - 1;                                      // its last block holds the new token
+#pragma unroll
+    for (int i = 0; i < NS - 1; ++i) {                // prologue: NS-1 stages in flight (empty groups keep the count uniform)
+        if (i < nblk) warp_attn_fetch<HD, KB, NS>(ring_u, i, k0, Tw, p, pages, bt, n_kv, kvh, lane);
+        cp_async_commit();
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // qkv comes from the predecessor
+    if (threadIdx.x == 0) trace_min(trace, 1);
+    float o[HD / 8][4], mrow[2], lrow[2];
+    if (live) {
+        // RoPE: q heads -> this warp's Q tile; the owner warp also rotates k and appends k, v
+        const __nv_bfloat16 *row = qkv + (size_t)b * qkv_ld;
+        const float2 *cs = rope + (size_t)p * HALF;
+        __nv_bfloat16 *kdst = pages + (((size_t)bt[p / kPage] * 2) * n_kv + kvh) * kPage * HD + (size_t)(p % kPage) * HD;
+        __nv_bfloat16 *vdst = kdst + (size_t)n_kv * kPage * HD;
+        for (int i = lane; i < (G + (owner ? 1 : 0)) * (HALF / 8); i += 32) {
+            const int h = i / (HALF / 8), c = i - h * (HALF / 8);
+            const __nv_bfloat16 *src = h < G ? row + (size_t)(kvh * G + h) * HD : row + (size_t)(n_q + kvh) * HD;
+            uint4 lo, hi;
+            rope8(src, HALF, cs, c, lo, hi);
+            if (h < G) {
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c)) = lo;
+                *reinterpret_cast<uint4 *>(Qs + swz<HD>(h, c + HALF / 8)) = hi;
+            } else {
+                reinterpret_cast<uint4 *>(kdst)[c] = lo; reinterpret_cast<uint4 *>(kdst)[c + HALF / 8] = hi;
+                reinterpret_cast<uint4 *>(knew)[c] = lo; reinterpret_cast<uint4 *>(knew)[c + HALF / 8] = hi;
+            }
+        }
+        if (owner) {
+            const __nv_bfloat16 *vsrc = row + (size_t)(n_q + n_kv + kvh) * HD;
+            for (int i = lane; i < CH; i += 32) {
+                const uint4 x = reinterpret_cast<const uint4 *>(vsrc)[i];
+                reinterpret_cast<uint4 *>(vdst)[i] = x; reinterpret_cast<uint4 *>(vnew)[i] = x;
+            }
+        }
+        for (int i = lane; i < (16 - G) * CH; i += 32)
+            *reinterpret_cast<uint4 *>(Qs + swz<HD>(G + i / CH, i % CH)) = make_uint4(0, 0, 0, 0);
+        __syncwarp();
+        warp_attn_loop<HD, G, KB, NS>(Qs, nblk, k0, Tw, p, pages, bt, n_kv, kvh, lane, scale_log2, o, mrow, lrow, owner);
+        const int g = lane >> 2, tq = lane & 3;
+        if (tq == 0) {
+            comb_m[warp * 16 + g] = mrow[0]; comb_m[warp * 16 + g + 8] = mrow[1];
+            comb_l[warp * 16 + g] = lrow[0]; comb_l[warp * 16 + g + 8] = lrow[1];
+        }
+        if (g < G) {
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) {
+                comb_o[(warp * G + g) * HD + j * 8 + 2 * tq] = o[j][0];
+                comb_o[(warp * G + g) * HD + j * 8 + 2 * tq + 1] = o[j][1];
+            }
+        }
+        if (G > 8 && g + 8 < G) {
+#pragma unroll
+            for (int j = 0; j < HD / 8; ++j) {
+                comb_o[(warp * G + g + 8) * HD + j * 8 + 2 * tq] = o[j][2];
+                comb_o[(warp * G + g + 8) * HD + j * 8 + 2 * tq + 1] = o[j][3];
+            }
+        }
+    }
+    __syncthreads();
+    if (live) {
+        const size_t part_rows = (size_t)(n_tasks / n_kv) * n_q;            // rows of one prefix partial: (sequence, q head)
+        const int w0 = pl * WPP;
+        for (int i = sub * 32 + lane; i < G * HD; i += WPP * 32) {
+            const int h = i / HD, d = i - h * HD;
+            const size_t prow = (size_t)b * n_q + kvh * G + h;
+            float M = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < WPP; ++w) M = fmaxf(M, comb_m[(w0 + w) * 16 + h]);
+            for (int c = 0; c < n_part; ++c) M = fmaxf(M, part_ml[(c * part_rows + prow) * 2]);
+            float num = 0.f, den = 0.f;
+#pragma unroll
+            for (int w = 0; w < WPP; ++w) {
+                const float f = exp2f((comb_m[(w0 + w) * 16 + h] - M) * scale_log2);   // 0 for a warp that saw no keys
+                num += f * comb_o[((w0 + w) * G + h) * HD + d];
+                den += f * comb_l[(w0 + w) * 16 + h];
+            }
+            for (int c = 0; c < n_part; ++c) {
+                const float2 ml = *reinterpret_cast<const float2 *>(part_ml + (c * part_rows + prow) * 2);
+                const float f = exp2f((ml.x - M) * scale_log2);
+                num += f * part_o[(c * part_rows + prow) * HD + d];
+                den += f * ml.y;
+            }
+            out[(size_t)b * out_ld + (size_t)(kvh * G + h) * HD + d] = __float2bfloat16(num / den);
+        }
+    }
+    if (tid == 0) trace_max(trace, 3);
+}
+
 // ---- decode attention over a prefix shared by the whole batch ("read the prefix once") ----
 // Every sequence's first P keys are the same cached pages (kx_engine_set_prefix), so for one kv head the
 // B x G query rows of the step attend to them as one tall tile problem: grid (n_kv, ceil(B G / 64), chunks),
@@ -883,6 +1005,48 @@ __global__ void pick_kernel(const int2 *__restrict__ gathered, int tp, int B, in
     out[b] = bi;
 }
 
+// ---- end of a decode step on the deferred-RMSNorm path (kx_gemm.cuh) ---------------------------------
+// One CTA per sequence: records the token the step chose (store != 0), moves the sequence to its next position and
+// gathers that token's embedding row as the next step's input -- the fp32 residual, bf16(residual * g) for the first
+// QKV projection and, per 128-feature tile, the sum of squares the projection turns into 1 / rms.  Replaces the
+// store-token, advance, embedding and first RMSNorm launches.
+__global__ void __launch_bounds__(128)
+decode_tail_kernel(const int *__restrict__ next_tok, int *__restrict__ out_ids, int n_new, int base_pos, int *__restrict__ pos,
+                   const __nv_bfloat16 *__restrict__ table, const __nv_bfloat16 *__restrict__ g, float *__restrict__ resid,
+                   __nv_bfloat16 *__restrict__ xg, float *__restrict__ ssq, int ssq_ld, int H, int store) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int tok = next_tok[b];
+    if (tid == 0) {
+        const int p = pos[b];
+        if (store) out_ids[(size_t)b * n_new + (p - base_pos)] = tok;
+        pos[b] = p + 1;
+    }
+    const __nv_bfloat16 *row = table + (size_t)tok * H;
+    __shared__ float ws[4];
+    for (int f0 = 0; f0 < H; f0 += 128) {
+        const float v = __bfloat162float(row[f0 + tid]);
+        resid[(size_t)b * H + f0 + tid] = v;
+        xg[(size_t)b * H + f0 + tid] = __float2bfloat16(__fmul_rn(v, __bfloat162float(g[f0 + tid])));
+        const float sq = warp_sum(__fmul_rn(v, v));
+        if ((tid & 31) == 0) ws[tid >> 5] = sq;
+        __syncthreads();
+        if (tid == 0) ssq[(size_t)(f0 >> 7) * ssq_ld + b] = (ws[0] + ws[1]) + (ws[2] + ws[3]);
+        __syncthreads();
+    }
+}
+
+// 1 / rms per batch column from the per-tile sums of squares (only the logits path needs it as an array: the
+// projections compute it themselves)
+__global__ void col_rinv_kernel(const float *__restrict__ ssq, int tiles, int ld, int B, float inv_n, float eps, float *__restrict__ out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    float ss = 0.f;
+    for (int t = 0; t < tiles; ++t) ss += ssq[(size_t)t * ld + b];
+    out[b] = 1.0f / sqrtf(ss * inv_n + eps);
+}
+
 // L2 prefetch of a byte range as a kernel of its own (microbenchmarks; the decode kernels issue their own)
 __global__ void l2_prefetch_kernel(const char *p, size_t bytes) {
     if (threadIdx.x == 0) sm100::l2_prefetch_share(p, bytes, blockIdx.x, gridDim.x);
@@ -917,6 +1081,33 @@ int launch_decode_warp(int G, int n_tasks, cudaStream_t st, const __nv_bfloat16 
             return KX_EINVAL;
     }
 #undef KX_DECW
+    return KX_OK;
+}
+
+template <int HD, int WPP>
+int launch_decode_split(int G, int n_tasks, cudaStream_t st, const __nv_bfloat16 *qkv, int qkv_ld, __nv_bfloat16 *out, int out_ld,
+                        __nv_bfloat16 *pages, const int *bt, int max_pages, const int *pos, const float2 *rope, int n_q, int n_kv,
+                        float scale, int key0, const float *part_o, const float *part_ml, int n_part) {
+    constexpr int KB = HD == 64 ? 32 : 16, NS = 3, PP = 4 / WPP;
+    const size_t smem = (size_t)4 * (16 * HD * 2 + NS * 2 * KB * HD * 2 + 2 * HD * 2) + sizeof(float) * (2 * 4 * 16 + (size_t)4 * G * HD);
+    const dim3 grid((n_tasks + PP - 1) / PP);
+#define KX_DECS(GV)                                                                                          \
+    case GV: {                                                                                               \
+        auto k = attn_decode_split_kernel<HD, GV, KB, NS, WPP>;                                              \
+        static size_t granted[64];     /* per device; raised outside any capture by the first, eager call */   \
+        size_t &have = granted[PerDeviceOnce::device()];                                                     \
+        if (smem > 48 * 1024 && smem > have) { KX_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); have = smem; } \
+        KX_CUDA(launch_pdl(k, grid, dim3(128), smem, st, qkv, qkv_ld, out, out_ld, pages, bt, max_pages, pos, rope, n_q, n_kv, scale, \
+                           key0, part_o, part_ml, n_part, n_tasks, trace_slot("attn.split")));               \
+        break;                                                                                               \
+    }
+    switch (G) {
+        KX_DECS(1) KX_DECS(2) KX_DECS(4) KX_DECS(7) KX_DECS(8)
+        default:
+            set_error("attention: unsupported GQA group size %d", G);
+            return KX_EINVAL;
+    }
+#undef KX_DECS
     return KX_OK;
 }
 
@@ -1006,6 +1197,21 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     dim3 grid(n_kv, B);
     int rc;
     const int n_tasks = n_kv * B;
+    if ((hd == 64 || hd == 128) && n_tasks >= 96 && n_tasks <= 592 && max_T - key0 > 128 && G <= 8) {
+        // a few hundred pairs with long key lists: 2 or 4 warps share a pair, the grid is one wave of 2 CTAs per SM
+        const __nv_bfloat16 *q = (const __nv_bfloat16 *)qkv;
+        __nv_bfloat16 *o = (__nv_bfloat16 *)out, *pg = (__nv_bfloat16 *)pages;
+        const float2 *rp = (const float2 *)rope;
+        if (n_tasks <= 296)
+            rc = hd == 64 ? launch_decode_split<64, 4>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part)
+                          : launch_decode_split<128, 4>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part);
+        else
+            rc = hd == 64 ? launch_decode_split<64, 2>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part)
+                          : launch_decode_split<128, 2>(G, n_tasks, st, q, qkv_ld, o, out_ld, pg, block_table, max_pages, pos, rp, n_q, n_kv, scale, key0, part_o, part_ml, n_part);
+        if (rc != KX_OK) return rc;
+        count_launch();
+        return KX_OK;
+    }
     if ((hd == 64 || hd == 128) && (n_tasks >= 512 || max_T - key0 <= 128)) {
         // many (sequence, kv head) pairs, or few keys each: one warp per pair, no CTA-level split of the keys
         const bool deep = (n_tasks + 3) / 4 <= 148;            // one CTA per SM anyway: spend the shared memory on a deeper ring
@@ -1134,6 +1340,22 @@ int op_argmax_pairs(const float *logits, int B, int V, int ld, int id_offset, vo
 
 int op_pick(const void *gathered, int tp, int B, int *out, cudaStream_t st) {
     pick_kernel<<<(B + 127) / 128, 128, 0, st>>>((const int2 *)gathered, tp, B, out);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, int *pos, const void *table, const void *g,
+                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, cudaStream_t st) {
+    KX_REQUIRE(H % 128 == 0, KX_EINVAL, "decode tail: hidden must be a multiple of 128");
+    KX_CUDA(launch_pdl(decode_tail_kernel, dim3(B), dim3(128), 0, st, next_tok, out_ids, n_new, base_pos, pos,
+                       (const __nv_bfloat16 *)table, (const __nv_bfloat16 *)g, resid, (__nv_bfloat16 *)xg, ssq, ssq_ld, H, store));
+    count_launch();
+    return KX_OK;
+}
+
+int op_col_rinv(const float *ssq, int tiles, int ld, int B, int H, float eps, float *out, cudaStream_t st) {
+    col_rinv_kernel<<<(B + 127) / 128, 128, 0, st>>>(ssq, tiles, ld, B, 1.0f / (float)H, eps, out);
     count_launch();
     KX_CUDA(cudaGetLastError());
     return KX_OK;

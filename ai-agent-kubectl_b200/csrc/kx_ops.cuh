@@ -34,6 +34,10 @@ int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cu
 int op_argmax_parts(const void *parts, int n_parts, int ld, int B, int id_offset, int *out, int *out2, void *out_pairs,
                     cudaStream_t st);
 int op_advance(int *pos, int n, cudaStream_t st);
+// deferred-RMSNorm decode path: end-of-step bookkeeping + embedding of the chosen token as the next step's input
+int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, int *pos, const void *table, const void *g,
+                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, cudaStream_t st);
+int op_col_rinv(const float *ssq, int tiles, int ld, int B, int H, float eps, float *out, cudaStream_t st);
 // tensor-parallel helpers
 int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st);
 int op_argmax_pairs(const float *logits, int B, int V, int ld, int id_offset, void *pairs, cudaStream_t st);

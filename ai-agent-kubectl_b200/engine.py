@@ -189,13 +189,13 @@ class Generator:
         return int(_lib.lib().kx_engine_p2p_launches(self._h))
 
     def attn_tc_launches(self) -> int:
-        """Prefill attention launches that took the tcgen05 kernel (KX_ATTN_TC=1) so far."""
+        """Prefill attention launches that took the tcgen05 kernel so far."""
         return int(_lib.lib().kx_engine_attn_tc_launches(self._h))
 
     def trace(self, max_slots: int = 2048):
-        """Diagnostic (KX_TRACE=1): [(label, start, deps_ready, main_done, end)] in ns for every instrumented
-        launch of the last decode step, in launch order."""
-        buf = np.zeros((max_slots, 4), np.uint64)
+        """Diagnostic (KX_DEBUG=trace): [(label, start, deps_ready, main_done, end, exchanged, ...)] in ns for every
+        instrumented launch of the last decode step, in launch order."""
+        buf = np.zeros((max_slots, 8), np.uint64)
         n = _lib.lib().kx_engine_trace(self._h, buf.ctypes.data, max_slots)
         if n < 0:
             _lib.check(n)

@@ -246,8 +246,8 @@ int64_t kx_engine_p2p_launches(const kx_engine *e);   /* GEMMs enqueued with the
 int64_t kx_engine_attn_tc_launches(const kx_engine *e);
 /* Diagnostic: with KX_TRACE=1 in the environment at creation every instrumented kernel of a decode step records
  * globaltimer values into its slot: [0] earliest CTA start, [1] earliest return from griddepcontrol.wait,
- * [2] latest end of the main loop, [3] latest CTA end (ns).  Copies the slots of the LAST step (launch order) to
- * h_slots (4 x uint64 each) and returns how many; kx_engine_trace_name gives the launch's label. */
+ * [2] latest end of the main loop, [3] latest CTA end, [4] latest end of the split-K exchange (ns), [5..7] spare.
+ * Copies the slots of the LAST step (launch order) to h_slots (8 x uint64 each) and returns how many; kx_engine_trace_name gives the launch's label. */
 int kx_engine_trace(kx_engine *e, uint64_t *h_slots, int32_t max_slots);
 const char *kx_engine_trace_name(const kx_engine *e, int32_t i);
 

@@ -14,10 +14,15 @@ Two numeric modes:
     bound is stated against).
   * ``emulate_bf16=True``  -- same fp32 arithmetic, but activations are rounded to
     bf16 exactly where the CUDA path stores bf16 (GEMM inputs, q/k/v, KV cache,
-    attention output, SwiGLU output).  Greedy ids are compared against this mode:
-    with random weights top-1 margins are tiny, and only a reference with the same
-    quantisation points makes "ids equal" a statement about the kernels rather
-    than about rounding luck.  DESIGN.md lists the rounding points.
+    attention output, SwiGLU output).  The small-model tests compare greedy ids
+    against this mode: with iid random weights top-1 margins are tiny, and only a
+    reference with the same quantisation points makes "ids equal" a statement
+    about the kernels rather than about rounding luck.  DESIGN.md lists the
+    rounding points.  ``deferred_decode`` (default on): single-token steps of
+    fewer than 256 sequences round the GEMM input BEFORE the division by the rms,
+    bf16(x * g), and divide the GEMM's output, as the decode kernels do
+    (kx_gemm.cuh, deferred RMSNorm); tensor-parallel engines keep the plain order.
+  The full-architecture tests (tests/test_parity_full_gpu.py) use the fp32 mode.
 """
 from __future__ import annotations
 
@@ -45,8 +50,9 @@ class StreamedWeights:
 
 
 class RefModel:
-    def __init__(self, cfg, weights, rope: torch.Tensor, emulate_bf16: bool = False):
+    def __init__(self, cfg, weights, rope: torch.Tensor, emulate_bf16: bool = False, deferred_decode: bool = True):
         self.cfg, self.emu = cfg, emulate_bf16
+        self.deferred_decode = deferred_decode
         self.w = weights if isinstance(weights, StreamedWeights) else {k: v.to(torch.float32) for k, v in weights.items()}
         self.rope = rope  # [max_pos, hd/2, 2]
 
@@ -63,11 +69,18 @@ class RefModel:
         x1, x2 = x[..., :half], x[..., half:]
         return torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], dim=-1)
 
+    def _pre(self, x, g):
+        """Input of the projections behind a norm and the factor their outputs are multiplied by afterwards."""
+        B, S, _ = x.shape
+        if self.emu and self.deferred_decode and S == 1 and B < 256:
+            return _r(x * g, True), torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + self.cfg.eps)
+        return _r(self._norm(x, g), self.emu), 1.0
+
     def _layer(self, i, x, pos, cache, mask):
         c, w, emu = self.cfg, self.w, self.emu
         B, S, _ = x.shape
-        h = _r(self._norm(x, w[f"ln1.{i}"]), emu)
-        q, k, v = h @ w[f"wq.{i}"].T, h @ w[f"wk.{i}"].T, h @ w[f"wv.{i}"].T
+        h, f = self._pre(x, w[f"ln1.{i}"])
+        q, k, v = (h @ w[f"wq.{i}"].T) * f, (h @ w[f"wk.{i}"].T) * f, (h @ w[f"wv.{i}"].T) * f
         if c.qkv_bias:
             q, k, v = q + w[f"bq.{i}"], k + w[f"bk.{i}"], v + w[f"bv.{i}"]
         q, k, v = _r(q, emu), _r(k, emu), _r(v, emu)
@@ -88,8 +101,8 @@ class RefModel:
         p = torch.softmax(s, dim=-1)
         a = _r((p @ vv).permute(0, 2, 1, 3).reshape(B, S, c.q_dim), emu)
         x = x + a @ w[f"wo.{i}"].T
-        h = _r(self._norm(x, w[f"ln2.{i}"]), emu)
-        g, u = h @ w[f"wg.{i}"].T, h @ w[f"wu.{i}"].T
+        h, f = self._pre(x, w[f"ln2.{i}"])
+        g, u = (h @ w[f"wg.{i}"].T) * f, (h @ w[f"wu.{i}"].T) * f
         m = _r(torch.nn.functional.silu(g) * u, emu)
         return x + m @ w[f"wd.{i}"].T
 
@@ -110,9 +123,9 @@ class RefModel:
             x = x[:, -1:, :]
         elif last_n is not None:
             x = x[:, -last_n:, :]
-        h = _r(self._norm(x, self.w["norm"]), self.emu)
+        h, f = self._pre(x, self.w["norm"])
         head = self.w["embed"] if self.cfg.tied else self.w["lm_head"]
-        logits = h @ head.T
+        logits = (h @ head.T) * f
         return logits[:, 0] if last_only else logits
 
     @torch.no_grad()

@@ -1,5 +1,5 @@
 """Shared-prefix generation probe: python profiles/run_prefix.py ARCH BATCH PREFIX SUFFIX NEW [reps]
-(KX_SHARED_PREFIX=0 in the environment makes every sequence re-read the prefix K/V, for A/B timing)."""
+(KX_DEBUG=no-shared-prefix in the environment makes every sequence re-read the prefix K/V, for A/B timing)."""
 import os
 import sys
 import time
@@ -18,7 +18,7 @@ gen = engine.Generator(arch, seed=5, max_batch=B, max_seq=P + S + N)
 rng = np.random.default_rng(0)
 gen.set_prefix(rng.integers(0, 256, P).astype(np.int32))
 print(f"engine + prefix up in {time.time() - t0:.1f}s, device bytes {gen.device_bytes() / 1e9:.2f} GB, "
-      f"KX_SHARED_PREFIX={os.environ.get('KX_SHARED_PREFIX', '1')}")
+      f"KX_DEBUG={os.environ.get('KX_DEBUG', '')}")
 toks = rng.integers(0, 256, (B, S)).astype(np.int32)
 for r in range(reps):
     ids, _ = gen.generate_ids(toks, N)

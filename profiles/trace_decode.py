@@ -1,9 +1,9 @@
-"""In-graph timeline of one decode step (KX_TRACE=1: every instrumented kernel records globaltimer values).
+"""In-graph timeline of one decode step (KX_DEBUG=trace: every instrumented kernel records globaltimer values).
 usage: python profiles/trace_decode.py ARCH BATCH PROMPT_LEN NEW_TOKENS [layers to print]"""
 import os
 import sys
 
-os.environ["KX_TRACE"] = "1"
+os.environ["KX_DEBUG"] = ",".join(filter(None, [os.environ.get("KX_DEBUG", ""), "trace"]))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np  # noqa: E402
 import kubectl_b200  # noqa: E402,F401
@@ -20,15 +20,15 @@ st = gen.last_stats
 tr = gen.trace()
 t0 = min(r[1] for r in tr)
 print(f"{arch} B={B} S={S}: decode {st.decode_ms / st.decode_steps * 1e3:.1f} us/step, {len(tr)} traced launches in the last step")
-print(f"{'#':>4} {'kernel':<12} {'start':>8} {'deps':>8} {'main':>8} {'end':>8} | {'dur':>6} {'after-deps':>10} {'gap':>6}   (us)")
+print(f"{'#':>4} {'kernel':<12} {'start':>8} {'deps':>8} {'main':>8} {'xchg':>8} {'bar/push':>11} {'wait/sums':>11} {'epi':>6} {'end':>8} | {'dur':>6} {'after-deps':>10} {'gap':>6}   (us)")
 prev_end = t0
 per = {}
-for i, (name, a, b, c, d) in enumerate(tr):
+for i, (name, a, b, c, d, x4, x5, x6, x7) in enumerate(tr):
     dur, work = (d - a) / 1e3, (d - b) / 1e3
     k = per.setdefault(name, [0, 0.0, 0.0, 0.0])
     k[0] += 1; k[1] += dur; k[2] += work; k[3] += (d - max(prev_end, a)) / 1e3 if d > prev_end else 0.0
     if i < show * 8 + 2 or i >= len(tr) - 4:
-        print(f"{i:>4} {name:<12} {(a - t0) / 1e3:8.2f} {(b - t0) / 1e3:8.2f} {(c - t0) / 1e3 if c else 0:8.2f} {(d - t0) / 1e3:8.2f} | "
+        print(f"{i:>4} {name:<12} {(a - t0) / 1e3:8.2f} {(b - t0) / 1e3:8.2f} {(c - t0) / 1e3 if c else 0:8.2f} {(x4 - t0) / 1e3 if x4 else 0:8.2f} {x5 >> 32:5d}/{x5 & 0xffffffff:<5d} {x6 >> 32:5d}/{x6 & 0xffffffff:<5d} {x7:6d} {(d - t0) / 1e3:8.2f} | "
               f"{dur:6.2f} {work:10.2f} {(a - prev_end) / 1e3:6.2f}")
     prev_end = max(prev_end, d)
 print(f"span of traced launches: {(prev_end - t0) / 1e3:.1f} us")

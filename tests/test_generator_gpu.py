@@ -91,7 +91,6 @@ def test_small_batch_ragged_block_sizes(arch):
 def test_tcgen05_prefill_attention(B, S, monkeypatch):
     """Causal prefill attention as tcgen05 MMAs (S = Q K^T and O = P V in TMEM, V consumed MN-major from
     the paged layout); same parity bar as the mma.sync kernel, prompts that are not a multiple of the 128-row tile."""
-    monkeypatch.delenv("KX_ATTN_TC", raising=False)
     cfg, gen, ref_emu, _ = _setup("tiny-qwen2", 3, B, S, 6)
     toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(21))
     ids, logits = gen.generate_ids(toks.numpy().astype(np.int32), 6, want_logits=True)
@@ -151,13 +150,13 @@ def test_shared_prefix_decode_attention(arch, B, P, S, monkeypatch):
     """Decode over a prefix shared by the batch: the prefix K/V are reduced once per 64 query rows
     (several row tiles, several chunks, a last chunk that is not a whole 64-key tile) and merged with each
     sequence's own keys.  Against the oracle run on the full prompts the logits must be as close as those of
-    the engine that re-reads the prefix per sequence (KX_SHARED_PREFIX=0), and ids may differ from the
+    the engine that re-reads the prefix per sequence (KX_DEBUG=no-shared-prefix), and ids may differ from the
     oracle's only where its top-2 margin is inside that noise."""
     n_new = 5
     g = torch.Generator().manual_seed(11)
     results = {}
     for shared in ("0", "1"):
-        monkeypatch.setenv("KX_SHARED_PREFIX", shared)
+        monkeypatch.setenv("KX_DEBUG", "" if shared == "1" else "no-shared-prefix")
         cfg, gen, ref_emu, _ = _setup(arch, 3, B, P + S, n_new)
         if shared == "0":
             prefix = torch.randint(0, cfg.vocab, (P,), generator=g)

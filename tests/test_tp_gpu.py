@@ -58,7 +58,7 @@ def test_tp2_matches_the_oracle(tmp_path, arch):
     assert r[0]["fused"] > 0 and r[1]["fused"] == r[0]["fused"] and r[0]["nccl_only_fused"] == 0
     cfg = model_config.get_config(arch)
     w = weights.make_weights(cfg, 3)
-    ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True)
+    ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True, deferred_decode=False)
     toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(103))
     want_ids, want_logits = ref.generate(toks, n_new, return_logits=True)
     logits = torch.cat([r[0]["logits"], r[1]["logits"]], dim=-1)   # vocabulary shards side by side
