@@ -23,7 +23,6 @@ void release_scratch();
 //   no-attn-tc       prefill attention on the mma.sync kernel
 //   no-shared-prefix every sequence re-reads a cached prefix in decode attention
 //   no-fused-argmax  lm_head writes logits, a second kernel picks the token
-//   prefetch         decode GEMMs ask the L2 for the weights of a later launch (experiment: slower on B200)
 // Nothing in the product path depends on it being set.
 bool debug_flag(const char *name);
 

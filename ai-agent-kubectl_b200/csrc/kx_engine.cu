@@ -38,7 +38,6 @@ struct kx_engine {
     bool share_prefix = true;                      // decode attention reads a cached prefix once per 64 query rows
     bool fused_norm = true;                        // decode (batch < 256, no TP): RMSNorm deferred into the GEMM epilogues
     float *ssq = nullptr, *col_rinv = nullptr;     // ... per-tile sums of squares [hidden / 128][max_batch]; 1 / rms per column
-    bool prefetch = false;                         // KX_DEBUG=prefetch: kernels ask the L2 for a later launch's weights (measured: no gain)
     bool fused_argmax = true;                      // lm_head keeps (max, index) per tile instead of writing logits
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
@@ -151,8 +150,6 @@ struct GemmCall {
     bool ssq_in = false;                           // deferred RMSNorm: scale the accumulator columns by 1 / rms (from e->ssq)
     const void *norm_g = nullptr;                  // EPI_RESID_NORM: gain of the next norm
     const float *col_scale = nullptr;
-    const void *pf_ptr = nullptr;                  // weights of a later launch to pull into the L2
-    size_t pf_bytes = 0;
 };
 
 int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
@@ -164,7 +161,6 @@ int run_gemm(kx_engine *e, const GemmCall &c, cudaStream_t st) {
     if (c.ssq_in) p.ssq_in = e->ssq;
     if (c.epi == EPI_RESID_NORM) { p.norm_g = c.norm_g; p.norm_out = e->xn; p.ssq_out = e->ssq; }
     p.col_scale = c.col_scale;
-    if (e->prefetch) { p.pf_ptr = c.pf_ptr; p.pf_bytes = c.pf_bytes; }
     if (c.extra) {
         p.pos = c.extra->pos; p.seq = c.extra->seq; p.rope = c.extra->rope; p.kv_pages = c.extra->kv_pages;
         p.block_table = c.extra->block_table; p.max_pages = c.extra->max_pages;
@@ -240,7 +236,7 @@ int norm_rows(kx_engine *e, const void *g, int M, const int *row_map, cudaStream
 // parallelism every rank holds a partial sum: it goes to tp_buf, is all-reduced, then added.
 int linear_resid(kx_engine *e, const Linear &l, int M, cudaStream_t st, bool decode) {
     const kx_model_desc &d = e->d;
-    constexpr int splitk_min_m = 257;
+    constexpr int splitk_min_m = 256;
     if (d.tp_size <= 1 && decode && M >= splitk_min_m && M <= 512 && d.hidden % 256 == 0 && e->splitk_part) {
         // 2 x (hidden / 256) tiles of 256 x 256 would use a fraction of the SMs: cut k so that ~64 CTA pairs work,
         // slices land in splitk_part and the next RMSNorm adds them to the residual
@@ -334,28 +330,22 @@ bool fused_norm_decode(const kx_engine *e, int B) { return e->fused_norm && e->d
 // One layer of a decode step with the RMSNorms folded into the projections (kx_gemm.cuh): five launches --
 // QKV (scaled by 1 / rms), attention, wo (+ residual, prepares norm 2), gate/up (scaled, SwiGLU), down (+ residual,
 // prepares the next layer's norm 1 or the final norm).  e->xn holds bf16(residual * g) of the pending norm, e->ssq
-// its per-tile sums of squares.  Each GEMM also asks the L2 for the weights of the launch after next.
+// its per-tile sums of squares.
 int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
-    const int bn = gemm_pick_bn(1, B), bi = bn_index(bn);
+    // batch tiles of at most 64 columns: a 128-wide tile doubles the split-K exchange and the epilogue of every CTA
+    // (Llama-3.2-1B, batch 128: 1.9 ms per step with one 128-wide tile, 1.55 with two 64-wide ones)
+    const int bn = B <= 32 ? 32 : 64, bi = bn_index(bn);
     const int b_tiles = (B + bn - 1) / bn;
     const bool last = li + 1 == d.layers;
-    const size_t w_qkv = (size_t)e->qkv_dim * d.hidden * 2, w_o = (size_t)d.hidden * e->q_dim * 2,
-                 w_gu = (size_t)2 * d.inter * d.hidden * 2, w_d = (size_t)d.hidden * d.inter * 2;
     auto gemm = [&](const CUtensorMap *w, const CUtensorMap *x, int features, int k, int epi, void *out, int ldo, const float *bias,
-                    const char *label, bool ssq_in, const void *norm_g, const void *pf, size_t pf_bytes) {
+                    const char *label, bool ssq_in, const void *norm_g) {
         GemmCall c{w, x + bi, features, B, k, epi, 1, pick_splits(features, k, b_tiles), bn, out, ldo, bias};
-        c.label = label; c.ssq_in = ssq_in; c.norm_g = norm_g; c.pf_ptr = pf; c.pf_bytes = pf_bytes;
+        c.label = label; c.ssq_in = ssq_in; c.norm_g = norm_g;
         return run_gemm(e, c, st);
     };
-    // Prefetch plan.  QKV, attention and wo are latency bound (their weights sit in the stage rings before their
-    // inputs exist) and leave HBM idle; gate/up is the one projection that has to stream (67 MB for Llama-3.2-1B).
-    // So the QKV launch asks the L2 for the part of gate/up's weights the rings will not already hold, and gate/up
-    // does the same for the down projection.
-    const size_t gu_skip = (size_t)32 << 20 < w_gu ? (size_t)16 << 20 : w_gu;   // the first 16 MB arrive through the rings anyway
-    KX_TRY(gemm(&L.wqkv, e->xn_b, e->qkv_dim, d.hidden, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, "qkv", true, nullptr,
-                (const char *)L.w.wgu + gu_skip, w_gu - gu_skip));
+    KX_TRY(gemm(&L.wqkv, e->xn_b, e->qkv_dim, d.hidden, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, "qkv", true, nullptr));
     int key0 = 0, n_part = 0;
     if (e->share_prefix && e->prefix_len >= 64 && B >= 2 && e->prefix_o &&
         (size_t)attn_prefix_parts(B, d.n_q, d.n_kv, e->prefix_len, nullptr) * B * d.n_q <= e->prefix_rows) {
@@ -365,11 +355,10 @@ int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st)
     }
     KX_TRY(op_attn_decode(e->qkv, e->qkv_dim, e->attn, e->q_dim, L.kv_pages, e->block_table, e->max_pages, e->pos,
                           e->rope, B, max_T, d.n_q, d.n_kv, d.head_dim, key0, e->prefix_o, e->prefix_ml, n_part, st));
-    KX_TRY(gemm(&L.wo, e->attn_b, d.hidden, e->q_dim, EPI_RESID_NORM, e->resid, d.hidden, nullptr, "wo", false, L.w.ln2, nullptr, 0));
-    KX_TRY(gemm(&L.wgu, e->xn_b, 2 * d.inter, d.hidden, EPI_SWIGLU, e->mlp, d.inter, nullptr, "gate_up", true, nullptr, L.w.wd, w_d));
+    KX_TRY(gemm(&L.wo, e->attn_b, d.hidden, e->q_dim, EPI_RESID_NORM, e->resid, d.hidden, nullptr, "wo", false, L.w.ln2));
+    KX_TRY(gemm(&L.wgu, e->xn_b, 2 * d.inter, d.hidden, EPI_SWIGLU, e->mlp, d.inter, nullptr, "gate_up", true, nullptr));
     KX_TRY(gemm(&L.wd, e->mlp_b, d.hidden, d.inter, EPI_RESID_NORM, e->resid, d.hidden, nullptr, "down", false,
-                last ? e->norm : e->layers[li + 1].w.ln1, nullptr, 0));
-    (void)w_qkv; (void)w_o;
+                last ? e->norm : e->layers[li + 1].w.ln1));
     return KX_OK;
 }
 
@@ -453,7 +442,6 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     e->share_prefix = !debug_flag("no-shared-prefix");
     e->attn_tc = !debug_flag("no-attn-tc");
     e->fused_norm = !debug_flag("no-fused-norm");
-    e->prefetch = debug_flag("prefetch");
     e->fused_argmax = !debug_flag("no-fused-argmax");
     if (e->d.prefill_chunk <= 0) e->d.prefill_chunk = 32768;
     e->qkv_dim = (d.n_q + 2 * d.n_kv) * d.head_dim;
@@ -695,6 +683,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     // graph); it is ordered after whatever the caller already enqueued on `stream`.
     cudaStream_t st = e->stream;
     const int64_t launches0 = kx_launch_count();
+    int64_t h2d = 0, d2h = 0;                        // counted where the copies are issued
     cudaEvent_t ev0, ev1, ev2;
     KX_CUDA(cudaEventCreate(&ev0)); KX_CUDA(cudaEventCreate(&ev1)); KX_CUDA(cudaEventCreate(&ev2));
     KX_CUDA(cudaEventRecord(ev0, (cudaStream_t)stream));
@@ -717,6 +706,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens + (size_t)b0 * S, (size_t)M * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        h2d += (int64_t)3 * M * 4;
         KX_CUDA(cudaStreamSynchronize(st));          // hpos/hseq are reused by the next chunk
         KX_TRY(op_embed(e->tokens, e->embed, e->resid, M, d.hidden, st));
         for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, b0, 0, st, P));
@@ -724,6 +714,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         std::vector<int> rows(nb);
         for (int b = 0; b < nb; ++b) rows[b] = b * S + S - 1;
         KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        h2d += (int64_t)nb * 4;
         KX_CUDA(cudaStreamSynchronize(st));
         {
             const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
@@ -743,6 +734,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         for (int b = 0; b < B; ++b) sq[b] = b;
         KX_CUDA(cudaMemcpyAsync(e->pos, p0.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
         KX_CUDA(cudaMemcpyAsync(e->seq, sq.data(), (size_t)B * 4, cudaMemcpyHostToDevice, st));
+        h2d += (int64_t)2 * B * 4;
         KX_CUDA(cudaStreamSynchronize(st));
     }
     const int max_T = P + S + n_new;
@@ -810,12 +802,14 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     }
     KX_CUDA(cudaEventRecord(ev2, st));
     KX_CUDA(cudaMemcpyAsync(h_out, e->out_ids, (size_t)B * n_new * 4, cudaMemcpyDeviceToHost, st));
+    d2h += (int64_t)B * n_new * 4;
     KX_CUDA(cudaStreamSynchronize(st));
     if (stats) {
         cudaEventElapsedTime(&stats->prefill_ms, ev0, ev1);
         cudaEventElapsedTime(&stats->decode_ms, ev1, ev2);
         stats->decode_steps = steps_done;
         stats->launches = (int32_t)(kx_launch_count() - launches0);
+        stats->h2d_bytes = h2d; stats->d2h_bytes = d2h;
     }
     cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
     return KX_OK;

@@ -42,10 +42,10 @@ template <int BN> struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-#ifndef KX_RING_KB
-#define KX_RING_KB 96
-#endif
-    static constexpr int STAGES = (KX_RING_KB * 1024) / STAGE_BYTES;  // 96 KB: two CTAs per SM
+    // 96 KB ring: two CTAs per SM.  (Three 72 KB CTAs per SM -- so that a launch and its early-started successor are
+    // resident together -- measured slower: Llama-3.2-1B batch 64, 1.20 against 1.05 ms per decode step.)
+    static constexpr int RING_KB = 96;
+    static constexpr int STAGES = (RING_KB * 1024) / STAGE_BYTES;
     static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
@@ -716,15 +716,15 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     static_assert(kRecvBytes + kStageBufs * 32 * BM * 4 <= C::STAGES * C::STAGE_BYTES, "exchange buffers must fit in the stage ring");
     __shared__ float rinv_s[BN];                               // deferred RMSNorm: 1 / rms of every batch column of this tile
     __shared__ float sq_s[EPI == EPI_RESID_NORM ? 4 * BN : 1]; // EPI_RESID_NORM: per-warp sums of squares
+    __shared__ long long stamp_s[4];                           // diagnostic cycle stamps of CTA (0, 0, 0) (tracing only)
+    const bool cta0 = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
     asm volatile("griddepcontrol.launch_dependents;");        // our own dependents may begin their prologue
     if (threadIdx.x == 0) {
         trace_min(p.trace, 0);
-        if (p.pf_ptr)     // weights of a later launch: ask the L2 for them now
-            l2_prefetch_share(p.pf_ptr, p.pf_bytes, (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z,
-                              gridDim.x * gridDim.y * gridDim.z);
+        trace_max(p.trace, 7);
     }
     const int S = gridDim.z, z = blockIdx.z;                  // cluster = the z column; rank == z
     const int total_kb = (p.k + BK - 1) / BK;
@@ -772,6 +772,8 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             }
             asm volatile("griddepcontrol.wait;" ::: "memory");
             trace_min(p.trace, 1);
+            trace_max(p.trace, 4);
+            if (cta0) stamp_s[0] = clock64();
             for (int i = 0; i < pre; ++i)
                 tma_load_2d_hint(smem + i * C::STAGE_BYTES + C::A_BYTES, &tmB, full + i, (kb0 + i) * BK, n0, pol_x);
             for (int i = pre; i < nkb; ++i) {
@@ -789,6 +791,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % C::STAGES;
                 mbar_wait(full + s, (i / C::STAGES) & 1);
+                if (cta0 && i == 0) stamp_s[1] = clock64();
                 tc_fence_after();
                 const uint32_t sa = base + s * C::STAGE_BYTES;
                 const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + C::A_BYTES);
@@ -797,6 +800,7 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 umma_commit(empty + s);
             }
             umma_commit(tmem_full);
+            if (cta0) stamp_s[2] = clock64();
         }
     } else {
         asm volatile("griddepcontrol.wait;" ::: "memory");     // outputs (and the residual read) follow the predecessor
@@ -858,7 +862,6 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             }
             if (probe) ckw = clock64();
             mbar_wait(xchg, 0);                                // all S slices of this CTA's columns have landed
-            if (threadIdx.x == 64) trace_max(p.trace, 4);
         }
     }
     if (probe) ck0 = clock64();
@@ -1012,10 +1015,11 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
             }
         }
     }
-    if (probe) {       // cycles: [5] = barrier | push loop, [6] = wait for the slices | first column sums, [7] = whole epilogue
-        p.trace[5] = ((unsigned long long)(ckp - ckb) << 32) | (unsigned long long)(unsigned)(ckw - ckp);
-        p.trace[6] = ((unsigned long long)(ck0 - ckw) << 32) | (unsigned long long)(unsigned)(ck1 - ck0);
-        p.trace[7] = (unsigned long long)(clock64() - ck0);
+    if (probe) {       // cycles of CTA (0,0,0): [5] = predecessor done -> first operands landed | -> last MMA issued,
+                       // [6] = -> accumulator complete | split-K exchange, [7] = reduce + epilogue
+        (void)ckp; (void)ckw; (void)ck1;
+        p.trace[5] = ((unsigned long long)(stamp_s[1] - stamp_s[0]) << 32) | (unsigned long long)(unsigned)(stamp_s[2] - stamp_s[1]);
+        p.trace[6] = ((unsigned long long)(ckb - stamp_s[2]) << 32) | (unsigned long long)(unsigned)(ck0 - ckb);
     }
     if (S > 1 && warp == 2) bulk_wait_group_read0();           // the copy engine has read this CTA's staging buffers
     tc_fence_before();
@@ -1201,7 +1205,7 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.splits = splits;
     KX_REQUIRE(p.epilogue != EPI_RESID_NORM || (p.swap && p.norm_g && p.norm_out && p.ssq_out && !p.tp_peer_recv), KX_EINVAL,
                "kx_gemm: EPI_RESID_NORM needs the swap-AB kernel and its norm arguments");
-    if (p.swap && (splits > 1 || p.tp_peer_recv || p.ssq_in || p.epilogue == EPI_RESID_NORM || p.pf_ptr)) {
+    if (p.swap && (splits > 1 || p.tp_peer_recv || p.ssq_in || p.epilogue == EPI_RESID_NORM)) {
         // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory
         if (splits > kMaxSplits) splits = kMaxSplits;
         p.kb_per_split = (total_kb + splits - 1) / splits;

@@ -60,9 +60,6 @@ struct GemmParams {
     int ssq_ld, ssq_tiles;
     float norm_eps, norm_inv_n;   // eps and 1 / hidden of the norm being applied
     const float *col_scale;  // single-CTA swap-AB kernel, EPI_F32: logits column b is multiplied by col_scale[b] (or NULL)
-    // L2 prefetch of the weights a later kernel will stream (issued at kernel start, spread over the CTAs)
-    const void *pf_ptr;
-    size_t pf_bytes;
 };
 
 int make_tmap_bf16_2d(CUtensorMap *out, const void *ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);

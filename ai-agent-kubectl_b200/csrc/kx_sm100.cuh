@@ -105,21 +105,6 @@ __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, 
                  ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// Ask the L2 to fetch [p, p + bytes) from HBM (bytes a multiple of 16, p 16 B aligned).  Fire and forget: no
-// shared memory, no completion to wait for.
-__device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-}
-// This CTA's share of a prefetch of [p, p + bytes) spread over n_ctas CTAs, issued by the calling thread in
-// `chunk`-byte pieces interleaved across the CTAs (so the range fills front to back as the CTAs issue in parallel).
-__device__ __forceinline__ void l2_prefetch_share(const void *p, size_t bytes, uint32_t cta, uint32_t n_ctas, uint32_t chunk = 8192) {
-    const char *base = reinterpret_cast<const char *>(p);
-    for (size_t o = (size_t)cta * chunk; o < bytes; o += (size_t)n_ctas * chunk) {
-        const size_t left = bytes - o;
-        l2_prefetch(base + o, (uint32_t)((left < chunk ? left : chunk) & ~(size_t)15));
-    }
-}
-
 // TMA reduce-store: global[tile] += smem[tile] (element type and box from the tensor map; performed by the L2's
 // reduction units, the SM never reads the destination).  Bulk-group completion: commit, then wait_group.read
 // before the shared-memory source is overwritten.

@@ -36,7 +36,8 @@ class KxModelWeights(ctypes.Structure):
 
 
 class KxGenStats(ctypes.Structure):
-    _fields_ = [("prefill_ms", c_float), ("decode_ms", c_float), ("decode_steps", c_int32), ("launches", c_int32)]
+    _fields_ = [("prefill_ms", c_float), ("decode_ms", c_float), ("decode_steps", c_int32), ("launches", c_int32),
+                ("h2d_bytes", ctypes.c_int64), ("d2h_bytes", ctypes.c_int64)]
 
 
 _lib.declare("kx_engine_create", ctypes.c_int, [ctypes.POINTER(KxModelDesc), ctypes.POINTER(KxModelWeights),

@@ -25,6 +25,10 @@ logger = logging.getLogger(__name__)
 SAFE, BAD_PREFIX, METACHAR, BAD_QUOTING = 0, 1, 2, 3
 FLAG_PARSE = 1
 
+# bytes handed to kx_validate_hash_host for the host -> device copy, and bytes it copies back, since import
+# (counted here, at the call that performs the copies; bench.py reads the difference around a step)
+copied = {"h2d": 0, "d2h": 0}
+
 
 def to_csr(strings: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
     """list[str] -> (uint8 data[sum len], int64 off[n+1]) in UTF-8."""
@@ -59,6 +63,8 @@ def validate_hash_host(data: np.ndarray, off: np.ndarray, flags: int = 0, *, ver
         out["san"] = np.empty(data.size, np.uint8)
         out["san_len"] = np.empty(n, np.int32)
     L = _lib.lib()
+    copied["h2d"] += data.nbytes + off.nbytes
+    copied["d2h"] += sum(out[k].nbytes for k in ("verdict", "hash", "span", "san", "san_len") if k in out)
     _lib.check(L.kx_validate_hash_host(_ptr(data), off.ctypes.data, n, flags, _ptr(out.get("verdict")),
                                        _ptr(out.get("hash")), _ptr(out.get("span")), _ptr(out.get("san")),
                                        _ptr(out.get("san_len")), device))

@@ -259,7 +259,8 @@ def run_validate_hash(args):
                          "parity_on_sample": parity},
         "e2e": {"value": world * n * e2e_steps / e2e_s, "unit": "strings/s",
                 "h2d_bytes_per_step": total_bytes + 8 * (n + 1), "d2h_bytes_per_step": 9 * n,
-                "api": "kx_validate_hash_host (pinned host CSR in, host verdict+hash out)", "steps": e2e_steps},
+                "api": "kx_validate_hash_host (pinned host CSR in, host verdict+hash out)", "steps": e2e_steps,
+                "note": "bound by the host -> device copy of the strings (PCIe), not by the kernel"},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
@@ -320,29 +321,30 @@ def gen_prompts(n, seed):
     return [PROMPT_PREFIX + f"{q} (request {i})" + PROMPT_SUFFIX for i, q in enumerate(synth.queries(n, seed=seed))]
 
 
-def cpu_generation_rate(arch, prompts, prompt_len, new_tokens, seed, prefix_tokens=None):
+def cpu_generation_rate(arch, prompts, prompt_len, new_tokens, seed, prefix_tokens=None, want_logits=False):
     """The repo pipeline on host cores: fp32 PyTorch CPU model of the same architecture
-    and weights in the llm slot, then parser + validator (Python port of app.py:95-104)."""
+    and weights in the llm slot, then parser + validator (Python port of app.py:95-104).
+    Returns (commands/s, ids, fp32 logits per step or None, verdicts)."""
     import torch
     from kubectl_b200 import model_config, tokenizer, weights
     from oracle import py_oracle as po
     from oracle.cpu_model import RefModel
     cfg = model_config.get_config(arch)
-    w = weights.make_weights(cfg, seed)
+    w = weights.make_weights(cfg, seed, embed_std=cfg.parity_embed_std)     # the init the GPU arm uses (weights.py)
     ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos))
     toks = torch.tensor([tokenizer.encode_fixed(p, prompt_len) for p in prompts], dtype=torch.int64)
     if prefix_tokens is not None:      # same token stream the GPU sees: cached prefix, then the request's own tokens
         toks = torch.cat([torch.tensor(prefix_tokens, dtype=torch.int64)[None, :].expand(len(prompts), -1), toks], dim=1)
     t0 = time.perf_counter()
-    ids, _ = ref.generate(toks, new_tokens)
+    ids, logits = ref.generate(toks, new_tokens, return_logits=want_logits)
     texts = [tokenizer.decode(r.tolist()) for r in ids]
     verdicts = [po.ref_parse(t)[1] for t in texts]
     dt = time.perf_counter() - t0
-    return len(prompts) / dt, ids.numpy(), verdicts
+    return len(prompts) / dt, ids.numpy(), (torch.stack(logits) if want_logits else None), verdicts
 
 
 def time_gemm_live(M, N, K, reps):
-    """The dominant kernel (prefill GEMM, gate/up shape) timed alone with CUDA events."""
+    """The prefill GEMM at the gate/up shape, timed alone with CUDA events."""
     import torch
     from kubectl_b200 import _lib
     L = _lib.lib()
@@ -364,6 +366,47 @@ def time_gemm_live(M, N, K, reps):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     return ms, 2.0 * M * N * K / (ms * 1e-3) / 1e12
+
+
+def k9_block(dev, pk, n_distinct=1_000_000, repeat=10, reps=10):
+    """BASELINE configs[1] inside the default line: validate + hash of 10 M command strings, device resident.
+    1 M distinct synthetic strings are generated on the host and laid out `repeat` times in HBM (530 MB, far beyond
+    the L2, every copy at its own addresses); the kernel's work per string does not depend on the others."""
+    import torch
+    from kubectl_b200 import strings, synth
+    data, off = synth.command_csr(n_distinct, seed=2)
+    nb = int(off[-1])
+    d1 = torch.from_numpy(data).to(dev)
+    o1 = torch.from_numpy(off).to(dev)
+    d_data = d1.repeat(repeat)
+    d_off = torch.cat([o1[:-1] + r * nb for r in range(repeat)] + [torch.tensor([repeat * nb], device=dev)])
+    n = n_distinct * repeat
+    verdict = torch.empty(n, dtype=torch.uint8, device=dev)
+    hsh = torch.empty(n, dtype=torch.int64, device=dev)
+    for _ in range(3):
+        strings.validate_hash_device(d_data, d_off, 0, verdict=verdict, hash=hsh)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        strings.validate_hash_device(d_data, d_off, 0, verdict=verdict, hash=hsh)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    # the ten copies must agree with each other and (first 20,000 strings) with the C oracle
+    v = verdict.view(repeat, n_distinct)
+    h = hsh.view(repeat, n_distinct)
+    assert bool((v == v[0]).all()) and bool((h == h[0]).all()), "k9: copies of the same strings disagree"
+    from oracle import c_oracle
+    m = 20_000
+    ref = c_oracle.validate_hash(data[:int(off[m])], off[:m + 1], 0)
+    if not (np.array_equal(ref["verdict"], v[0, :m].cpu().numpy()) and np.array_equal(ref["hash"], h[0, :m].cpu().numpy())):
+        raise SystemExit("bench: k9 results differ from the C oracle")
+    algo = repeat * nb + n * (8 + 1 + 8)
+    gbs = algo / (ms * 1e-3) / 1e9
+    return {"strings": n, "strings_per_s": n / (ms * 1e-3), "kernel_ms": ms, "algorithmic_bytes": algo, "achieved_gbs": gbs,
+            "frac": gbs / pk["hbm_gbs"], "layout": f"{n_distinct} distinct strings x {repeat} copies, device resident",
+            "parity": f"first {m} strings equal to the C oracle; all copies equal"}
 
 
 def run_generate(args):
@@ -398,7 +441,7 @@ def run_generate(args):
     else:
         prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
     eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank,
-                            tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX)
+                            tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX, parity_init=True)
     model = B200ChatModel(temperature=0, api_key=None, model=args.arch, request_timeout=600, engine=eng, max_wait_ms=50)
     parser = strings.KubectlOutputParser()
     toks = np.asarray([tokenizer.encode_fixed(p, S) for p in prompts], np.int32)
@@ -430,12 +473,19 @@ def run_generate(args):
         dev_ms = e0.elapsed_time(e1)
         # ---- end-to-end leg: strings in, validated commands out, through the drop-in's public API ----
         e2e_steps = max(2, min(args.steps, 3))
+        copies = {"h2d": 0, "d2h": 0}
+
         def api_pass():
+            c0 = dict(strings.copied)
             if tp > 1:      # TP ranks must form identical batches: drive the engine below the batching front end
                 texts = eng.generate(prompts)
             else:
                 texts = [o.content for o in model.batch(prompts)]        # tokenise -> H2D -> generate -> D2H -> text
-            return texts, parser.parse_batch(texts)                      # fence strip + validator on the GPU (k9)
+            cmds_ = parser.parse_batch(texts)                            # fence strip + validator on the GPU (k9)
+            st_ = eng.gen.last_stats                                     # bytes counted where the copies are issued
+            copies["h2d"] = st_.h2d_bytes + strings.copied["h2d"] - c0["h2d"]
+            copies["d2h"] = st_.d2h_bytes + strings.copied["d2h"] - c0["d2h"]
+            return texts, cmds_
         outs, cmds = api_pass()
         barrier()
         t0 = time.perf_counter()
@@ -443,7 +493,7 @@ def run_generate(args):
             outs, cmds = api_pass()
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
-        # ---- the dominant kernel alone: prefill GEMM at the gate/up shape ----
+        # ---- the prefill GEMM alone, at the gate/up shape ----
         gM = min(mine * S, 32768)
         gemm_ms, gemm_tflops = time_gemm_live(gM, 2 * cfg.inter // tp, cfg.hidden, 20)
     clocks = sampler.summary()
@@ -455,64 +505,104 @@ def run_generate(args):
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_s, prefill_ms, decode_ms = (float(x) for x in t.tolist())
-    model.close()
     if rank != 0:
+        model.close()
         return None
 
     pk = peaks()
     n_safe = sum(c is not None for c in cmds)
     step_ms = decode_ms / max(1, dsteps)
     kv_avg = mine * (PFX + S + NEW / 2.0) * cfg.kv_bytes_per_token() / tp
-    decode_gbs = (cfg.decode_weight_bytes() / tp + kv_avg) / (step_ms * 1e-3) / 1e9          # per rank
+    decode_bytes = cfg.decode_weight_bytes() / tp + kv_avg                                    # per rank and step
+    decode_gbs = decode_bytes / (step_ms * 1e-3) / 1e9
     prefill_flops = 2.0 * cfg.matmul_params() * mine * S / tp
-    # CPU baseline: same pipeline with the fp32 CPU model, bounded sample, checked against the GPU ids
+    # ---- CPU baseline + parity gate (BASELINE north_star checks 1-2): the same pipeline with the fp32 CPU model on a
+    # bounded sample of the same requests; ids must be equal for every generated token, the logits within 1e-2, and the
+    # fp32 model's top-2 margins at least 4x the largest logit difference (oracle/parity.py states the gate)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     sample = max(1, min(mine, args.cpu_requests))
     pfx_toks = tokenizer.encode_fixed(PROMPT_PREFIX * 8, PFX) if PFX else None
-    cpu_rate, cpu_ids, _ = cpu_generation_rate(args.arch, prompts[:sample], S, NEW, args.seed, pfx_toks)
+    big = cfg.hidden * cfg.layers > 100_000             # 8B: the fp32 model does not fit comfortably; ids only, fewer requests
+    cpu_rate, cpu_ids, cpu_logits, _ = cpu_generation_rate(args.arch, prompts[:sample], S, NEW, args.seed, pfx_toks,
+                                                           want_logits=(tp == 1 and not big))
     first_diff = [int(np.argmax(np.append(cpu_ids[i] != ids[i], True))) for i in range(sample)]
+    parity = {"first_differing_token_vs_gpu": first_diff, "new_tokens": NEW}
+    if cpu_logits is not None:
+        _, gl = eng.gen.generate_ids(toks[:sample], NEW, want_logits=True)     # outside every timed region
+        gl = gl.cpu()
+        scale = cpu_logits.abs().amax(dim=(1, 2))
+        err = (gl - cpu_logits).abs().amax(dim=(1, 2))
+        top2 = cpu_logits.topk(2, dim=-1).values
+        margin = (top2[..., 0] - top2[..., 1]).amin(dim=1)
+        parity.update({"max_logit_err_over_scale": float((err / scale).max()), "min_margin_over_noise": float((margin / err).min()),
+                       "gate": "ids equal for all new tokens; logit error <= 1e-2 of the logit scale; top-2 margin >= 4x the error"})
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "pair_gemm_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
         if tj.get("shape") == [gM, 2 * cfg.inter // tp, cfg.hidden]:
             traffic = tj["dram_bytes_per_launch"]
+    dtraffic = None
+    dpath = os.path.join(ROOT, "profiles", "decode_gemm_traffic.json")
+    if os.path.exists(dpath):
+        dj = json.load(open(dpath))
+        if dj.get("batch") == mine and dj.get("arch") == args.arch:
+            dtraffic = dj["dram_bytes_per_step"]
+    coalesced = int(model.frontend.coalesced)
+    model.close()
+    k9 = k9_block(dev, pk) if (args.k9 and tp == 1) else None
     line = {
         "metric": "generated kubectl commands/sec (box)", "value": total * args.steps / (dev_ms / 1e3),
         "unit": "commands/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "bf16 (fp32 accumulate, fp32 residual)", "data": "synthetic",
-        "config": {"workload": f"BASELINE configs: {args.arch} architecture, random-init weights (seed {args.seed}), "
-                               f"{total} concurrent requests split over {world} replica(s), {S}-token prompt, "
-                               f"{NEW} greedy tokens, byte-level tokenizer",
+        "config": {"workload": f"BASELINE configs: {args.arch} architecture, random-init weights (seed {args.seed}, embedding std "
+                               f"{cfg.parity_embed_std}: weights.py), {total} concurrent requests split over {replicas} replica(s), "
+                               f"{S}-token prompt, {NEW} greedy tokens, byte-level tokenizer",
                    "requests": total, "requests_per_gpu": mine, "prompt_len": S, "new_tokens": NEW,
                    "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (decode: all-reduce fused into the GEMM epilogue over NVLink peer memory; prefill: NCCL)" if tp > 1 else "") +
                                    ", no collective between replicas"),
                    "prefix_cached_tokens": PFX,
                    "l2": "weights + KV + activations per step exceed the 126 MB L2 (%.2f GB weights)" % (cfg.decode_weight_bytes() / 1e9),
                    "validator_verdicts": {"safe": n_safe, "rejected": len(cmds) - n_safe},
-                   "coalesced_duplicates": int(model.frontend.coalesced)},
-        "ttft_p50_ms": prefill_ms, "decode_ms_per_step": step_ms, "decode_hbm_gbs": decode_gbs,
+                   "coalesced_duplicates": coalesced},
+        "ttft_p50_ms": prefill_ms, "ttft_note": "all requests arrive at t = 0 and are prefilled as one batch: TTFT = the batch's prefill",
+        "decode_ms_per_step": step_ms, "decode_hbm_gbs": decode_gbs,
         "decode_hbm_frac": decode_gbs / pk["hbm_gbs"], "prefill_tflops": prefill_flops / (prefill_ms * 1e-3) / 1e12,
         "prefill_tensor_frac": prefill_flops / (prefill_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
-        "roofline": {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / pk["bf16_tflops"], "traffic": traffic, "peak_source": pk["source"] + " (burst: kernel timed alone)",
-                     "kernel": "kx_gemm_bf16_kernel (prefill, SwiGLU epilogue)", "kernel_ms": gemm_ms,
-                     "shape": [gM, 2 * cfg.inter // tp, cfg.hidden],
-                     "algorithmic_flops_per_launch": 2.0 * gM * 2 * cfg.inter // tp * cfg.hidden},
+        # the phase furthest below its roofline: the decode step (weights + KV streamed once per step), all of its kernels
+        "roofline": {"bound": "hbm", "achieved": decode_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                     "frac": decode_gbs / pk["hbm_gbs"], "traffic": dtraffic, "peak_source": pk["source"] + " (copy bandwidth)",
+                     "kernel": "decode step: kx_gemm_bf16_ksplit_kernel (projections) + attention + lm_head, timed as a whole "
+                               "with CUDA events on the engine's stream",
+                     "kernel_ms": step_ms, "algorithmic_bytes_per_launch": decode_bytes,
+                     "frac_of_nominal_8TBs": decode_gbs / 8000.0},
+        "roofline_prefill": {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
+                             "frac": gemm_tflops / pk["bf16_tflops"], "traffic": traffic,
+                             "peak_source": pk["source"] + " (burst: kernel timed alone)",
+                             "kernel": "kx_gemm_bf16_pair_kernel (prefill, SwiGLU epilogue)", "kernel_ms": gemm_ms,
+                             "shape": [gM, 2 * cfg.inter // tp, cfg.hidden],
+                             "algorithmic_flops_per_launch": 2.0 * gM * 2 * cfg.inter // tp * cfg.hidden,
+                             "whole_prefill_frac_of_sustained": prefill_flops / (prefill_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"]},
+        "k9": k9,
         "cpu_baseline": {"value": cpu_rate, "unit": "commands/s", "cores": cores, "kind": "port",
-                         "sample": f"{sample} of the same requests: fp32 PyTorch CPU model of {args.arch} (same weights) "
+                         "sample": f"{sample} of the same requests in one batch: fp32 PyTorch CPU model of {args.arch} (same weights) "
                                    f"+ Python port of parser/validator, torch threads = {cores}",
-                         "first_differing_token_vs_gpu": first_diff},
+                         **parity},
         "e2e": {"value": total * e2e_steps / e2e_s, "unit": "commands/s",
-                "h2d_bytes_per_step": int(toks.nbytes + sum(len(o.encode()) for o in outs) + 8 * (len(outs) + 1)),
-                "d2h_bytes_per_step": int(mine * NEW * 4 + 5 * len(outs)),
+                "h2d_bytes_per_step": int(copies["h2d"]), "d2h_bytes_per_step": int(copies["d2h"]),
+                "bytes_counted": "at the copy sites: kx_engine_generate (kx_gen_stats) + kx_validate_hash_host (strings.copied), per rank",
                 "api": "B200ChatModel.batch(prompts) -> KubectlOutputParser.parse_batch (strings in, validated commands out)",
                 "steps": e2e_steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    # the parity gate is part of the result: a line whose ids differ from the fp32 model is not a valid measurement
+    ok = all(f == NEW for f in first_diff)
+    if cpu_logits is not None:
+        ok = ok and parity["max_logit_err_over_scale"] <= 1e-2 and parity["min_margin_over_noise"] >= 4.0
+    line["parity_ok"] = bool(ok)
     return line
 
 
@@ -528,7 +618,7 @@ def run_reference_generate(args):
     prompts = gen_prompts(args.requests, seed=1)[:n]
     rates = []
     for i in range(args.warmup + args.steps):
-        r, _, _ = cpu_generation_rate(args.arch, prompts, args.prompt_len, args.new_tokens, args.seed)
+        r, _, _, _ = cpu_generation_rate(args.arch, prompts, args.prompt_len, args.new_tokens, args.seed)
         if i >= args.warmup:
             rates.append(r)
     value = float(np.mean(rates))
@@ -536,8 +626,9 @@ def run_reference_generate(args):
         "impl": "reference", "metric": "generated kubectl commands/sec (box)", "value": value, "unit": "commands/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": n / value * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": {"workload": f"{args.arch} architecture on host cores, {n} requests per step, "
+        "config": {"workload": f"{args.arch} architecture on host cores, {n} requests per step (one batch), "
                                f"{args.prompt_len}-token prompt, {args.new_tokens} greedy tokens",
+                   "requests_per_step": n,
                    "note": "the reference sends this step to OpenAI (app.py:117); offline its pipeline is timed with an "
                            "fp32 CPU model of the named architecture in the llm slot"},
         "cpu_baseline": {"value": value, "unit": "commands/s", "cores": cores, "kind": "port",
@@ -563,7 +654,8 @@ def main():
     ap.add_argument("--prompt-len", type=int, default=256)
     ap.add_argument("--new-tokens", type=int, default=32)
     ap.add_argument("--seed", type=int, default=4)
-    ap.add_argument("--cpu-requests", type=int, default=4)
+    ap.add_argument("--cpu-requests", type=int, default=8, help="requests per CPU batch (cpu_baseline sample / reference-arm step)")
+    ap.add_argument("--k9", type=int, default=1, help="1: add the validate+hash block (BASELINE configs[1]) to the generate line")
     ap.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per replica (config 5: 2)")
     ap.add_argument("--prefix-len", type=int, default=0, help="tokens of shared, prefix-cached system prompt (config 5: 1024)")
     ap.add_argument("--strings", type=int, default=10_000_000)
@@ -583,6 +675,10 @@ def main():
         import torch.distributed as dist
         if dist.is_initialized():
             dist.destroy_process_group()
+    if line is not None and line.get("parity_ok") is False:
+        print("bench: the GPU's greedy ids / logits do not pass the parity gate against the fp32 CPU model "
+              f"({line['cpu_baseline']})", file=sys.stderr)
+        sys.exit(3)
 
 
 if __name__ == "__main__":

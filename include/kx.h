@@ -140,11 +140,6 @@ int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, 
                  int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
                  void *stream);
 
-/* Asks the L2 to fetch [d_ptr, d_ptr + bytes) (16-byte aligned) from HBM ahead of the kernels that will read it
- * (cp.async.bulk.prefetch.L2); the decode kernels do this themselves for the weights of their successor.
- * No reference counterpart. */
-int kx_l2_prefetch(const void *d_ptr, int64_t bytes, void *stream);
-
 /* Second stage of KX_EPI_ARGMAX: d_parts int2 [n_parts][ld] -> d_ids int32 [B]; ties go to the lowest id. */
 int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream);
 
@@ -211,6 +206,8 @@ typedef struct kx_gen_stats {
     float decode_ms;       /* all remaining steps                                      */
     int32_t decode_steps;
     int32_t launches;      /* kernels launched by this call (graph replays counted)    */
+    int64_t h2d_bytes;     /* bytes this call copied host -> device (tokens, positions) */
+    int64_t d2h_bytes;     /* ... and device -> host (the generated ids)               */
 } kx_gen_stats;
 
 typedef struct kx_engine kx_engine;

@@ -20,7 +20,7 @@ st = gen.last_stats
 tr = gen.trace()
 t0 = min(r[1] for r in tr)
 print(f"{arch} B={B} S={S}: decode {st.decode_ms / st.decode_steps * 1e3:.1f} us/step, {len(tr)} traced launches in the last step")
-print(f"{'#':>4} {'kernel':<12} {'start':>8} {'deps':>8} {'main':>8} {'xchg':>8} {'bar/push':>11} {'wait/sums':>11} {'epi':>6} {'end':>8} | {'dur':>6} {'after-deps':>10} {'gap':>6}   (us)")
+print(f"{'#':>4} {'kernel':<12} {'start':>8} {'deps':>8} {'main':>8} {'depsmax':>8} {'ops/mma':>11} {'acc/xchg':>11} {'startmax':>8} {'end':>8} | {'dur':>6} {'after-deps':>10} {'gap':>6}   (us)")
 prev_end = t0
 per = {}
 for i, (name, a, b, c, d, x4, x5, x6, x7) in enumerate(tr):
@@ -28,7 +28,7 @@ for i, (name, a, b, c, d, x4, x5, x6, x7) in enumerate(tr):
     k = per.setdefault(name, [0, 0.0, 0.0, 0.0])
     k[0] += 1; k[1] += dur; k[2] += work; k[3] += (d - max(prev_end, a)) / 1e3 if d > prev_end else 0.0
     if i < show * 8 + 2 or i >= len(tr) - 4:
-        print(f"{i:>4} {name:<12} {(a - t0) / 1e3:8.2f} {(b - t0) / 1e3:8.2f} {(c - t0) / 1e3 if c else 0:8.2f} {(x4 - t0) / 1e3 if x4 else 0:8.2f} {x5 >> 32:5d}/{x5 & 0xffffffff:<5d} {x6 >> 32:5d}/{x6 & 0xffffffff:<5d} {x7:6d} {(d - t0) / 1e3:8.2f} | "
+        print(f"{i:>4} {name:<12} {(a - t0) / 1e3:8.2f} {(b - t0) / 1e3:8.2f} {(c - t0) / 1e3 if c else 0:8.2f} {(x4 - t0) / 1e3 if x4 else 0:8.2f} {x5 >> 32:5d}/{x5 & 0xffffffff:<5d} {x6 >> 32:5d}/{x6 & 0xffffffff:<5d} {(x7 - t0) / 1e3 if x7 else 0:8.2f} {(d - t0) / 1e3:8.2f} | "
               f"{dur:6.2f} {work:10.2f} {(a - prev_end) / 1e3:6.2f}")
     prev_end = max(prev_end, d)
 print(f"span of traced launches: {(prev_end - t0) / 1e3:.1f} us")
