@@ -30,9 +30,9 @@ __device__ const k9::FastTables g_tables = k9::make_fast_tables();
 struct __align__(16) Shared {
     k9::FastTables tab;
     int32_t soff[kThreads + 1];           // string offsets relative to the staged base
-    int32_t hist[32];
+    int32_t hist[64];
     int32_t perm[kThreads];
-    int32_t slowq[kThreads];
+    int32_t slowq[kThreads];              // strings for the general pass (second kernel)
     int32_t nslow;
     uint32_t qbase;
 };
@@ -74,24 +74,25 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
         uint32_t *dst = reinterpret_cast<uint32_t *>(&sh.tab);
         for (int i = tid; i < (int)(sizeof(k9::FastTables) / 4); i += kThreads) dst[i] = src[i];
         for (int i = tid; i <= cnt; i += kThreads) sh.soff[i] = (int32_t)(off[s0 + i] - g_beg) + lead;
-        if (tid < 32) sh.hist[tid] = 0;
+        if (tid < 64) sh.hist[tid] = 0;
         __syncthreads();
 
-        // ---- give each warp strings of similar length (counting sort on len/8) ----
+        // ---- give each warp strings of similar length (counting sort on len/4: the scan loop runs once per word) ----
         int bucket = 0, rank = 0;
         if (tid < cnt) {
-            bucket = min((sh.soff[tid + 1] - sh.soff[tid]) >> 3, 31);
+            bucket = min((sh.soff[tid + 1] - sh.soff[tid]) >> 2, 63);
             rank = atomicAdd(&sh.hist[bucket], 1);
         }
         __syncthreads();
         if (tid < 32) {
-            const int c = sh.hist[tid];
-            int incl = c;
+            const int c0 = sh.hist[2 * tid], c1 = sh.hist[2 * tid + 1];
+            int incl = c0 + c1;
             for (int d = 1; d < 32; d <<= 1) {
                 const int t = __shfl_up_sync(0xffffffffu, incl, d);
                 if (tid >= d) incl += t;
             }
-            sh.hist[tid] = incl - c;                      // exclusive prefix
+            sh.hist[2 * tid] = incl - c0 - c1;            // exclusive prefix
+            sh.hist[2 * tid + 1] = incl - c1;
         }
         __syncthreads();
         if (tid < cnt) sh.perm[sh.hist[bucket] + rank] = tid;
@@ -101,7 +102,7 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
             const int i = sh.perm[tid];
             k9::Result r;
             const bool slow = k9::fast_string<PARSE>(reinterpret_cast<uint32_t *>(stage), sh.soff[i], sh.soff[i + 1],
-                                                     sh.tab.cls, sh.tab.trans, hash != nullptr,
+                                                     sh.tab.flags, hash != nullptr,
                                                      san ? san + g_beg + (sh.soff[i] - lead) : nullptr, r);
             if (slow) sh.slowq[atomicAdd(&sh.nslow, 1)] = i;
             else store_result(r, s0 + i, verdict, hash, span, san_len);
@@ -119,23 +120,69 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
     for (int q = tid; q < nslow; q += kThreads) queue[2 + sh.qbase + q] = (uint32_t)(s0 + sh.slowq[q]);
 }
 
-// Pass 2: general code-point path (k9::process_string) over the queued strings,
-// read from global memory, one string per thread with the queue packed densely.
+// Pass 2: general code-point path (k9::process_string) over the queued strings, read from global memory, one
+// string per thread.  A CTA takes 256 consecutive queue entries and hands them to its threads sorted by length
+// (counting sort on len / 8, as pass 1 does): the queue arrives in no particular order and the strings are
+// 12 - 200 bytes long, so without the sort a warp runs as long as its longest string with a third of its lanes
+// active (8.9 of 32 measured); adjacent threads now hold strings of similar length.
+constexpr int kGeneralPer = 2;                                  // strings per thread and batch
 template <bool PARSE>
 __global__ void __launch_bounds__(kGeneralThreads)
 k9_validate_hash_general(const uint8_t *__restrict__ data, const int64_t *__restrict__ off,
                          uint8_t *__restrict__ verdict, int64_t *__restrict__ hash, int32_t *__restrict__ span,
                          uint8_t *__restrict__ san, int32_t *__restrict__ san_len,
                          const uint32_t *__restrict__ queue) {
+    constexpr int kBatch = kGeneralThreads * kGeneralPer;
+    __shared__ int32_t hist[32];
+    __shared__ uint32_t order[kBatch];
+    __shared__ uint8_t lut[256];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 256; i += kGeneralThreads) lut[i] = g_tables.flags[i];
     const uint32_t count = queue[0];
-    for (uint32_t q = blockIdx.x * kGeneralThreads + threadIdx.x; q < count; q += gridDim.x * kGeneralThreads) {
-        const int64_t s = queue[2 + q];
-        const int64_t o0 = off[s], o1 = off[s + 1];
-        const uintptr_t sa = (uintptr_t)(data + o0);
-        const uint32_t *w = (const uint32_t *)(sa & ~(uintptr_t)15);
-        const int lo = (int)(sa & 15), hi = lo + (int)(o1 - o0);
-        const k9::Result r = k9::process_string<PARSE>(w, lo, hi, hash != nullptr, san ? san + o0 : nullptr);
-        store_result(r, s, verdict, hash, span, san_len);
+    for (uint32_t base = blockIdx.x * kBatch; base < count; base += gridDim.x * kBatch) {
+        const int cnt = (int)min((uint32_t)kBatch, count - base);
+        if (tid < 32) hist[tid] = 0;
+        __syncthreads();
+        uint32_t sidx[kGeneralPer];
+        int bucket[kGeneralPer], rank[kGeneralPer];
+#pragma unroll
+        for (int u = 0; u < kGeneralPer; ++u) {
+            const int q = u * kGeneralThreads + tid;
+            sidx[u] = 0; bucket[u] = 0; rank[u] = 0;
+            if (q < cnt) {
+                sidx[u] = queue[2 + base + q];
+                bucket[u] = (int)min((off[sidx[u] + 1] - off[sidx[u]]) >> 3, (int64_t)31);
+                rank[u] = atomicAdd(&hist[bucket[u]], 1);
+            }
+        }
+        __syncthreads();
+        if (tid < 32) {
+            const int c = hist[tid];
+            int incl = c;
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (tid >= d) incl += t;
+            }
+            hist[tid] = incl - c;                              // exclusive prefix
+        }
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < kGeneralPer; ++u)
+            if (u * kGeneralThreads + tid < cnt) order[hist[bucket[u]] + rank[u]] = sidx[u];
+        __syncthreads();
+#pragma unroll 1
+        for (int u = 0; u < kGeneralPer; ++u) {
+            const int q = u * kGeneralThreads + tid;
+            if (q >= cnt) continue;
+            const int64_t s = order[q];
+            const int64_t o0 = off[s], o1 = off[s + 1];
+            const uintptr_t sa = (uintptr_t)(data + o0);
+            const uint32_t *w = (const uint32_t *)(sa & ~(uintptr_t)15);
+            const int lo = (int)(sa & 15), hi = lo + (int)(o1 - o0);
+            const k9::Result r = k9::process_string<PARSE>(w, lo, hi, lut, hash != nullptr, san ? san + o0 : nullptr);
+            store_result(r, s, verdict, hash, span, san_len);
+        }
+        __syncthreads();                                       // order / hist are reused by the next batch
     }
 }
 
@@ -151,7 +198,8 @@ int launch_passes(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const unsigned gblocks = (unsigned)min((int64_t)sms * 8, (n + kGeneralThreads - 1) / kGeneralThreads);
+    const int64_t gbatch = kGeneralThreads * kGeneralPer;
+    const unsigned gblocks = (unsigned)min((int64_t)sms * 32, (n + gbatch - 1) / gbatch);
     if (flags & KX_FLAG_PARSE) {
         k9_validate_hash_fast<true><<<blocks, kThreads, kSmemBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
         k9_validate_hash_general<true><<<gblocks, kGeneralThreads, 0, st>>>(d_data, d_off, d_verdict, d_hash, d_span, d_san, d_san_len, queue);

@@ -24,13 +24,13 @@ extern "C" int64_t k9_emul(const uint8_t *data, const int64_t *off, int64_t n, u
         k9::Result r;
         bool slow = true;
         if (mode != 1)     // the kernel's staged fast path (mutates its buffer in place)
-            slow = parse ? k9::fast_string<true>(buf.data(), lead, lead + (int)len, tab.cls, tab.trans, hash != nullptr, sp, r)
-                         : k9::fast_string<false>(buf.data(), lead, lead + (int)len, tab.cls, tab.trans, hash != nullptr, sp, r);
+            slow = parse ? k9::fast_string<true>(buf.data(), lead, lead + (int)len, tab.flags, hash != nullptr, sp, r)
+                         : k9::fast_string<false>(buf.data(), lead, lead + (int)len, tab.flags, hash != nullptr, sp, r);
         if (slow) {        // general path re-reads the pristine bytes, as the kernel does from global memory
             buf.assign(buf.size(), 0x5A5A5A5Au);
             memcpy((uint8_t *)buf.data() + lead, data + off[s], (size_t)len);
-            r = parse ? k9::process_string<true>(buf.data(), lead, lead + (int)len, hash != nullptr, sp)
-                      : k9::process_string<false>(buf.data(), lead, lead + (int)len, hash != nullptr, sp);
+            r = parse ? k9::process_string<true>(buf.data(), lead, lead + (int)len, tab.flags, hash != nullptr, sp)
+                      : k9::process_string<false>(buf.data(), lead, lead + (int)len, tab.flags, hash != nullptr, sp);
             ++nslow;
         }
         if (hash) hash[s] = r.hash;
