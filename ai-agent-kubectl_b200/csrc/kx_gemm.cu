@@ -1050,12 +1050,15 @@ int launch_ksplit(const CUtensorMap &ta, const CUtensorMap &tb, const GemmParams
     cfg.attrs = attr;
     cfg.numAttrs = 2;
     if (p.tp_peer_recv) {
-        // every CTA spins on a flag the SAME tile's CTA on the peer GPU publishes: that only terminates if all clusters
-        // of the grid are resident at once on both GPUs
-        int max_clusters = 0;
-        KX_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
-        KX_REQUIRE((int)(grid.x * grid.y) <= max_clusters, KX_EINVAL,
-                   "kx_gemm: fused all-reduce needs all %u clusters of %u CTAs co-resident, the GPU holds %d", grid.x * grid.y, grid.z, max_clusters);
+        // Every CTA waits for a flag the SAME tile's CTA on the peer GPU publishes, so the grid has to be one resident
+        // wave on both GPUs: two CTAs of this kernel fit an SM (ncu: shared-memory limit 2), and the measured sweep
+        // (profiles/r01_sweep_decode_gemm.txt) shows clusters of up to 8 packing up to ~256 CTAs, larger ones ~192.
+        // (cudaOccupancyMaxActiveClusters reports one CTA per SM for this kernel -- 15 clusters of 8 -- which the
+        // launch list contradicts, so the bound is the measured one.)  A rank that still never sees its peer's flag
+        // traps after a bounded number of polls instead of hanging both GPUs.
+        const unsigned ctas = grid.x * grid.y * grid.z, limit = grid.z <= 8 ? 256u : 192u;
+        KX_REQUIRE(ctas <= limit, KX_EINVAL, "kx_gemm: fused all-reduce needs its %u CTAs (clusters of %u) in one resident wave (<= %u)",
+                   ctas, grid.z, limit);
     }
     KX_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     count_launch();

@@ -143,7 +143,12 @@ class Generator:
         self.cfg = get_config(arch)
         self.device = torch.device("cuda", device)
         self.max_batch, self.max_seq = max_batch, max_seq
-        self.logical = weights if weights is not None else weights_mod.make_weights(self.cfg, seed, embed_std)
+        if weights is not None:
+            self.logical = weights
+        elif embed_std is not None:      # per-tensor seeds: regenerate on demand, keep nothing on the host (8B: 16 GB otherwise)
+            self.logical = weights_mod.LazyWeights(self.cfg, seed, embed_std)
+        else:
+            self.logical = weights_mod.make_weights(self.cfg, seed)
         with torch.cuda.device(self.device):
             self.packed = pack_weights(self.cfg, self.logical, self.device, tp_rank, tp_size)
             self.rope = weights_mod.rope_table(self.cfg, self.cfg.max_pos).to(self.device)
@@ -248,13 +253,13 @@ class B200Engine(Engine):
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
                  device: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl: Optional[NcclComm] = None,
                  prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512,
-                 parity_init: bool = False):
+                 parity_init: bool = False, p2p: bool = True):
         self.auto_prefix, self.max_prefix = auto_prefix, (max_prefix // 16) * 16
         self._prefix_bytes, self.prefix_sets = b"", 0
         if auto_prefix:
             prefix_len = self.max_prefix
         self.gen = Generator(arch, seed=seed, max_batch=max_batch, max_seq=prefix_len + prompt_len + max_new, device=device,
-                             tp_rank=tp_rank, tp_size=tp_size, nccl=nccl,
+                             tp_rank=tp_rank, tp_size=tp_size, nccl=nccl, p2p=p2p,
                              prefill_chunk=max(32768, prefix_len),
                              embed_std=get_config(arch).parity_embed_std if parity_init else None)
         self.max_batch, self.prompt_len, self.max_new = max_batch, prompt_len, max_new

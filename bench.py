@@ -441,7 +441,8 @@ def run_generate(args):
     else:
         prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
     eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank,
-                            tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX, parity_init=True)
+                            tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX, parity_init=True,
+                            p2p=(args.tp_allreduce == "fused"))
     model = B200ChatModel(temperature=0, api_key=None, model=args.arch, request_timeout=600, engine=eng, max_wait_ms=50)
     parser = strings.KubectlOutputParser()
     toks = np.asarray([tokenizer.encode_fixed(p, S) for p in prompts], np.int32)
@@ -561,7 +562,7 @@ def run_generate(args):
                                f"{cfg.parity_embed_std}: weights.py), {total} concurrent requests split over {replicas} replica(s), "
                                f"{S}-token prompt, {NEW} greedy tokens, byte-level tokenizer",
                    "requests": total, "requests_per_gpu": mine, "prompt_len": S, "new_tokens": NEW,
-                   "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (decode: all-reduce fused into the GEMM epilogue over NVLink peer memory; prefill: NCCL)" if tp > 1 else "") +
+                   "parallelism": (f"dp{replicas} replicas" + (f" x tp{tp} (decode all-reduce: " + ("fused into the GEMM epilogue over NVLink peer memory" if args.tp_allreduce == "fused" else "NCCL") + "; prefill: NCCL)" if tp > 1 else "") +
                                    ", no collective between replicas"),
                    "prefix_cached_tokens": PFX,
                    "l2": "weights + KV + activations per step exceed the 126 MB L2 (%.2f GB weights)" % (cfg.decode_weight_bytes() / 1e9),
@@ -657,6 +658,7 @@ def main():
     ap.add_argument("--cpu-requests", type=int, default=8, help="requests per CPU batch (cpu_baseline sample / reference-arm step)")
     ap.add_argument("--k9", type=int, default=1, help="1: add the validate+hash block (BASELINE configs[1]) to the generate line")
     ap.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per replica (config 5: 2)")
+    ap.add_argument("--tp-allreduce", default="fused", choices=["fused", "nccl"], help="decode all-reduce of a TP=2 replica (A/B)")
     ap.add_argument("--prefix-len", type=int, default=0, help="tokens of shared, prefix-cached system prompt (config 5: 1024)")
     ap.add_argument("--strings", type=int, default=10_000_000)
     ap.add_argument("--cpu-sample", type=int, default=0)
