@@ -108,7 +108,8 @@ class NcclComm:
         if rank == 0:
             assert self.lib.ncclGetUniqueId(ctypes.byref(uid)) == 0
         box = [bytes(uid)]
-        dist.broadcast_object_list(box, src=0, group=group)
+        src = dist.get_global_rank(group, 0) if group is not None else 0     # `src` is a GLOBAL rank: the group's first member
+        dist.broadcast_object_list(box, src=src, group=group)
         ctypes.memmove(uid, box[0], 128)
         self.comm = c_void_p()
 
