@@ -127,7 +127,8 @@ class Engine:
 
 
 class CallableEngine(Engine):
-    """Engine from a plain function prompt -> completion (stub LLM of config 1)."""
+    """Engine from a plain function prompt -> completion (stub LLM of config 1).  The function may return an
+    exception instance to fail that one request."""
 
     def __init__(self, fn: Callable[[str], str], max_batch: int = 64):
         self.fn, self.max_batch, self.batches = fn, max_batch, []
@@ -236,7 +237,11 @@ class BatchingFrontend:
                 if len(outs) != len(uniq):
                     raise RuntimeError(f"engine returned {len(outs)} completions for {len(uniq)} prompts")
                 for r in live:
-                    self._resolve(r, result=outs[first[r.prompt]])
+                    o = outs[first[r.prompt]]
+                    if isinstance(o, BaseException):       # this request alone failed (e.g. its prompt does not fit): a 500 for it only
+                        self._resolve(r, exc=o if isinstance(o, RuntimeError) else RuntimeError(f"{type(o).__name__}: {o}"))
+                    else:
+                        self._resolve(r, result=o)
             except BaseException as e:  # noqa: BLE001 - surfaced to every waiter as a 500
                 err = e if isinstance(e, RuntimeError) else RuntimeError(f"{type(e).__name__}: {e}")
                 for r in live:
@@ -274,6 +279,8 @@ class B200ChatModel(_LCRunnable):
         self.arch = resolve_arch(model)
         self.request_timeout = request_timeout
         self.base_url, self._api_key_ignored = base_url, api_key is not None
+        if base_url:
+            logger.warning("B200ChatModel generates locally on the GPU: base_url=%r (and the API key) are not used", base_url)
         if engine is None:
             if engine_factory is None:
                 from .engine import default_engine_factory  # the CUDA generator; raises if it cannot start

@@ -38,6 +38,8 @@ struct kx_engine {
     bool share_prefix = true;                      // decode attention reads a cached prefix once per 64 query rows
     bool fused_norm = true;                        // decode (batch < 256, no TP): RMSNorm deferred into the GEMM epilogues
     float *ssq = nullptr, *col_rinv = nullptr;     // ... per-tile sums of squares [hidden / 128][max_batch]; 1 / rms per column
+    int eos_id = -1;                               // kx_engine_set_eos: decode stops once every sequence has emitted it
+    int *done = nullptr, *h_done = nullptr;        // device [1 + max_batch]: count, per-sequence flag; pinned host copy of the count
     bool fused_argmax = true;                      // lm_head keeps (max, index) per tile instead of writing logits
     std::vector<LayerPlan> layers;
     const void *embed, *lm_head, *norm;
@@ -546,6 +548,8 @@ extern "C" int kx_engine_create(const kx_model_desc *desc, const kx_model_weight
     }
     KX_E(dev_alloc(e, (void **)&e->ssq, sizeof(float) * (size_t)(d.hidden / 128) * d.max_batch));
     KX_E(dev_alloc(e, (void **)&e->col_rinv, sizeof(float) * (size_t)d.max_batch));
+    KX_E(dev_alloc(e, (void **)&e->done, sizeof(int) * (size_t)(1 + d.max_batch)));
+    if (cudaMallocHost((void **)&e->h_done, sizeof(int)) != cudaSuccess) return fail(KX_ECUDA);
 #undef KX_E
     *out = e;
     return KX_OK;
@@ -588,6 +592,14 @@ extern "C" int kx_engine_set_collectives(kx_engine *e, void *comm, void *allredu
     e->comm = comm;
     e->allreduce = reinterpret_cast<decltype(e->allreduce)>(allreduce);
     e->allgather = reinterpret_cast<decltype(e->allgather)>(allgather);
+    return KX_OK;
+}
+
+extern "C" int kx_engine_set_eos(kx_engine *e, int32_t eos_id) {
+    KX_REQUIRE(e, KX_EINVAL, "kx_engine_set_eos: NULL engine");
+    KX_REQUIRE(eos_id < e->d.vocab * (e->d.tp_size > 1 ? e->d.tp_size : 1), KX_EINVAL, "kx_engine_set_eos: id %d is outside the vocabulary", eos_id);
+    drop_step_graphs(e);                                       // the id is a kernel argument baked into captured steps
+    e->eos_id = eos_id < 0 ? -1 : eos_id;
     return KX_OK;
 }
 
@@ -649,6 +661,7 @@ extern "C" void kx_engine_destroy(kx_engine *e) {
     if (e->p2p_peer_flag) cudaIpcCloseMemHandle(e->p2p_peer_flag);
     for (void *p : e->owned) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->h_done) cudaFreeHost(e->h_done);
     delete e->trace;
     delete e;
 }
@@ -751,7 +764,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
             for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward_fused(e, li, B, max_T, st));
             KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st, true));
             return op_decode_tail(e->next_tok, e->out_ids, n_new, P + S - 1, e->pos, e->embed, e->layers[0].w.ln1, e->resid, e->xn,
-                                  e->ssq, d.max_batch, B, d.hidden, 1, st);
+                                  e->ssq, d.max_batch, B, d.hidden, 1, e->eos_id, e->done, st);
         }
         // pos[b] currently holds the previous token's position
         advance_step_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->pos, e->step, B);
@@ -761,9 +774,20 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         KX_TRY(head_forward(e, B, nullptr, n_new, logits_dst, st));
         return KX_OK;
     };
+    // End of sequence (kx_engine_set_eos, deferred-norm path): the tail kernel counts the sequences that have emitted
+    // eos; every 8 replayed steps the host reads the count and stops launching once all have.  (Sequences that
+    // finished keep decoding until the last one has.)
+    const bool watch_eos = fused && e->eos_id >= 0;
+    if (watch_eos) KX_CUDA(cudaMemsetAsync(e->done, 0, sizeof(int) * (size_t)(1 + B), st));
     if (fused && n_new > 1)      // first decode step's input: embedding of the token prefill chose, pos -> P + S
         KX_TRY(op_decode_tail(e->next_tok, e->out_ids, n_new, P + S - 1, e->pos, e->embed, e->layers[0].w.ln1, e->resid, e->xn,
-                              e->ssq, d.max_batch, B, d.hidden, 0, st));
+                              e->ssq, d.max_batch, B, d.hidden, 0, e->eos_id, e->done, st));
+    auto all_done = [&](int t) -> bool {
+        if (!watch_eos || (t & 7) != 0) return false;
+        if (cudaMemcpyAsync(e->h_done, e->done, sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess) return false;
+        if (cudaStreamSynchronize(st) != cudaSuccess) return false;
+        return *e->h_done >= B;
+    };
     int steps_done = 0;
     if (n_new > 1 && d_logits) {
         for (int t = 1; t < n_new; ++t) KX_TRY(step_once(d_logits + (size_t)t * B * d.vocab));
@@ -772,9 +796,14 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
         kx_engine::StepGraph *hit = nullptr;
         for (auto &g : e->step_graphs)
             if (g.B == B && g.S == S && g.n_new == n_new && g.P == P) hit = &g;
+        steps_done = n_new - 1;
         if (hit) {                                             // every step replays the cached graph
-            for (int t = 1; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(hit->exec, st));
-            count_launch((int)(hit->launches * (n_new - 1)));
+            int t = 1;
+            for (; t < n_new; ++t) {
+                KX_CUDA(cudaGraphLaunch(hit->exec, st));
+                if (all_done(t)) { steps_done = t; break; }
+            }
+            count_launch((int)(hit->launches * steps_done));
         } else {
             KX_TRY(step_once(nullptr));                        // eager: also sets kernel attributes outside any capture
             if (n_new > 2) {
@@ -789,8 +818,11 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
                 const int64_t per_step = kx_launch_count() - l0;
                 KX_CUDA(cudaGraphInstantiate(&exec, graph, 0));
                 cudaGraphDestroy(graph);
-                for (int t = 2; t < n_new; ++t) KX_CUDA(cudaGraphLaunch(exec, st));
-                count_launch((int)(per_step * (n_new - 3)));  // the capture itself was counted once
+                for (int t = 2; t < n_new; ++t) {
+                    KX_CUDA(cudaGraphLaunch(exec, st));
+                    if (all_done(t)) { steps_done = t; break; }
+                }
+                count_launch((int)(per_step * (steps_done - 2)));  // the capture itself was counted once
                 if (e->step_graphs.size() >= 8) {              // small cache, oldest entry out
                     cudaGraphExecDestroy(e->step_graphs.front().exec);
                     e->step_graphs.erase(e->step_graphs.begin());
@@ -798,12 +830,14 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
                 e->step_graphs.push_back({B, S, n_new, P, exec, per_step});
             }
         }
-        steps_done = n_new - 1;
     }
     KX_CUDA(cudaEventRecord(ev2, st));
     KX_CUDA(cudaMemcpyAsync(h_out, e->out_ids, (size_t)B * n_new * 4, cudaMemcpyDeviceToHost, st));
     d2h += (int64_t)B * n_new * 4;
     KX_CUDA(cudaStreamSynchronize(st));
+    if (watch_eos && steps_done < n_new - 1)                   // steps that never ran: every sequence had already ended
+        for (int b = 0; b < B; ++b)
+            for (int t = steps_done + 1; t < n_new; ++t) h_out[(size_t)b * n_new + t] = e->eos_id;
     if (stats) {
         cudaEventElapsedTime(&stats->prefill_ms, ev0, ev1);
         cudaEventElapsedTime(&stats->decode_ms, ev1, ev2);

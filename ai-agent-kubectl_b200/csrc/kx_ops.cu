@@ -1013,7 +1013,8 @@ __global__ void pick_kernel(const int2 *__restrict__ gathered, int tp, int B, in
 __global__ void __launch_bounds__(128)
 decode_tail_kernel(const int *__restrict__ next_tok, int *__restrict__ out_ids, int n_new, int base_pos, int *__restrict__ pos,
                    const __nv_bfloat16 *__restrict__ table, const __nv_bfloat16 *__restrict__ g, float *__restrict__ resid,
-                   __nv_bfloat16 *__restrict__ xg, float *__restrict__ ssq, int ssq_ld, int H, int store) {
+                   __nv_bfloat16 *__restrict__ xg, float *__restrict__ ssq, int ssq_ld, int H, int store,
+                   int eos_id, int *__restrict__ done) {
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int b = blockIdx.x, tid = threadIdx.x;
@@ -1022,6 +1023,8 @@ decode_tail_kernel(const int *__restrict__ next_tok, int *__restrict__ out_ids, 
         const int p = pos[b];
         if (store) out_ids[(size_t)b * n_new + (p - base_pos)] = tok;
         pos[b] = p + 1;
+        // end-of-sequence bookkeeping: done[1 + b] = this sequence has emitted eos, done[0] = how many have
+        if (eos_id >= 0 && tok == eos_id && done[1 + b] == 0) { done[1 + b] = 1; atomicAdd(done, 1); }
     }
     const __nv_bfloat16 *row = table + (size_t)tok * H;
     __shared__ float ws[4];
@@ -1342,10 +1345,11 @@ int op_pick(const void *gathered, int tp, int B, int *out, cudaStream_t st) {
 }
 
 int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, int *pos, const void *table, const void *g,
-                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, cudaStream_t st) {
+                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, int eos_id, int *done, cudaStream_t st) {
     KX_REQUIRE(H % 128 == 0, KX_EINVAL, "decode tail: hidden must be a multiple of 128");
     KX_CUDA(launch_pdl(decode_tail_kernel, dim3(B), dim3(128), 0, st, next_tok, out_ids, n_new, base_pos, pos,
-                       (const __nv_bfloat16 *)table, (const __nv_bfloat16 *)g, resid, (__nv_bfloat16 *)xg, ssq, ssq_ld, H, store));
+                       (const __nv_bfloat16 *)table, (const __nv_bfloat16 *)g, resid, (__nv_bfloat16 *)xg, ssq, ssq_ld, H, store,
+                       eos_id, done));
     count_launch();
     return KX_OK;
 }

@@ -36,7 +36,7 @@ int op_argmax_parts(const void *parts, int n_parts, int ld, int B, int id_offset
 int op_advance(int *pos, int n, cudaStream_t st);
 // deferred-RMSNorm decode path: end-of-step bookkeeping + embedding of the chosen token as the next step's input
 int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, int *pos, const void *table, const void *g,
-                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, cudaStream_t st);
+                   float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, int eos_id, int *done, cudaStream_t st);
 int op_col_rinv(const float *ssq, int tiles, int ld, int B, int H, float eps, float *out, cudaStream_t st);
 // tensor-parallel helpers
 int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st);

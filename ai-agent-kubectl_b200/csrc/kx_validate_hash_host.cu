@@ -24,8 +24,11 @@ struct Staging {
     Slot slot[2];
 };
 
-std::mutex g_mu;
-Staging g_st;
+// one staging area (and one lock) per device: calls for different GPUs neither wait for each other nor free and
+// reallocate each other's buffers
+constexpr int kMaxDevices = 64;
+std::mutex g_mu[kMaxDevices];
+Staging g_st[kMaxDevices];
 
 void free_slot(Slot &s) {
     if (s.stream) cudaStreamDestroy(s.stream);
@@ -35,10 +38,7 @@ void free_slot(Slot &s) {
 }
 
 int ensure(Staging &st, int device, int64_t rows, int64_t bytes, bool want_san) {
-    if (st.device != device) {
-        for (auto &s : st.slot) free_slot(s);
-        st.device = device;
-    }
+    st.device = device;
     for (auto &s : st.slot) {
         if (!s.stream) KX_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         if (s.data_cap < bytes + 16 || (want_san && !s.san)) {
@@ -63,15 +63,16 @@ int ensure(Staging &st, int device, int64_t rows, int64_t bytes, bool want_san) 
 }  // namespace
 
 extern "C" void kx_release_host_staging(void) {
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (g_st.device >= 0) {
-        int prev = 0;
-        cudaGetDevice(&prev);
-        cudaSetDevice(g_st.device);
-        for (auto &s : g_st.slot) free_slot(s);
-        cudaSetDevice(prev);
-        g_st.device = -1;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (int d = 0; d < kMaxDevices; ++d) {
+        std::lock_guard<std::mutex> lk(g_mu[d]);
+        if (g_st[d].device < 0) continue;
+        cudaSetDevice(d);
+        for (auto &s : g_st[d].slot) free_slot(s);
+        g_st[d].device = -1;
     }
+    cudaSetDevice(prev);
 }
 
 extern "C" int kx_validate_hash_host(const uint8_t *h_data, const int64_t *h_off, int64_t n, uint32_t flags,
@@ -93,32 +94,39 @@ extern "C" int kx_validate_hash_host(const uint8_t *h_data, const int64_t *h_off
         if (h_off[r1] - h_off[r0] > max_bytes) max_bytes = h_off[r1] - h_off[r0];
     }
 
-    std::lock_guard<std::mutex> lk(g_mu);
+    KX_REQUIRE(device >= 0 && device < kMaxDevices, KX_EINVAL, "kx_validate_hash_host: device ordinal %d not supported", device);
+    std::lock_guard<std::mutex> lk(g_mu[device]);
+    Staging &st = g_st[device];
     int prev = 0;
     KX_CUDA(cudaGetDevice(&prev));
-    KX_CUDA(cudaSetDevice(device));
-    int rc = ensure(g_st, device, n < kRows ? n : kRows, max_bytes, h_san != nullptr);
-    if (rc != KX_OK) { cudaSetDevice(prev); return rc; }
-
-    for (int64_t c = 0; c < nchunks && rc == KX_OK; ++c) {
-        Slot &s = g_st.slot[c & 1];
-        const int64_t r0 = c * kRows, r1 = (r0 + kRows < n) ? r0 + kRows : n, rows = r1 - r0;
-        const int64_t b0 = h_off[r0], bytes = h_off[r1] - b0;
-        if (bytes) KX_CUDA(cudaMemcpyAsync(s.data, h_data + b0, (size_t)bytes, cudaMemcpyHostToDevice, s.stream));
-        KX_CUDA(cudaMemcpyAsync(s.off, h_off + r0, sizeof(int64_t) * (size_t)(rows + 1), cudaMemcpyHostToDevice, s.stream));
-        // offsets stay absolute: bias the base pointers instead of rewriting them
-        rc = kx_validate_hash(s.data - b0, s.off, rows, flags, h_verdict ? s.verdict : nullptr,
-                              h_hash ? s.hash : nullptr, h_span ? s.span : nullptr,
-                              h_san ? s.san - b0 : nullptr, h_san_len ? s.san_len : nullptr, s.stream);
-        if (rc != KX_OK) break;
-        if (h_verdict) KX_CUDA(cudaMemcpyAsync(h_verdict + r0, s.verdict, (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
-        if (h_hash) KX_CUDA(cudaMemcpyAsync(h_hash + r0, s.hash, sizeof(int64_t) * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
-        if (h_span) KX_CUDA(cudaMemcpyAsync(h_span + 2 * r0, s.span, sizeof(int32_t) * 2 * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
-        if (h_san_len) KX_CUDA(cudaMemcpyAsync(h_san_len + r0, s.san_len, sizeof(int32_t) * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
-        if (h_san && bytes) KX_CUDA(cudaMemcpyAsync(h_san + b0, s.san, (size_t)bytes, cudaMemcpyDeviceToHost, s.stream));
-    }
-    cudaError_t e0 = cudaStreamSynchronize(g_st.slot[0].stream);
-    cudaError_t e1 = cudaStreamSynchronize(g_st.slot[1].stream);
+    // Everything that can fail from here on runs inside this lambda, so that EVERY exit passes through the code
+    // below it: both slot streams are drained (no copy to or from the caller's buffers is still in flight when the
+    // call returns, failed or not) and the caller's current device is restored.
+    auto run = [&]() -> int {
+        KX_CUDA(cudaSetDevice(device));
+        int rc = ensure(st, device, n < kRows ? n : kRows, max_bytes, h_san != nullptr);
+        for (int64_t c = 0; c < nchunks && rc == KX_OK; ++c) {
+            Slot &s = st.slot[c & 1];
+            const int64_t r0 = c * kRows, r1 = (r0 + kRows < n) ? r0 + kRows : n, rows = r1 - r0;
+            const int64_t b0 = h_off[r0], bytes = h_off[r1] - b0;
+            if (bytes) KX_CUDA(cudaMemcpyAsync(s.data, h_data + b0, (size_t)bytes, cudaMemcpyHostToDevice, s.stream));
+            KX_CUDA(cudaMemcpyAsync(s.off, h_off + r0, sizeof(int64_t) * (size_t)(rows + 1), cudaMemcpyHostToDevice, s.stream));
+            // offsets stay absolute: bias the base pointers instead of rewriting them
+            rc = kx_validate_hash(s.data - b0, s.off, rows, flags, h_verdict ? s.verdict : nullptr,
+                                  h_hash ? s.hash : nullptr, h_span ? s.span : nullptr,
+                                  h_san ? s.san - b0 : nullptr, h_san_len ? s.san_len : nullptr, s.stream);
+            if (rc != KX_OK) break;
+            if (h_verdict) KX_CUDA(cudaMemcpyAsync(h_verdict + r0, s.verdict, (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
+            if (h_hash) KX_CUDA(cudaMemcpyAsync(h_hash + r0, s.hash, sizeof(int64_t) * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
+            if (h_span) KX_CUDA(cudaMemcpyAsync(h_span + 2 * r0, s.span, sizeof(int32_t) * 2 * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
+            if (h_san_len) KX_CUDA(cudaMemcpyAsync(h_san_len + r0, s.san_len, sizeof(int32_t) * (size_t)rows, cudaMemcpyDeviceToHost, s.stream));
+            if (h_san && bytes) KX_CUDA(cudaMemcpyAsync(h_san + b0, s.san, (size_t)bytes, cudaMemcpyDeviceToHost, s.stream));
+        }
+        return rc;
+    };
+    const int rc = run();
+    cudaError_t e0 = st.slot[0].stream ? cudaStreamSynchronize(st.slot[0].stream) : cudaSuccess;
+    cudaError_t e1 = st.slot[1].stream ? cudaStreamSynchronize(st.slot[1].stream) : cudaSuccess;
     cudaSetDevice(prev);
     if (rc != KX_OK) return rc;
     KX_REQUIRE(e0 == cudaSuccess && e1 == cudaSuccess, KX_ECUDA, "kx_validate_hash_host: %s",

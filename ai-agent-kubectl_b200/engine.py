@@ -9,6 +9,7 @@ device raises.
 from __future__ import annotations
 
 import ctypes
+import logging
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -50,6 +51,7 @@ _lib.declare("kx_engine_attn_tc_launches", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_trace", ctypes.c_int, [c_void_p, c_void_p, ctypes.c_int])
 _lib.declare("kx_engine_trace_name", ctypes.c_char_p, [c_void_p, ctypes.c_int])
 _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_void_p])
+_lib.declare("kx_engine_set_eos", ctypes.c_int, [c_void_p, c_int32])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
 _lib.declare("kx_engine_generate", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p,
@@ -219,6 +221,10 @@ class Generator:
             st = torch.cuda.current_stream(self.device).cuda_stream
             _lib.check(_lib.lib().kx_engine_set_prefix(self._h, toks.ctypes.data if toks.size else None, toks.size, st))
 
+    def set_eos(self, eos_id: Optional[int]) -> None:
+        """Token id that ends a sequence (None: none).  Decode stops once every sequence of the batch has emitted it."""
+        _lib.check(_lib.lib().kx_engine_set_eos(self._h, -1 if eos_id is None else int(eos_id)))
+
     def generate_ids(self, tokens: np.ndarray, n_new: int, want_logits: bool = False):
         """tokens int32 [B, S] -> (ids int32 [B, n_new], logits torch fp32 [n_new, B, V] or None)."""
         import torch
@@ -246,15 +252,32 @@ class Generator:
             pass
 
 
+class PromptTooLong(RuntimeError):
+    """The prompt does not fit the engine's context.  A RuntimeError on purpose: the reference maps ValueError to 422
+    ("unsafe command", app.py:192-194) and everything else to 500 (app.py:195-197), which is where a context-length
+    error of the OpenAI client ends up too."""
+
+
 class B200Engine(Engine):
-    """``chat_model.Engine`` over a ``Generator``: prompts are byte-tokenised and padded /
-    truncated to ``prompt_len`` tokens (BASELINE configs 3-4 use exactly 256), ``max_new``
-    tokens are decoded greedily and the ids are mapped back to text."""
+    """``chat_model.Engine`` over a ``Generator``: prompts are byte-tokenised into ``prompt_len`` token slots (left-padded
+    with spaces), ``max_new`` tokens are decoded greedily -- stopping early once every sequence has produced the
+    end-of-sequence token -- and the ids are mapped back to text.
+
+    A prompt longer than ``prompt_len`` tokens is an error for that request (``PromptTooLong``; the other requests of
+    the batch are served).  ``on_overflow="truncate"`` keeps the prompt's tail instead: BASELINE configs 3-4 define their
+    synthetic prompts as "padded / truncated to exactly 256 tokens", so bench.py asks for that explicitly.
+
+    ``cancelled`` (one callable per prompt, from the batching front end): requests whose waiter is already gone when the
+    batch is formed are not prefilled at all; the engine runs a static batch, so a request cancelled after that point
+    still occupies its row until the batch ends (continuous batching is not built)."""
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
                  device: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl: Optional[NcclComm] = None,
                  prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512,
-                 parity_init: bool = False, p2p: bool = True):
+                 parity_init: bool = False, p2p: bool = True, on_overflow: str = "error", eos: bool = True):
+        if on_overflow not in ("error", "truncate"):
+            raise ValueError("on_overflow must be 'error' or 'truncate'")
+        self.on_overflow = on_overflow
         self.auto_prefix, self.max_prefix = auto_prefix, (max_prefix // 16) * 16
         self._prefix_bytes, self.prefix_sets = b"", 0
         if auto_prefix:
@@ -263,25 +286,52 @@ class B200Engine(Engine):
                              tp_rank=tp_rank, tp_size=tp_size, nccl=nccl, p2p=p2p,
                              prefill_chunk=max(32768, prefix_len),
                              embed_std=get_config(arch).parity_embed_std if parity_init else None)
+        if eos:
+            self.gen.set_eos(tokenizer.EOS)
         self.max_batch, self.prompt_len, self.max_new = max_batch, prompt_len, max_new
+        self.skipped_cancelled = 0
         if prefix_len and not auto_prefix:
             # constant instruction prefix (app.py:50-57 in the service; a system prompt in BASELINE config 5),
             # byte-tokenised and padded/truncated to a whole number of KV pages, prefilled once
             self.gen.set_prefix(np.asarray(tokenizer.encode_fixed(prefix or "", prefix_len), np.int32))
 
-    def generate(self, prompts: Sequence[str], cancelled=None) -> List[str]:
-        if self.auto_prefix:
-            toks = self._with_learned_prefix(prompts)
-        else:
-            toks = tokenizer.encode_fixed_batch(prompts, self.prompt_len)
-        ids, _ = self.gen.generate_ids(toks, self.max_new)
-        return tokenizer.decode_batch(ids)
+    def generate(self, prompts: Sequence[str], cancelled=None) -> List:
+        """Completions in the order of ``prompts``; an element is an exception instance when that request alone failed
+        (prompt too long) and ``""`` when its waiter had gone before the batch was formed."""
+        out: List = [None] * len(prompts)
+        live = []
+        for i, p in enumerate(prompts):
+            if cancelled is not None and cancelled[i] is not None and cancelled[i]():
+                out[i] = ""
+                self.skipped_cancelled += 1
+            else:
+                live.append(i)
+        if self.auto_prefix and live:
+            toks, live = self._with_learned_prefix([prompts[i] for i in live], live, out)
+        elif live:
+            room = self.prompt_len - 1                                   # one slot is the BOS token
+            if self.on_overflow == "error":
+                keep = []
+                for i in live:
+                    n = len(prompts[i].encode("utf-8"))
+                    if n > room:
+                        out[i] = PromptTooLong(f"prompt of {n + 1} tokens exceeds the engine's {self.prompt_len}-token prompt window")
+                    else:
+                        keep.append(i)
+                live = keep
+            toks = tokenizer.encode_fixed_batch([prompts[i] for i in live], self.prompt_len) if live else None
+        if live:
+            ids, _ = self.gen.generate_ids(toks, self.max_new)
+            for i, text in zip(live, tokenizer.decode_batch(ids)):
+                out[i] = text
+        return out
 
-    def _with_learned_prefix(self, prompts: Sequence[str]) -> np.ndarray:
+    def _with_learned_prefix(self, prompts: Sequence[str], index: List[int], out: List):
         """Prefix cache for the service's own template: every prompt the chain renders starts with the
         same instruction text (app.py:50-57).  The longest common byte prefix of the batch (and of the
         prefix already cached) is rounded down to whole KV pages, prefilled once, and only the remainder
-        of each prompt is prefilled per request."""
+        of each prompt is prefilled per request.  A prompt whose remainder does not fit the suffix window is
+        that request's error (or truncated, see ``on_overflow``); it does not shrink the cached prefix."""
         import os.path
         raw = [p.encode("utf-8") for p in prompts]
         common = os.path.commonprefix(raw + ([self._prefix_bytes] if self._prefix_bytes else []))
@@ -294,9 +344,20 @@ class B200Engine(Engine):
         elif not n_tok and self._prefix_bytes:
             self.gen.set_prefix(np.zeros(0, np.int32))
             self._prefix_bytes = b""
+        room = self.prompt_len if n_tok else self.prompt_len - 1
+        keep_pos, keep_idx = [], []
+        for k, (r, i) in enumerate(zip(raw, index)):
+            n = len(r) - len(want if n_tok else b"")
+            if n > room and self.on_overflow == "error":
+                out[i] = PromptTooLong(f"prompt needs {n} tokens after the cached prefix, the suffix window holds {room}")
+            else:
+                keep_pos.append(k)
+                keep_idx.append(i)
+        if not keep_idx:
+            return None, []
         if not n_tok:
-            return tokenizer.encode_fixed_batch(prompts, self.prompt_len)
-        return tokenizer.encode_suffix_batch([r[len(want):] for r in raw], self.prompt_len)
+            return tokenizer.encode_fixed_batch([prompts[k] for k in keep_pos], self.prompt_len), keep_idx
+        return tokenizer.encode_suffix_batch([raw[k][len(want):] for k in keep_pos], self.prompt_len), keep_idx
 
     def close(self):
         self.gen.close()
@@ -310,6 +371,11 @@ def default_engine_factory(arch: str) -> Engine:
     worker drives the whole box; alternatively run one uvicorn worker per GPU with its own KX_DEVICE."""
     import os
     dev0, n = int(os.environ.get("KX_DEVICE", "0")), int(os.environ.get("KX_REPLICAS", "1"))
+
+    logging.getLogger(__name__).warning(
+        "B200ChatModel serves seeded RANDOM-INIT weights of the %s architecture through a byte-level tokenizer (no checkpoint or "
+        "tokenizer vocabulary can be loaded offline): completions are noise and the reference's validator will reject them (422).",
+        arch)
 
     def make(device: int) -> Engine:
         return B200Engine(arch, prompt_len=128, auto_prefix=True, device=device)

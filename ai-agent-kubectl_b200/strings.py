@@ -31,8 +31,10 @@ copied = {"h2d": 0, "d2h": 0}
 
 
 def to_csr(strings: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
-    """list[str] -> (uint8 data[sum len], int64 off[n+1]) in UTF-8."""
-    enc = [s.encode("utf-8") for s in strings]
+    """list[str] -> (uint8 data[sum len], int64 off[n+1]) in UTF-8.  Lone surrogates (which the reference's str
+    functions accept but UTF-8 cannot carry) are encoded with 'surrogatepass': three bytes ED A0..BF xx, which the
+    kernels treat as an ordinary 3-byte character, as str.split / strip / shlex do."""
+    enc = [s.encode("utf-8", "surrogatepass") for s in strings]
     off = np.zeros(len(enc) + 1, np.int64)
     if enc:
         np.cumsum(np.fromiter((len(b) for b in enc), np.int64, len(enc)), out=off[1:])
@@ -104,7 +106,7 @@ def sanitize_queries(queries: Sequence[str], device: int = 0) -> Tuple[List[str]
     r = validate_hash_host(data, off, 0, verdict=False, san=True, device=device)
     sb = r["san"].tobytes()
     lens = r["san_len"]
-    return [sb[off[i]:off[i] + lens[i]].decode("utf-8") for i in range(len(queries))], r["hash"]
+    return [sb[off[i]:off[i] + lens[i]].decode("utf-8", "surrogatepass") for i in range(len(queries))], r["hash"]
 
 
 def parse_outputs(texts: Sequence[str], device: int = 0) -> Tuple[List[str], np.ndarray]:
@@ -112,7 +114,7 @@ def parse_outputs(texts: Sequence[str], device: int = 0) -> Tuple[List[str], np.
     data, off = to_csr(texts)
     r = validate_hash_host(data, off, FLAG_PARSE, hash=False, span=True, device=device)
     raw = data.tobytes()
-    cmds = [raw[off[i] + r["span"][i, 0]:off[i] + r["span"][i, 1]].decode("utf-8") for i in range(len(texts))]
+    cmds = [raw[off[i] + r["span"][i, 0]:off[i] + r["span"][i, 1]].decode("utf-8", "surrogatepass") for i in range(len(texts))]
     return cmds, r["verdict"]
 
 

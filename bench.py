@@ -442,7 +442,8 @@ def run_generate(args):
         prompts = gen_prompts(total, seed=1)[r0:r0 + mine]
     eng = engine.B200Engine(args.arch, seed=args.seed, max_batch=mine, prompt_len=S, max_new=NEW, device=local_rank,
                             tp_rank=tp_rank, tp_size=tp, nccl=nccl, prefix=PROMPT_PREFIX * 8, prefix_len=PFX, parity_init=True,
-                            p2p=(args.tp_allreduce == "fused"))
+                            p2p=(args.tp_allreduce == "fused"),
+                            on_overflow="truncate")      # BASELINE configs 3-4: prompts "padded / truncated to exactly 256 tokens"
     model = B200ChatModel(temperature=0, api_key=None, model=args.arch, request_timeout=600, engine=eng, max_wait_ms=50)
     parser = strings.KubectlOutputParser()
     toks = np.asarray([tokenizer.encode_fixed(p, S) for p in prompts], np.int32)

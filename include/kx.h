@@ -258,6 +258,14 @@ const char *kx_engine_trace_name(const kx_engine *e, int32_t i);
 int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32_t n, void *stream);
 
 /*
+ * kx_engine_set_eos -- end-of-sequence token id (negative: none, the default).  Decode steps of fewer than 256
+ * sequences on a single-GPU replica stop being launched once every sequence has emitted it (checked every 8 steps);
+ * the remaining positions of h_out are filled with the id.  The reference's LLM ends a completion the same way
+ * (the OpenAI service stops at its end-of-text token; app.py:117 only sees the finished text).
+ */
+int kx_engine_set_eos(kx_engine *e, int32_t eos_id);
+
+/*
  * kx_engine_generate -- prefill `batch` prompts of `prompt_len` tokens each (host int32
  * [batch, prompt_len]) and decode `n_new` tokens greedily; h_out receives int32
  * [batch, n_new].  d_logits (device fp32 [n_new, batch, vocab]) may be NULL; when given,

@@ -102,6 +102,28 @@ def test_engine_failure_surfaces_as_runtime_error_not_value_error():
     m.close()
 
 
+def test_one_failed_request_does_not_fail_its_batch():
+    """An engine may return an exception instance for one prompt (e.g. a prompt that does not fit its context): that
+    request gets a RuntimeError (-> 500, app.py:195-197), the others of the same batch their completions."""
+    m, eng = make(lambda p: OverflowError("prompt too long") if "LONG" in p else "kubectl get pods", max_wait_ms=50)
+    outs = [None, None, None]
+
+    def call(i, p):
+        try:
+            outs[i] = m.invoke(p).content
+        except BaseException as e:  # noqa: BLE001
+            outs[i] = e
+    ts = [threading.Thread(target=call, args=(i, p)) for i, p in enumerate(["a", "LONG b", "c"])]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert outs[0] == outs[2] == "kubectl get pods"
+    assert isinstance(outs[1], RuntimeError) and not isinstance(outs[1], ValueError) and "prompt too long" in str(outs[1])
+    assert max(eng.batches) >= 2                                # they really shared a batch
+    m.close()
+
+
 @pytest.mark.skipif(not ref_loader.reference_available(), reason="/root/reference only exists in the build container")
 def test_zero_diff_install_into_unmodified_app_py():
     """app.py is executed verbatim; only `langchain_openai.ChatOpenAI` is ours."""

@@ -197,14 +197,14 @@ def test_service_engine_learns_the_template_prefix():
     from kubectl_b200 import engine, tokenizer
     head = "You are a Kubernetes CLI specialist. " * 6 + "User Request: "
     prompts = [head + q + "\nKubectl Command:\n" for q in ("list pods", "show all nodes in namespace ns3", "get svc")]
-    eng = engine.B200Engine("tiny-qwen2", max_batch=4, prompt_len=48, max_new=6, auto_prefix=True, max_prefix=256)
+    eng = engine.B200Engine("tiny-qwen2", max_batch=4, prompt_len=64, max_new=6, auto_prefix=True, max_prefix=256)
     out1 = eng.generate(prompts)
     out2 = eng.generate(prompts[::-1])
     assert out2 == out1[::-1] and eng.prefix_sets == 1                   # prefix prefilled once, reused
     want = len(os.path.commonprefix([p.encode() for p in prompts]))
     n_tok = ((1 + want) // 16) * 16
-    plain = engine.Generator("tiny-qwen2", weights=eng.gen.logical, max_batch=4, max_seq=n_tok + 48 + 6)
-    toks = np.asarray([[tokenizer.BOS] + list(p.encode()[:n_tok - 1]) + tokenizer.encode_suffix(p.encode()[n_tok - 1:], 48)
+    plain = engine.Generator("tiny-qwen2", weights=eng.gen.logical, max_batch=4, max_seq=n_tok + 64 + 6)
+    toks = np.asarray([[tokenizer.BOS] + list(p.encode()[:n_tok - 1]) + tokenizer.encode_suffix(p.encode()[n_tok - 1:], 64)
                        for p in prompts], np.int32)
     ids, _ = plain.generate_ids(toks, 6)
     assert [tokenizer.decode(r) for r in ids] == out1
@@ -240,3 +240,48 @@ def test_engine_edge_shapes_and_argument_errors():
 def test_long_context_head_dim_128_decode_rounds():
     """Context longer than one shared-memory round of the decode attention kernel (head_dim 128)."""
     _check("tiny-llama-hd128", B=3, S=700, n_new=4)
+
+
+def test_decode_stops_when_every_sequence_has_emitted_eos():
+    """kx_engine_set_eos: with an embedding-dominated init and an untied head the tiny Llama counts upwards
+    (weights.py), so prompts ending in token 250 reach the end-of-sequence id 257 at generated index 6; the host
+    notices at its next check (every 8 steps), stops launching steps and fills the rest of the output with the id."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine, model_config
+    cfg = model_config.get_config("tiny-llama")
+    gen = engine.Generator("tiny-llama", seed=3, max_batch=6, max_seq=40 + 32, embed_std=2.0)
+    toks = torch.randint(0, cfg.vocab, (6, 40), generator=torch.Generator().manual_seed(4)).numpy().astype(np.int32)
+    toks[:, -1] = 250
+    full, _ = gen.generate_ids(toks, 32)
+    assert (full[:, :7] == np.arange(251, 258)[None, :]).all(), full[:, :8]
+    assert gen.last_stats.decode_steps == 31
+    gen.set_eos(257)
+    ids, _ = gen.generate_ids(toks, 32)
+    assert gen.last_stats.decode_steps == 8                         # stopped at the first check after index 6
+    assert (ids[:, :9] == full[:, :9]).all() and (ids[:, 9:] == 257).all()
+    ids2, _ = gen.generate_ids(toks, 32)                            # cached step graph: same behaviour
+    assert np.array_equal(ids, ids2) and gen.last_stats.decode_steps == 8
+    toks[0, -1] = 100                                               # one sequence that never ends keeps the batch running
+    ids3, _ = gen.generate_ids(toks, 32)
+    assert gen.last_stats.decode_steps == 31 and (ids3[1:, 6] == 257).all()
+    gen.close()
+
+
+def test_service_engine_overlong_prompt_and_cancelled_request():
+    """A prompt that does not fit is that request's error (RuntimeError -> HTTP 500 like a context-length error of the
+    OpenAI client, app.py:195-197), the rest of the batch is served; a request whose waiter is gone is not prefilled;
+    on_overflow='truncate' keeps the tail instead (what BASELINE configs 3-4 ask of their synthetic prompts)."""
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine
+    eng = engine.B200Engine("tiny-qwen2", max_batch=4, prompt_len=32, max_new=4)
+    prompts = ["list pods", "x" * 200, "get svc", "get nodes"]
+    out = eng.generate(prompts, [None, None, lambda: True, lambda: False])
+    assert isinstance(out[1], engine.PromptTooLong) and isinstance(out[1], RuntimeError) and not isinstance(out[1], ValueError)
+    assert out[2] == "" and eng.skipped_cancelled == 1
+    assert isinstance(out[0], str) and isinstance(out[3], str)
+    assert out[0] == eng.generate(["list pods"])[0]                 # batch composition does not change a completion
+    eng.close()
+    eng = engine.B200Engine("tiny-qwen2", max_batch=4, prompt_len=32, max_new=4, on_overflow="truncate")
+    out = eng.generate(prompts)
+    assert all(isinstance(o, str) for o in out)
+    eng.close()

@@ -158,3 +158,13 @@ def test_router_affinity_key_is_the_cache_key_hash(ks):
     assert where == [k % 8 for k in keys]
     assert len(set(where[3:])) > 4                                         # and distinct requests spread out
     r.close()
+
+
+def test_lone_surrogates_are_accepted_like_the_reference_does(ks):
+    """Python strings may hold lone surrogates; the reference's str functions (split, strip, hash; app.py:60-88) take
+    them.  They travel as 'surrogatepass' UTF-8 (ED A0..BF xx) and come back the same way."""
+    for s in ["list \ud800 pods", "  kubectl get \udfff\tpods ", "\ud83d kubectl get x"]:
+        assert ks.sanitize_query(s) == po.ref_sanitize_query(s)
+        assert ks.is_safe_kubectl_command(s) == (po.ref_verdict(s) == 0)
+    _, hashes = ks.sanitize_queries(["list \ud800 pods"])
+    assert int(hashes[0]) == po.spec_hash(po.ref_sanitize_query("list \ud800 pods"))
