@@ -368,8 +368,14 @@ def default_engine_factory(arch: str) -> Engine:
     The service's prompts share the template's instruction text: its KV is cached, only the rest is prefilled.
     ``KX_DEVICE`` picks the GPU (default 0); ``KX_REPLICAS=n`` starts n engines on GPUs KX_DEVICE .. KX_DEVICE+n-1
     inside this process behind a ReplicaRouter (hash affinity on the cache key), so one unmodified ``app.py``
-    worker drives the whole box; alternatively run one uvicorn worker per GPU with its own KX_DEVICE."""
+    worker drives the whole box; alternatively run one uvicorn worker per GPU with its own KX_DEVICE.
+    ``KX_ENGINE_SOCKET=/path``: the engine lives in another process (``python -m kubectl_b200.engine_server``) shared
+    by all uvicorn workers of the service; this process gets a forwarding ``RemoteEngine``."""
     import os
+    sock = os.environ.get("KX_ENGINE_SOCKET")
+    if sock:   # several uvicorn workers in front of one engine process (engine_server.py): this worker only forwards
+        from .engine_server import RemoteEngine
+        return RemoteEngine(sock)
     dev0, n = int(os.environ.get("KX_DEVICE", "0")), int(os.environ.get("KX_REPLICAS", "1"))
 
     logging.getLogger(__name__).warning(
