@@ -170,9 +170,13 @@ class BatchingFrontend:
     def submit(self, req: _Request) -> None:
         self.q.put(req)
 
-    def close(self):
+    def stop(self):
+        """Ends the consumer thread; the engine stays usable (close() also closes it)."""
         self.q.put(None)
-        self._thr.join(timeout=5)
+        self._thr.join(timeout=30)
+
+    def close(self):
+        self.stop()
         self.engine.close()
 
     @staticmethod
@@ -248,6 +252,224 @@ class BatchingFrontend:
                     self._resolve(r, exc=err)
 
 
+class SlotEngine(Engine):
+    """An engine whose ``max_batch`` sequence slots are admitted, stepped and released one by one
+    (``kx_engine_session_*``), which is what ``ContinuousFrontend`` drives.  All methods are called from the
+    front end's single thread."""
+
+    continuous = True
+    max_new = 32
+
+    def slots_open(self) -> None:
+        raise NotImplementedError
+
+    def slots_prepare(self, prompts: Sequence[str], idle: bool) -> List:
+        """Per prompt: its token row (numpy int32 [S]), an exception instance (that request fails), or ``None``
+        (cannot join the running sequences -- e.g. it does not share their cached prefix -- ask again once idle)."""
+        raise NotImplementedError
+
+    def slots_admit(self, slot0: int, rows) -> None:
+        raise NotImplementedError
+
+    def slots_step(self, n_steps: int, n_slots: int) -> None:
+        raise NotImplementedError
+
+    def slots_poll(self):
+        """(tokens produced per slot, finished flag per slot) after the enqueued steps."""
+        raise NotImplementedError
+
+    def slots_read(self, slot0: int, counts: Sequence[int]) -> List[str]:
+        """Completions of slots slot0 .. slot0+len(counts)-1, which have produced counts[j] tokens."""
+        raise NotImplementedError
+
+    def slots_release(self, slot0: int, n: int) -> None:
+        raise NotImplementedError
+
+
+def _runs(slots: Sequence[int]):
+    """Sorted slot numbers -> [(first, count)] of consecutive runs."""
+    out = []
+    for s in sorted(slots):
+        if out and out[-1][0] + out[-1][1] == s:
+            out[-1][1] += 1
+        else:
+            out.append([s, 1])
+    return [(a, n) for a, n in out]
+
+
+class ContinuousFrontend(BatchingFrontend):
+    """Continuous batching: requests join the running sequences at the next step boundary instead of waiting for a
+    static batch to end, a finished request is answered (and its slot reused) as soon as its own sequence ends, and a
+    request whose waiter has gone (``asyncio.wait_for`` timed out, app.py:183-191) gives its slot back mid-sequence.
+
+    One loop iteration = take what arrived -> drop what was cancelled -> admit into free slots (one prefill per run of
+    consecutive slots) -> ``steps_per_poll`` decode steps for every live slot -> answer the slots that ended.
+    Identical prompts share one slot, also with a sequence that is already running (single flight)."""
+
+    def __init__(self, engine: SlotEngine, max_wait_ms: float = 2.0, steps_per_poll: int = 4):
+        self.steps_per_poll = max(1, int(steps_per_poll))
+        self.cancelled_in_flight = 0
+        self.admissions = 0
+        self.ttft: List[float] = []          # seconds from submit to the first token, last 4096 requests
+        self.latency: List[float] = []       # seconds from submit to the answer
+        super().__init__(engine, max_wait_ms=max_wait_ms)
+
+    def _note(self, series: List[float], value: float):
+        series.append(value)
+        if len(series) > 4096:
+            del series[:2048]
+
+    def _run(self):
+        eng = self.engine
+        n_slots_max = eng.max_batch
+        free = set(range(n_slots_max))
+        groups = {}                          # slot -> requests waiting for that sequence
+        prompt_of, slot_of = {}, {}          # slot -> prompt, prompt -> slot
+        waiting: List[_Request] = []
+        opened = False
+        closing = False
+
+        def fail_all(err):
+            for r in waiting:
+                self._resolve(r, exc=err)
+            for g in groups.values():
+                for r in g:
+                    self._resolve(r, exc=err)
+
+        def free_slot(slot):
+            slot_of.pop(prompt_of.pop(slot), None)
+            groups.pop(slot, None)
+            free.add(slot)
+
+        while True:
+            # ---- 1. intake: block only when there is nothing to do ----
+            if not groups and not waiting:
+                if closing:
+                    return
+                first = self.q.get()
+                if first is None:
+                    return
+                waiting.append(first)
+                t_end = time.monotonic() + self.max_wait        # idle: let a burst form one prefill
+                while len(waiting) < n_slots_max:
+                    try:
+                        nxt = self.q.get(timeout=max(0.0, t_end - time.monotonic()))
+                    except queue.Empty:
+                        break
+                    if nxt is None:
+                        closing = True
+                        break
+                    waiting.append(nxt)
+            else:
+                while True:
+                    try:
+                        nxt = self.q.get_nowait()
+                    except queue.Empty:
+                        break
+                    if nxt is None:
+                        closing = True
+                        break
+                    waiting.append(nxt)
+            try:
+                if not opened:
+                    eng.slots_open()
+                    opened = True
+                # ---- 2. requests nobody waits for any more ----
+                keep = []
+                for r in waiting:
+                    if r.cancelled():
+                        self.dropped += 1
+                        self._resolve(r, exc=TimeoutError("request cancelled before it was scheduled"))
+                    else:
+                        keep.append(r)
+                waiting = keep
+                gone = [s for s, g in groups.items() if all(r.cancelled() for r in g)]
+                for a, n in _runs(gone):
+                    eng.slots_release(a, n)
+                for s in gone:
+                    for r in groups[s]:
+                        self._resolve(r, exc=TimeoutError("request cancelled while it was decoding"))
+                    self.cancelled_in_flight += 1
+                    free_slot(s)
+                # ---- 3. admission ----
+                if waiting and free:
+                    idle = not groups
+                    take, index, rest = [], {}, []
+                    for r in waiting:
+                        if r.prompt in slot_of:                 # the same prompt is already decoding: wait for that one
+                            groups[slot_of[r.prompt]].append(r)
+                            self.coalesced += 1
+                        elif r.prompt in index:
+                            take[index[r.prompt]].append(r)
+                        elif len(take) < len(free):
+                            index[r.prompt] = len(take)
+                            take.append([r])
+                        else:
+                            rest.append(r)
+                    rows = eng.slots_prepare([g[0].prompt for g in take], idle) if take else []
+                    ready, held = [], []
+                    for g, row in zip(take, rows):
+                        if isinstance(row, BaseException):
+                            err = row if isinstance(row, RuntimeError) else RuntimeError(f"{type(row).__name__}: {row}")
+                            for r in g:
+                                self._resolve(r, exc=err)
+                        elif row is None:
+                            held.extend(g)
+                        else:
+                            ready.append((g, row))
+                    # a held request needs the engine idle: nothing new is admitted ahead of it, the live slots drain
+                    waiting = held + rest
+                    if ready and not (held and not idle):
+                        slots = sorted(free)[:len(ready)]
+                        k = 0
+                        for a, n in _runs(slots):
+                            eng.slots_admit(a, [row for _, row in ready[k:k + n]])
+                            self.admissions += 1
+                            now = time.monotonic()
+                            for j in range(n):
+                                g = ready[k + j][0]
+                                self.coalesced += len(g) - 1
+                                groups[a + j] = g
+                                prompt_of[a + j] = g[0].prompt
+                                slot_of[g[0].prompt] = a + j
+                                free.discard(a + j)
+                                for r in g:
+                                    self._note(self.ttft, now - r.t_enqueue)
+                            k += n
+                    elif ready:
+                        waiting = [r for g, _ in ready for r in g] + waiting
+                # ---- 4. decode steps for every live slot, answer the ones that ended ----
+                if groups:
+                    eng.slots_step(self.steps_per_poll, max(groups) + 1)
+                    cnt, fin = eng.slots_poll()
+                    ended = [s for s in groups if fin[s]]
+                    for a, n in _runs(ended):
+                        texts = eng.slots_read(a, [int(c) for c in cnt[a:a + n]])
+                        eng.slots_release(a, n)
+                        now = time.monotonic()
+                        for j in range(n):
+                            for r in groups[a + j]:
+                                self._note(self.latency, now - r.t_enqueue)
+                                self._resolve(r, result=texts[j])
+                            free_slot(a + j)
+            except BaseException as e:  # noqa: BLE001 - the engine failed: every waiter gets a 500, the session starts over
+                err = e if isinstance(e, RuntimeError) else RuntimeError(f"{type(e).__name__}: {e}")
+                logger.exception("continuous batching loop failed")
+                fail_all(err)
+                waiting, groups, prompt_of, slot_of = [], {}, {}, {}
+                free = set(range(n_slots_max))
+                opened = False
+            if closing and not groups and not waiting:
+                return
+
+
+def make_frontend(engine: Engine, max_wait_ms: float = 2.0) -> BatchingFrontend:
+    """Continuous batching when the engine has slots, static batches otherwise."""
+    if getattr(engine, "continuous", False):
+        return ContinuousFrontend(engine, max_wait_ms=max_wait_ms)
+    return BatchingFrontend(engine, max_wait_ms=max_wait_ms)
+
+
 #: names the ``model`` kwarg / OPENAI_MODEL may carry -> architecture key
 ARCH_ALIASES = {
     "qwen2.5-0.5b": "qwen2.5-0.5b", "qwen/qwen2.5-0.5b": "qwen2.5-0.5b", "qwen2.5-0.5b-instruct": "qwen2.5-0.5b",
@@ -287,7 +509,7 @@ class B200ChatModel(_LCRunnable):
                 engine_factory = default_engine_factory
             engine = engine_factory(self.arch)
         self.engine = engine
-        self.frontend = BatchingFrontend(engine, max_wait_ms=max_wait_ms)
+        self.frontend = make_frontend(engine, max_wait_ms=max_wait_ms)
 
     # ---- Runnable protocol -------------------------------------------------
     def __or__(self, other):

@@ -78,6 +78,12 @@ struct kx_engine {
     // cost about a millisecond of idle GPU per call otherwise); dropped whenever buffers they point to may change
     struct StepGraph { int B, S, n_new, P; cudaGraphExec_t exec; int64_t launches; };
     std::vector<StepGraph> step_graphs;
+    // continuous batching (kx_engine_session_*): per-slot state, device int [max_batch] each -- tokens produced (< 0: the
+    // slot is free), how many it may produce, ended; copies of the live positions / last tokens across an admission's
+    // prefill (which overwrites e->pos, e->seq and e->next_tok); the identity sequence map of a decode step
+    int *s_cnt = nullptr, *s_limit = nullptr, *s_fin = nullptr, *s_pos = nullptr, *s_tok = nullptr, *s_seq = nullptr;
+    bool s_open = false, s_need_input = false;     // ... the deferred-norm path's step input has to be rebuilt
+    int s_live = 0;                                // slots admitted and not yet released
     int64_t device_bytes = 0;
     std::vector<void *> owned;
     TraceCtx *trace = nullptr;                     // KX_TRACE=1: per-launch timeline of the last decode step
@@ -377,8 +383,9 @@ int greedy_pick(kx_engine *e, int B, cudaStream_t st) {
 
 // final norm over `rows` (row_map selects which residual rows), lm_head, argmax, store
 // deferred: e->xn already holds bf16(residual * g_final) and e->ssq its sums of squares (decode on the fused-norm path);
-// the caller's tail kernel then stores the token instead of store_token_kernel
-int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st, bool deferred = false) {
+// the caller's tail kernel then stores the token instead of store_token_kernel (store = false: so it does on the classic path)
+int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_logits_step, cudaStream_t st, bool deferred = false,
+                 bool store = true) {
     const kx_model_desc &d = e->d;
     if (!deferred) KX_TRY(norm_rows(e, e->norm, B, row_map, st));
     const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden, "lm_head"};
@@ -403,7 +410,7 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
             KX_REQUIRE(rc == 0, KX_ECUDA, "engine: ncclAllGather failed with %d", rc);
             KX_TRY(op_pick(e->tp_gathered, d.tp_size, B, e->next_tok, st));
         }
-        if (deferred) return KX_OK;                    // argmax is unchanged by the positive per-token factor 1 / rms
+        if (deferred || !store) return KX_OK;          // argmax is unchanged by the positive per-token factor 1 / rms
         store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
         count_launch();
         KX_CUDA(cudaGetLastError());
@@ -421,10 +428,49 @@ int head_forward(kx_engine *e, int B, const int *row_map, int n_new, float *d_lo
     if (d_logits_step)
         KX_CUDA(cudaMemcpyAsync(d_logits_step, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
     KX_TRY(greedy_pick(e, B, st));
-    if (deferred) return KX_OK;
+    if (deferred || !store) return KX_OK;
     store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
     count_launch();
     KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+// Prefill of B whole sequences of S tokens each (host int32 [B, S]) into the KV pages of sequences slot0 .. slot0 + B - 1,
+// in chunks of at most prefill_chunk tokens; leaves the logits of every sequence's last prompt row in
+// e->logits[slot0 + b].  Overwrites the per-token buffers (tokens, pos, seq, activations).
+int prefill_sequences(kx_engine *e, const int32_t *h_tokens, int slot0, int B, int S, cudaStream_t st, int64_t *h2d) {
+    const kx_model_desc &d = e->d;
+    const int P = e->prefix_len;
+    int seqs_per_chunk = d.prefill_chunk / S;
+    if (seqs_per_chunk < 1) seqs_per_chunk = 1;
+    KX_REQUIRE((int64_t)seqs_per_chunk * S <= e->max_tokens || S <= e->max_tokens, KX_ETOOBIG, "kx_engine_generate: prompt too long");
+    if ((int64_t)seqs_per_chunk * S > e->max_tokens) seqs_per_chunk = e->max_tokens / S;
+    std::vector<int> hpos, hseq;
+    for (int b0 = 0; b0 < B; b0 += seqs_per_chunk) {
+        const int nb = (B - b0 < seqs_per_chunk) ? B - b0 : seqs_per_chunk;
+        const int M = nb * S;
+        hpos.resize(M); hseq.resize(M);
+        for (int b = 0; b < nb; ++b)
+            for (int t = 0; t < S; ++t) { hpos[b * S + t] = P + t; hseq[b * S + t] = slot0 + b0 + b; }
+        KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens + (size_t)b0 * S, (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
+        *h2d += (int64_t)3 * M * 4;
+        KX_CUDA(cudaStreamSynchronize(st));          // hpos/hseq are reused by the next chunk
+        KX_TRY(op_embed(e->tokens, e->embed, e->resid, M, d.hidden, st));
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, slot0 + b0, 0, st, P));
+        // first token of this chunk's sequences: final norm on each last prompt row
+        std::vector<int> rows(nb);
+        for (int b = 0; b < nb; ++b) rows[b] = b * S + S - 1;
+        KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        *h2d += (int64_t)nb * 4;
+        KX_CUDA(cudaStreamSynchronize(st));
+        {
+            const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
+            KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, nb, d.hidden, d.eps, e->last_rows, st));
+            KX_TRY(linear(e, head, nb, EPI_F32, e->logits + (size_t)(slot0 + b0) * d.vocab, d.vocab, nullptr, st));
+        }
+    }
     return KX_OK;
 }
 
@@ -610,6 +656,8 @@ extern "C" int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32
     KX_REQUIRE(n >= 0 && n % KX_KV_PAGE == 0, KX_EINVAL, "kx_engine_set_prefix: length %d is not a multiple of %d", n, KX_KV_PAGE);
     KX_REQUIRE(n < d.max_seq && n <= e->max_tokens, KX_ETOOBIG, "kx_engine_set_prefix: prefix of %d tokens is too long", n);
     KX_REQUIRE(n == 0 || h_tokens, KX_EINVAL, "kx_engine_set_prefix: NULL tokens");
+    KX_REQUIRE(e->s_live == 0, KX_EINVAL, "kx_engine_set_prefix: %d session slots are live and attend to the current prefix", e->s_live);
+    e->s_open = false;                               // free slots park behind the prefix: sessions start over
     drop_step_graphs(e);
     cudaStream_t st = e->stream;
     cudaEvent_t ev;
@@ -689,6 +737,8 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     KX_CUDA(cudaSetDevice(e->device));               // a host thread serving several engines may have another device current
     const kx_model_desc &d = e->d;
     KX_REQUIRE(B >= 1 && B <= d.max_batch, KX_ETOOBIG, "kx_engine_generate: batch %d exceeds max_batch %d", B, d.max_batch);
+    KX_REQUIRE(e->s_live == 0, KX_EINVAL, "kx_engine_generate: %d session slots are live (kx_engine_session_release)", e->s_live);
+    e->s_open = false;                               // a static batch overwrites the slots' state: sessions start over
     const int P = e->prefix_len;
     KX_REQUIRE(S >= 1 && n_new >= 1 && P + S + n_new <= d.max_seq, KX_ETOOBIG,
                "kx_engine_generate: %d cached + %d prompt + %d new tokens exceed max_seq %d", P, S, n_new, d.max_seq);
@@ -704,37 +754,7 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     KX_CUDA(cudaMemsetAsync(e->step, 0, 4, st));
     KX_CUDA(cudaEventRecord(ev0, st));
 
-    // ---- prefill, whole sequences per chunk ----
-    int seqs_per_chunk = d.prefill_chunk / S;
-    if (seqs_per_chunk < 1) seqs_per_chunk = 1;
-    KX_REQUIRE((int64_t)seqs_per_chunk * S <= e->max_tokens || S <= e->max_tokens, KX_ETOOBIG, "kx_engine_generate: prompt too long");
-    if ((int64_t)seqs_per_chunk * S > e->max_tokens) seqs_per_chunk = e->max_tokens / S;
-    std::vector<int> hpos, hseq;
-    for (int b0 = 0; b0 < B; b0 += seqs_per_chunk) {
-        const int nb = (B - b0 < seqs_per_chunk) ? B - b0 : seqs_per_chunk;
-        const int M = nb * S;
-        hpos.resize(M); hseq.resize(M);
-        for (int b = 0; b < nb; ++b)
-            for (int t = 0; t < S; ++t) { hpos[b * S + t] = P + t; hseq[b * S + t] = b0 + b; }
-        KX_CUDA(cudaMemcpyAsync(e->tokens, h_tokens + (size_t)b0 * S, (size_t)M * 4, cudaMemcpyHostToDevice, st));
-        KX_CUDA(cudaMemcpyAsync(e->pos, hpos.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
-        KX_CUDA(cudaMemcpyAsync(e->seq, hseq.data(), (size_t)M * 4, cudaMemcpyHostToDevice, st));
-        h2d += (int64_t)3 * M * 4;
-        KX_CUDA(cudaStreamSynchronize(st));          // hpos/hseq are reused by the next chunk
-        KX_TRY(op_embed(e->tokens, e->embed, e->resid, M, d.hidden, st));
-        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, M, false, nb, S, b0, 0, st, P));
-        // first token of this chunk's sequences: final norm on each last prompt row
-        std::vector<int> rows(nb);
-        for (int b = 0; b < nb; ++b) rows[b] = b * S + S - 1;
-        KX_CUDA(cudaMemcpyAsync(e->last_rows, rows.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
-        h2d += (int64_t)nb * 4;
-        KX_CUDA(cudaStreamSynchronize(st));
-        {
-            const Linear head{&e->lm_head_map, e->lm_head_h, &e->xn_a, e->xn_b, d.vocab, d.hidden};
-            KX_TRY(op_rmsnorm(e->resid, e->norm, e->xn, nb, d.hidden, d.eps, e->last_rows, st));
-            KX_TRY(linear(e, head, nb, EPI_F32, e->logits + (size_t)b0 * d.vocab, d.vocab, nullptr, st));
-        }
-    }
+    KX_TRY(prefill_sequences(e, h_tokens, 0, B, S, st, &h2d));
     if (d_logits) KX_CUDA(cudaMemcpyAsync(d_logits, e->logits, sizeof(float) * (size_t)B * d.vocab, cudaMemcpyDeviceToDevice, st));
     KX_TRY(greedy_pick(e, B, st));
     store_token_kernel<<<(B + 127) / 128, 128, 0, st>>>(e->next_tok, e->out_ids, e->step, B, n_new);
@@ -848,3 +868,188 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
     cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
     return KX_OK;
 }
+
+// --------------------------------------------------------------------------- //
+// Continuous batching.  The reference serves requests as they arrive, each one awaiting its own completion
+// (app.py:183-186), and cancels the one whose deadline passes (app.py:189-191).  A static batch makes a request that
+// arrives mid-batch wait for every remaining step of that batch; here the engine's max_batch sequence SLOTS are
+// admitted, stepped and released independently, so the host scheduler (engine.py) can admit at any step boundary
+// and free a cancelled or finished request's slot (its KV pages with it) at the next one.
+//
+// State per slot lives on the device (s_cnt / s_limit / s_fin, e->pos, e->next_tok); a decode step is the same launch
+// sequence as kx_engine_generate's with session_tail_kernel keeping the books, replayed as a CUDA graph per batch
+// bucket.  Single-GPU replicas only (a tensor-parallel pair would have to take the same decisions on both ranks).
+// --------------------------------------------------------------------------- //
+namespace {
+
+int session_bucket(const kx_engine *e, int n_slots) {   // decode batch for slots [0, n_slots): whole 32-column tiles
+    int B = ((n_slots < 1 ? 1 : n_slots) + 31) / 32 * 32;
+    return B > e->d.max_batch ? e->d.max_batch : B;
+}
+
+int session_step_once(kx_engine *e, int B, cudaStream_t st) {
+    const kx_model_desc &d = e->d;
+    if (fused_norm_decode(e, B)) {
+        for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward_fused(e, li, B, d.max_seq, st));
+        KX_TRY(head_forward(e, B, nullptr, 0, nullptr, st, true));
+        return op_session_tail(e->next_tok, e->out_ids, d.max_seq, e->pos, e->s_cnt, e->s_limit, e->s_fin, e->eos_id, 1, e->embed,
+                               e->layers[0].w.ln1, e->resid, e->xn, e->ssq, d.max_batch, B, d.hidden, st);
+    }
+    KX_TRY(op_embed(e->next_tok, e->embed, e->resid, B, d.hidden, st));
+    for (int li = 0; li < d.layers; ++li) KX_TRY(layer_forward(e, li, B, true, B, 1, 0, d.max_seq, st));
+    KX_TRY(head_forward(e, B, nullptr, 0, nullptr, st, false, false));
+    return op_session_tail(e->next_tok, e->out_ids, d.max_seq, e->pos, e->s_cnt, e->s_limit, e->s_fin, e->eos_id, 1, nullptr, nullptr,
+                           nullptr, nullptr, nullptr, 0, B, d.hidden, st);
+}
+
+}  // namespace
+
+extern "C" int kx_engine_session_open(kx_engine *e) {
+    KX_REQUIRE(e, KX_EINVAL, "kx_engine_session_open: NULL argument");
+    KX_REQUIRE(e->d.tp_size <= 1, KX_EINVAL, "kx_engine_session_open: continuous batching runs on single-GPU replicas only");
+    KX_CUDA(cudaSetDevice(e->device));
+    const kx_model_desc &d = e->d;
+    const size_t n = (size_t)d.max_batch;
+    if (!e->s_cnt) {
+        int *base = nullptr;
+        KX_TRY(dev_alloc(e, (void **)&base, 6 * n * sizeof(int)));
+        e->s_cnt = base; e->s_limit = base + n; e->s_fin = base + 2 * n; e->s_pos = base + 3 * n; e->s_tok = base + 4 * n;
+        e->s_seq = base + 5 * n;
+        std::vector<int> ident(n);
+        for (size_t b = 0; b < n; ++b) ident[b] = (int)b;
+        KX_CUDA(cudaMemcpy(e->s_seq, ident.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    }
+    cudaStream_t st = e->stream;
+    KX_CUDA(cudaMemsetAsync(e->next_tok, 0, n * sizeof(int), st));
+    KX_CUDA(cudaMemsetAsync(e->s_limit, 0, n * sizeof(int), st));
+    KX_CUDA(cudaMemcpyAsync(e->seq, e->s_seq, n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    KX_TRY(op_session_release(e->pos, e->s_cnt, e->s_fin, 0, d.max_batch, e->prefix_len, st));
+    KX_CUDA(cudaStreamSynchronize(st));
+    e->s_open = true; e->s_need_input = true; e->s_live = 0;
+    return KX_OK;
+}
+
+extern "C" int kx_engine_session_admit(kx_engine *e, int32_t slot0, int32_t n, const int32_t *h_tokens, int32_t S, int32_t max_new,
+                                       kx_gen_stats *stats) {
+    KX_REQUIRE(e && h_tokens, KX_EINVAL, "kx_engine_session_admit: NULL argument");
+    KX_REQUIRE(e->s_open, KX_EINVAL, "kx_engine_session_admit: no open session (kx_engine_session_open)");
+    KX_CUDA(cudaSetDevice(e->device));
+    const kx_model_desc &d = e->d;
+    const int P = e->prefix_len;
+    KX_REQUIRE(slot0 >= 0 && n >= 1 && slot0 + n <= d.max_batch, KX_ETOOBIG, "kx_engine_session_admit: slots %d .. %d outside 0 .. %d",
+               slot0, slot0 + n - 1, d.max_batch - 1);
+    KX_REQUIRE(S >= 1 && max_new >= 1 && P + S + max_new <= d.max_seq, KX_ETOOBIG,
+               "kx_engine_session_admit: %d cached + %d prompt + %d new tokens exceed max_seq %d", P, S, max_new, d.max_seq);
+    cudaStream_t st = e->stream;
+    const int64_t launches0 = kx_launch_count();
+    const size_t nb = sizeof(int) * (size_t)d.max_batch;
+    int64_t h2d = 0;
+    cudaEvent_t ev0, ev1;
+    KX_CUDA(cudaEventCreate(&ev0)); KX_CUDA(cudaEventCreate(&ev1));
+    KX_CUDA(cudaEventRecord(ev0, st));
+    // the prefill uses pos / seq / next_tok as per-token scratch: the live slots' values wait in s_pos / s_tok
+    KX_CUDA(cudaMemcpyAsync(e->s_pos, e->pos, nb, cudaMemcpyDeviceToDevice, st));
+    KX_CUDA(cudaMemcpyAsync(e->s_tok, e->next_tok, nb, cudaMemcpyDeviceToDevice, st));
+    int rc = prefill_sequences(e, h_tokens, slot0, n, S, st, &h2d);
+    if (rc == KX_OK) rc = op_argmax(e->logits + (size_t)slot0 * d.vocab, n, d.vocab, d.vocab, e->s_tok + slot0, nullptr, st);
+    if (rc == KX_OK)
+        rc = op_session_admit(e->s_tok, e->out_ids, d.max_seq, e->s_pos, e->s_cnt, e->s_limit, e->s_fin, slot0, n, P + S, max_new,
+                              e->eos_id, st);
+    // (also after a failure: the live slots get their state back)
+    cudaMemcpyAsync(e->pos, e->s_pos, nb, cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(e->next_tok, e->s_tok, nb, cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(e->seq, e->s_seq, nb, cudaMemcpyDeviceToDevice, st);
+    cudaEventRecord(ev1, st);
+    const cudaError_t ce = cudaStreamSynchronize(st);
+    e->s_need_input = true;
+    if (rc == KX_OK && ce == cudaSuccess) e->s_live += n;
+    if (stats && rc == KX_OK && ce == cudaSuccess) {
+        cudaEventElapsedTime(&stats->prefill_ms, ev0, ev1);
+        stats->decode_ms = 0.f; stats->decode_steps = 0;
+        stats->launches = (int32_t)(kx_launch_count() - launches0);
+        stats->h2d_bytes = h2d; stats->d2h_bytes = 0;
+    }
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    if (rc != KX_OK) return rc;
+    KX_CUDA(ce);
+    return KX_OK;
+}
+
+extern "C" int kx_engine_session_step(kx_engine *e, int32_t n_steps, int32_t n_slots) {
+    KX_REQUIRE(e && e->s_open, KX_EINVAL, "kx_engine_session_step: no open session");
+    KX_REQUIRE(n_steps >= 1 && n_slots >= 1 && n_slots <= e->d.max_batch, KX_EINVAL, "kx_engine_session_step: bad argument");
+    KX_CUDA(cudaSetDevice(e->device));
+    const kx_model_desc &d = e->d;
+    cudaStream_t st = e->stream;
+    const int B = session_bucket(e, n_slots), P = e->prefix_len;
+    if (fused_norm_decode(e, B) && e->s_need_input)     // an admission (or a wider bucket) left no step input behind
+        KX_TRY(op_session_tail(e->next_tok, e->out_ids, d.max_seq, e->pos, e->s_cnt, e->s_limit, e->s_fin, e->eos_id, 0, e->embed,
+                               e->layers[0].w.ln1, e->resid, e->xn, e->ssq, d.max_batch, d.max_batch, d.hidden, st));
+    e->s_need_input = !fused_norm_decode(e, B);         // the classic path leaves none either
+    kx_engine::StepGraph *hit = nullptr;
+    for (auto &g : e->step_graphs)
+        if (g.B == B && g.S == -1 && g.n_new == -1 && g.P == P) hit = &g;
+    int t = 0;
+    if (!hit) {
+        KX_TRY(session_step_once(e, B, st));               // eager: also sets kernel attributes outside any capture
+        t = 1;
+        if (n_steps > 1) {
+            cudaGraph_t graph = nullptr;
+            cudaGraphExec_t exec = nullptr;
+            const int64_t l0 = kx_launch_count();
+            KX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            const int rc = session_step_once(e, B, st);
+            const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (rc != KX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+            KX_CUDA(ce);
+            const int64_t per_step = kx_launch_count() - l0;
+            KX_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+            cudaGraphDestroy(graph);
+            count_launch(-(int)per_step);                  // the capture launched nothing
+            if (e->step_graphs.size() >= 8) {
+                cudaGraphExecDestroy(e->step_graphs.front().exec);
+                e->step_graphs.erase(e->step_graphs.begin());
+            }
+            e->step_graphs.push_back({B, -1, -1, P, exec, per_step});
+            hit = &e->step_graphs.back();
+        }
+    }
+    for (; t < n_steps; ++t) {
+        KX_CUDA(cudaGraphLaunch(hit->exec, st));
+        count_launch((int)hit->launches);
+    }
+    return KX_OK;
+}
+
+extern "C" int kx_engine_session_poll(kx_engine *e, int32_t *h_count, int32_t *h_finished) {
+    KX_REQUIRE(e && e->s_open && h_count && h_finished, KX_EINVAL, "kx_engine_session_poll: no open session or NULL argument");
+    KX_CUDA(cudaSetDevice(e->device));
+    const size_t nb = sizeof(int) * (size_t)e->d.max_batch;
+    KX_CUDA(cudaMemcpyAsync(h_count, e->s_cnt, nb, cudaMemcpyDeviceToHost, e->stream));
+    KX_CUDA(cudaMemcpyAsync(h_finished, e->s_fin, nb, cudaMemcpyDeviceToHost, e->stream));
+    KX_CUDA(cudaStreamSynchronize(e->stream));
+    return KX_OK;
+}
+
+extern "C" int kx_engine_session_read(kx_engine *e, int32_t slot0, int32_t n_slots, int32_t *h_out, int32_t n) {
+    KX_REQUIRE(e && e->s_open && h_out, KX_EINVAL, "kx_engine_session_read: no open session or NULL argument");
+    KX_REQUIRE(slot0 >= 0 && n_slots >= 1 && slot0 + n_slots <= e->d.max_batch && n >= 1 && n <= e->d.max_seq, KX_EINVAL,
+               "kx_engine_session_read: bad slots or count");
+    KX_CUDA(cudaSetDevice(e->device));
+    KX_CUDA(cudaMemcpy2DAsync(h_out, sizeof(int) * (size_t)n, e->out_ids + (size_t)slot0 * e->d.max_seq, sizeof(int) * (size_t)e->d.max_seq,
+                              sizeof(int) * (size_t)n, (size_t)n_slots, cudaMemcpyDeviceToHost, e->stream));
+    KX_CUDA(cudaStreamSynchronize(e->stream));
+    return KX_OK;
+}
+
+extern "C" int kx_engine_session_release(kx_engine *e, int32_t slot0, int32_t n) {
+    KX_REQUIRE(e && e->s_open, KX_EINVAL, "kx_engine_session_release: no open session");
+    KX_REQUIRE(slot0 >= 0 && n >= 1 && slot0 + n <= e->d.max_batch, KX_EINVAL, "kx_engine_session_release: bad slots");
+    KX_CUDA(cudaSetDevice(e->device));
+    KX_TRY(op_session_release(e->pos, e->s_cnt, e->s_fin, slot0, n, e->prefix_len, e->stream));
+    e->s_live -= n;
+    if (e->s_live < 0) e->s_live = 0;
+    return KX_OK;
+}
+
+extern "C" int32_t kx_engine_session_live(const kx_engine *e) { return (e && e->s_open) ? e->s_live : 0; }

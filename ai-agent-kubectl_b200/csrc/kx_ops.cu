@@ -925,31 +925,49 @@ argmax_kernel(const float *__restrict__ logits, int V, int ld, int *__restrict__
 }
 
 // ---- second stage of the fused lm_head argmax: parts[n_parts][ld] (value bits, index) -> one id per token ----
-// block = 32 tokens x 32 part groups; ties -> lowest index (what torch.argmax over the full row returns)
+// block = 8 tokens x 128 part groups (a 64-byte run of one part row per 8 lanes), so batch 64 already spreads over 8 SMs and
+// a thread walks n_parts / 128 parts with four loads in flight; ties -> lowest index (what torch.argmax over the full
+// row returns).  (32 tokens x 32 groups per block left batch 64 on two SMs with 125 dependent steps per thread: 55 us.)
+__device__ __forceinline__ void argmax_take(float &best, int &bi, float f, int i) {
+    if (f > best || (f == best && i < bi)) { best = f; bi = i; }
+}
 __global__ void __launch_bounds__(1024)
 argmax_parts_kernel(const int2 *__restrict__ parts, int n_parts, int ld, int B, int id_offset, int *__restrict__ out,
                     int *__restrict__ out2, int2 *__restrict__ out_pairs) {
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int b = blockIdx.x * 32 + tx;
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;      // token within the block, part group 0..127
+    const int b = blockIdx.x * 8 + tx;
     float best = -INFINITY;
     int bi = 0x7fffffff;
     if (b < B) {
-        for (int pi = ty; pi < n_parts; pi += 32) {
+        int pi = ty;
+        for (; pi + 384 < n_parts; pi += 512) {
+            const int2 v0 = parts[(size_t)pi * ld + b], v1 = parts[(size_t)(pi + 128) * ld + b];
+            const int2 v2 = parts[(size_t)(pi + 256) * ld + b], v3 = parts[(size_t)(pi + 384) * ld + b];
+            argmax_take(best, bi, __int_as_float(v0.x), v0.y); argmax_take(best, bi, __int_as_float(v1.x), v1.y);
+            argmax_take(best, bi, __int_as_float(v2.x), v2.y); argmax_take(best, bi, __int_as_float(v3.x), v3.y);
+        }
+        for (; pi < n_parts; pi += 128) {
             const int2 v = parts[(size_t)pi * ld + b];
-            const float f = __int_as_float(v.x);
-            if (f > best || (f == best && v.y < bi)) { best = f; bi = v.y; }
+            argmax_take(best, bi, __int_as_float(v.x), v.y);
         }
     }
-    __shared__ float sv[32][33];
-    __shared__ int si[32][33];
-    sv[ty][tx] = best; si[ty][tx] = bi;
+    // the four part groups of a warp (lanes tx, tx + 8, tx + 16, tx + 24), then the 32 warps through shared memory
+#pragma unroll
+    for (int d = 8; d < 32; d <<= 1) {
+        const float f = __shfl_xor_sync(0xffffffffu, best, d);
+        const int i = __shfl_xor_sync(0xffffffffu, bi, d);
+        argmax_take(best, bi, f, i);
+    }
+    __shared__ float sv[32][8];
+    __shared__ int si[32][8];
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) < 8) { sv[warp][tx] = best; si[warp][tx] = bi; }
     __syncthreads();
-    if (ty == 0 && b < B) {
-        for (int g = 1; g < 32; ++g) {
-            const float f = sv[g][tx];
-            const int i = si[g][tx];
-            if (f > best || (f == best && i < bi)) { best = f; bi = i; }
-        }
+    if (threadIdx.x < 8 && b < B) {
+        best = sv[0][tx]; bi = si[0][tx];
+        for (int g = 1; g < 32; ++g) argmax_take(best, bi, sv[g][tx], si[g][tx]);
         if (out_pairs) out_pairs[b] = make_int2(__float_as_int(best), bi + id_offset);
         else { out[b] = bi + id_offset; if (out2) out2[b] = bi + id_offset; }
     }
@@ -1038,6 +1056,67 @@ decode_tail_kernel(const int *__restrict__ next_tok, int *__restrict__ out_ids, 
         if (tid == 0) ssq[(size_t)(f0 >> 7) * ssq_ld + b] = (ws[0] + ws[1]) + (ws[2] + ws[3]);
         __syncthreads();
     }
+}
+
+// Continuous batching (kx_engine_session_*): what decode_tail_kernel does, with the bookkeeping per SLOT instead of per
+// batch.  cnt[b] = tokens the slot has produced (< 0: the slot is free), limit[b] = how many it may produce, fin[b] = it
+// has ended (eos or limit).  A free or finished slot keeps its position: it re-decodes one harmless position of its own
+// pages until the host reuses it.  book = 0: only prepare the step's input (after an admission overwrote the buffers);
+// table = NULL: only the bookkeeping (the classic decode path embeds at the start of its step).
+__global__ void __launch_bounds__(128)
+session_tail_kernel(const int *__restrict__ next_tok, int *__restrict__ out, int out_ld, int *__restrict__ pos, int *__restrict__ cnt,
+                    const int *__restrict__ limit, int *__restrict__ fin, int eos_id, int book,
+                    const __nv_bfloat16 *__restrict__ table, const __nv_bfloat16 *__restrict__ g, float *__restrict__ resid,
+                    __nv_bfloat16 *__restrict__ xg, float *__restrict__ ssq, int ssq_ld, int H) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int tok = next_tok[b];
+    if (tid == 0 && book) {
+        const int c = cnt[b];
+        if (c >= 0 && fin[b] == 0) {
+            out[(size_t)b * out_ld + c] = tok;
+            cnt[b] = c + 1;
+            if (tok == eos_id || c + 1 >= limit[b]) fin[b] = 1;
+            else pos[b] += 1;
+        }
+    }
+    if (table == nullptr) return;
+    const __nv_bfloat16 *row = table + (size_t)tok * H;
+    __shared__ float ws[4];
+    for (int f0 = 0; f0 < H; f0 += 128) {
+        const float v = __bfloat162float(row[f0 + tid]);
+        resid[(size_t)b * H + f0 + tid] = v;
+        xg[(size_t)b * H + f0 + tid] = __float2bfloat16(__fmul_rn(v, __bfloat162float(g[f0 + tid])));
+        const float sq = warp_sum(__fmul_rn(v, v));
+        if ((tid & 31) == 0) ws[tid >> 5] = sq;
+        __syncthreads();
+        if (tid == 0) ssq[(size_t)(f0 >> 7) * ssq_ld + b] = (ws[0] + ws[1]) + (ws[2] + ws[3]);
+        __syncthreads();
+    }
+}
+
+// slots [slot0, slot0 + n) start a sequence whose prefill chose tok[b]: token 0 of the slot's output
+__global__ void session_admit_kernel(const int *__restrict__ tok, int *__restrict__ out, int out_ld, int *__restrict__ pos,
+                                     int *__restrict__ cnt, int *__restrict__ limit, int *__restrict__ fin, int slot0, int n,
+                                     int first_pos, int max_new, int eos_id) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = slot0 + i, t = tok[b];
+    out[(size_t)b * out_ld] = t;
+    cnt[b] = 1;
+    limit[b] = max_new;
+    fin[b] = (t == eos_id || max_new <= 1) ? 1 : 0;
+    pos[b] = first_pos;
+}
+
+// slots [slot0, slot0 + n) become free; their position parks at `park` (the first position after a cached prefix)
+__global__ void session_release_kernel(int *__restrict__ pos, int *__restrict__ cnt, int *__restrict__ fin, int slot0, int n, int park) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    cnt[slot0 + i] = -1;
+    fin[slot0 + i] = 0;
+    pos[slot0 + i] = park;
 }
 
 // 1 / rms per batch column from the per-tile sums of squares (only the logits path needs it as an array: the
@@ -1320,9 +1399,9 @@ int op_argmax(const float *logits, int B, int V, int ld, int *out, int *out2, cu
 
 int op_argmax_parts(const void *parts, int n_parts, int ld, int B, int id_offset, int *out, int *out2, void *out_pairs,
                     cudaStream_t st) {
-    argmax_parts_kernel<<<(B + 31) / 32, 1024, 0, st>>>((const int2 *)parts, n_parts, ld, B, id_offset, out, out2, (int2 *)out_pairs);
+    KX_CUDA(launch_pdl(argmax_parts_kernel, dim3((B + 7) / 8), dim3(1024), 0, st, (const int2 *)parts, n_parts, ld, B, id_offset, out,
+                       out2, (int2 *)out_pairs));
     count_launch();
-    KX_CUDA(cudaGetLastError());
     return KX_OK;
 }
 
@@ -1355,6 +1434,30 @@ int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, i
                        (const __nv_bfloat16 *)table, (const __nv_bfloat16 *)g, resid, (__nv_bfloat16 *)xg, ssq, ssq_ld, H, store,
                        eos_id, done));
     count_launch();
+    return KX_OK;
+}
+
+int op_session_tail(const int *next_tok, int *out, int out_ld, int *pos, int *cnt, const int *limit, int *fin, int eos_id, int book,
+                    const void *table, const void *g, float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, cudaStream_t st) {
+    KX_REQUIRE(H % 128 == 0, KX_EINVAL, "session tail: hidden must be a multiple of 128");
+    KX_CUDA(launch_pdl(session_tail_kernel, dim3(B), dim3(128), 0, st, next_tok, out, out_ld, pos, cnt, limit, fin, eos_id, book,
+                       (const __nv_bfloat16 *)table, (const __nv_bfloat16 *)g, resid, (__nv_bfloat16 *)xg, ssq, ssq_ld, H));
+    count_launch();
+    return KX_OK;
+}
+
+int op_session_admit(const int *tok, int *out, int out_ld, int *pos, int *cnt, int *limit, int *fin, int slot0, int n, int first_pos,
+                     int max_new, int eos_id, cudaStream_t st) {
+    session_admit_kernel<<<(n + 127) / 128, 128, 0, st>>>(tok, out, out_ld, pos, cnt, limit, fin, slot0, n, first_pos, max_new, eos_id);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
+    return KX_OK;
+}
+
+int op_session_release(int *pos, int *cnt, int *fin, int slot0, int n, int park, cudaStream_t st) {
+    session_release_kernel<<<(n + 127) / 128, 128, 0, st>>>(pos, cnt, fin, slot0, n, park);
+    count_launch();
+    KX_CUDA(cudaGetLastError());
     return KX_OK;
 }
 

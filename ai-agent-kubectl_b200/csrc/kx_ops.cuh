@@ -38,6 +38,13 @@ int op_advance(int *pos, int n, cudaStream_t st);
 int op_decode_tail(const int *next_tok, int *out_ids, int n_new, int base_pos, int *pos, const void *table, const void *g,
                    float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, int store, int eos_id, int *done, cudaStream_t st);
 int op_col_rinv(const float *ssq, int tiles, int ld, int B, int H, float eps, float *out, cudaStream_t st);
+// continuous batching: per-slot bookkeeping of a decode step (+ the next step's input on the deferred-norm path when
+// `table` is given), admission and release of slots
+int op_session_tail(const int *next_tok, int *out, int out_ld, int *pos, int *cnt, const int *limit, int *fin, int eos_id, int book,
+                    const void *table, const void *g, float *resid, void *xg, float *ssq, int ssq_ld, int B, int H, cudaStream_t st);
+int op_session_admit(const int *tok, int *out, int out_ld, int *pos, int *cnt, int *limit, int *fin, int slot0, int n, int first_pos,
+                     int max_new, int eos_id, cudaStream_t st);
+int op_session_release(int *pos, int *cnt, int *fin, int slot0, int n, int park, cudaStream_t st);
 // tensor-parallel helpers
 int op_add_inplace(float *x, const float *d, size_t n, cudaStream_t st);
 int op_argmax_pairs(const float *logits, int B, int V, int ld, int id_offset, void *pairs, cudaStream_t st);

@@ -15,7 +15,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 
 from . import _lib, tokenizer, weights as weights_mod
-from .chat_model import Engine
+from .chat_model import Engine, SlotEngine
 from .model_config import ModelConfig, get_config
 
 c_int32, c_float, c_void_p = ctypes.c_int32, ctypes.c_float, ctypes.c_void_p
@@ -54,6 +54,14 @@ _lib.declare("kx_engine_set_prefix", ctypes.c_int, [c_void_p, c_void_p, c_int32,
 _lib.declare("kx_engine_set_eos", ctypes.c_int, [c_void_p, c_int32])
 _lib.declare("kx_engine_destroy", None, [c_void_p])
 _lib.declare("kx_engine_device_bytes", ctypes.c_int64, [c_void_p])
+_lib.declare("kx_engine_session_open", ctypes.c_int, [c_void_p])
+_lib.declare("kx_engine_session_admit", ctypes.c_int, [c_void_p, c_int32, c_int32, c_void_p, c_int32, c_int32,
+                                                        ctypes.POINTER(KxGenStats)])
+_lib.declare("kx_engine_session_step", ctypes.c_int, [c_void_p, c_int32, c_int32])
+_lib.declare("kx_engine_session_poll", ctypes.c_int, [c_void_p, c_void_p, c_void_p])
+_lib.declare("kx_engine_session_read", ctypes.c_int, [c_void_p, c_int32, c_int32, c_void_p, c_int32])
+_lib.declare("kx_engine_session_release", ctypes.c_int, [c_void_p, c_int32, c_int32])
+_lib.declare("kx_engine_session_live", c_int32, [c_void_p])
 _lib.declare("kx_engine_generate", ctypes.c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p,
                                                    ctypes.POINTER(KxGenStats), c_void_p])
 
@@ -240,6 +248,39 @@ class Generator:
         self.last_stats = stats
         return out, logits
 
+    # ---- continuous batching: thin wrappers of kx_engine_session_* (include/kx.h), driven by one host thread ----
+    def session_open(self) -> None:
+        _lib.check(_lib.lib().kx_engine_session_open(self._h))
+
+    def session_admit(self, slot0: int, tokens: np.ndarray, max_new: int) -> KxGenStats:
+        """tokens int32 [n, S] -> slots slot0 .. slot0+n-1 hold the prompts' KV and their first token."""
+        tokens = np.ascontiguousarray(tokens, np.int32)
+        n, S = tokens.shape
+        stats = KxGenStats()
+        _lib.check(_lib.lib().kx_engine_session_admit(self._h, slot0, n, tokens.ctypes.data, S, max_new, ctypes.byref(stats)))
+        return stats
+
+    def session_step(self, n_steps: int, n_slots: int) -> None:
+        _lib.check(_lib.lib().kx_engine_session_step(self._h, n_steps, n_slots))
+
+    def session_poll(self):
+        """(count int32 [max_batch] (-1: free slot), finished int32 [max_batch]) after the enqueued steps."""
+        cnt, fin = np.empty(self.max_batch, np.int32), np.empty(self.max_batch, np.int32)
+        _lib.check(_lib.lib().kx_engine_session_poll(self._h, cnt.ctypes.data, fin.ctypes.data))
+        return cnt, fin
+
+    def session_read(self, slot0: int, n_slots: int, n: int) -> np.ndarray:
+        """int32 [n_slots, n]: the first n tokens of the outputs of slots slot0 .. slot0+n_slots-1."""
+        out = np.empty((n_slots, n), np.int32)
+        _lib.check(_lib.lib().kx_engine_session_read(self._h, slot0, n_slots, out.ctypes.data, n))
+        return out
+
+    def session_release(self, slot0: int, n: int = 1) -> None:
+        _lib.check(_lib.lib().kx_engine_session_release(self._h, slot0, n))
+
+    def session_live(self) -> int:
+        return int(_lib.lib().kx_engine_session_live(self._h))
+
     def close(self):
         if getattr(self, "_h", None):
             _lib.lib().kx_engine_destroy(self._h)
@@ -258,7 +299,7 @@ class PromptTooLong(RuntimeError):
     error of the OpenAI client ends up too."""
 
 
-class B200Engine(Engine):
+class B200Engine(SlotEngine):
     """``chat_model.Engine`` over a ``Generator``: prompts are byte-tokenised into ``prompt_len`` token slots (left-padded
     with spaces), ``max_new`` tokens are decoded greedily -- stopping early once every sequence has produced the
     end-of-sequence token -- and the ids are mapped back to text.
@@ -268,15 +309,23 @@ class B200Engine(Engine):
     synthetic prompts as "padded / truncated to exactly 256 tokens", so bench.py asks for that explicitly.
 
     ``cancelled`` (one callable per prompt, from the batching front end): requests whose waiter is already gone when the
-    batch is formed are not prefilled at all; the engine runs a static batch, so a request cancelled after that point
-    still occupies its row until the batch ends (continuous batching is not built)."""
+    batch is formed are not prefilled at all.  ``generate`` runs a static batch: a request cancelled after that point
+    occupies its row until the batch ends.
+
+    ``continuous=True`` makes ``B200ChatModel`` / ``EngineServer`` drive the engine through its slots instead
+    (``chat_model.ContinuousFrontend`` over ``kx_engine_session_*``): requests join at the next step boundary, leave as
+    soon as their own sequence ends, and a cancelled request frees its slot mid-sequence.  Single-GPU replicas only."""
 
     def __init__(self, arch: str, seed: int = 3, max_batch: int = 64, prompt_len: int = 256, max_new: int = 32,
                  device: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl: Optional[NcclComm] = None,
                  prefix: Optional[str] = None, prefix_len: int = 0, auto_prefix: bool = False, max_prefix: int = 512,
-                 parity_init: bool = False, p2p: bool = True, on_overflow: str = "error", eos: bool = True):
+                 parity_init: bool = False, p2p: bool = True, on_overflow: str = "error", eos: bool = True,
+                 continuous: bool = False):
         if on_overflow not in ("error", "truncate"):
             raise ValueError("on_overflow must be 'error' or 'truncate'")
+        if continuous and tp_size > 1:
+            raise ValueError("continuous batching runs on single-GPU replicas (tp_size = 1)")
+        self.continuous = continuous
         self.on_overflow = on_overflow
         self.auto_prefix, self.max_prefix = auto_prefix, (max_prefix // 16) * 16
         self._prefix_bytes, self.prefix_sets = b"", 0
@@ -358,6 +407,73 @@ class B200Engine(Engine):
         if not n_tok:
             return tokenizer.encode_fixed_batch([prompts[k] for k in keep_pos], self.prompt_len), keep_idx
         return tokenizer.encode_suffix_batch([raw[k][len(want):] for k in keep_pos], self.prompt_len), keep_idx
+
+    # ---- SlotEngine (continuous batching), called from ContinuousFrontend's thread ----
+    def slots_open(self) -> None:
+        self.gen.session_open()
+
+    def slots_prepare(self, prompts: Sequence[str], idle: bool) -> List:
+        out: List = [None] * len(prompts)
+        index = list(range(len(prompts)))
+        if not self.auto_prefix:
+            room = self.prompt_len - 1
+            keep = []
+            for i in index:
+                n = len(prompts[i].encode("utf-8"))
+                if n > room and self.on_overflow == "error":
+                    out[i] = PromptTooLong(f"prompt of {n + 1} tokens exceeds the engine's {self.prompt_len}-token prompt window")
+                else:
+                    keep.append(i)
+            toks = tokenizer.encode_fixed_batch([prompts[i] for i in keep], self.prompt_len) if keep else []
+        elif idle:
+            # nothing is decoding: the cached prefix may be re-learned from these prompts (that ends the session)
+            sets = self.prefix_sets
+            had = self._prefix_bytes
+            toks, keep = self._with_learned_prefix(prompts, index, out)
+            if self.prefix_sets != sets or self._prefix_bytes != had:
+                self.gen.session_open()
+            toks = toks if keep else []
+        else:
+            # sequences are decoding against the cached prefix: only prompts that continue it can join them
+            want = self._prefix_bytes
+            raw = [p.encode("utf-8") for p in prompts]
+            room = self.prompt_len if want else self.prompt_len - 1
+            keep = []
+            for i in index:
+                if want and not raw[i].startswith(want):
+                    continue                                             # None: wait until the engine is idle
+                n = len(raw[i]) - len(want)
+                if n > room and self.on_overflow == "error":
+                    out[i] = PromptTooLong(f"prompt needs {n} tokens after the cached prefix, the suffix window holds {room}")
+                else:
+                    keep.append(i)
+            if not keep:
+                toks = []
+            elif want:
+                toks = tokenizer.encode_suffix_batch([raw[i][len(want):] for i in keep], self.prompt_len)
+            else:
+                toks = tokenizer.encode_fixed_batch([prompts[i] for i in keep], self.prompt_len)
+        for i, row in zip(keep, toks):
+            out[i] = row
+        return out
+
+    def slots_admit(self, slot0: int, rows) -> None:
+        self.last_admit = self.gen.session_admit(slot0, np.stack(rows), self.max_new)
+
+    def slots_step(self, n_steps: int, n_slots: int) -> None:
+        self.gen.session_step(n_steps, n_slots)
+
+    def slots_poll(self):
+        return self.gen.session_poll()
+
+    def slots_read(self, slot0: int, counts: Sequence[int]) -> List[str]:
+        ids = self.gen.session_read(slot0, len(counts), max(1, max(counts)))
+        for j, c in enumerate(counts):
+            ids[j, c:] = tokenizer.EOS                                  # beyond what the slot produced
+        return tokenizer.decode_batch(ids)
+
+    def slots_release(self, slot0: int, n: int) -> None:
+        self.gen.session_release(slot0, n)
 
     def close(self):
         self.gen.close()

@@ -26,7 +26,7 @@ import threading
 from multiprocessing.connection import Client, Listener
 from typing import List, Optional, Sequence
 
-from .chat_model import BatchingFrontend, Engine, _Request
+from .chat_model import Engine, _Request, make_frontend
 
 logger = logging.getLogger(__name__)
 _AUTHKEY = b"kx-engine"
@@ -39,7 +39,7 @@ class EngineServer:
         if os.path.exists(address):
             os.unlink(address)
         self.address = address
-        self.frontend = BatchingFrontend(engine, max_wait_ms=max_wait_ms)
+        self.frontend = make_frontend(engine, max_wait_ms=max_wait_ms)   # continuous batching if the engine has slots
         self.listener = Listener(address, family="AF_UNIX", authkey=authkey)
         self.clients = 0
         self._closing = False

@@ -409,6 +409,46 @@ def k9_block(dev, pk, n_distinct=1_000_000, repeat=10, reps=10):
             "parity": f"first {m} strings equal to the C oracle; all copies equal"}
 
 
+def poisson_block(eng, rate, seconds, seed=7):
+    """Open-loop arrivals (exponential gaps, `rate` requests/s for `seconds`) served with continuous batching
+    (chat_model.ContinuousFrontend over the engine's slots): time to first token and to the answer per request."""
+    from kubectl_b200.chat_model import ContinuousFrontend, _Request
+    n = max(8, int(rate * seconds))
+    prompts = gen_prompts(n, seed=seed)
+    gaps = np.random.default_rng(seed).exponential(1.0 / rate, n)
+    fe = ContinuousFrontend(eng, max_wait_ms=1.0)
+    reqs = []
+    t0 = time.monotonic()
+    due = t0
+    for p, g in zip(prompts, gaps):
+        due += g
+        while True:
+            d = due - time.monotonic()
+            if d <= 0:
+                break
+            time.sleep(min(d, 0.002))
+        r = _Request(p, None)
+        reqs.append(r)
+        fe.submit(r)
+    t_sent = time.monotonic()
+    failed = 0
+    for r in reqs:
+        try:
+            r.future.result(timeout=120)
+        except Exception:  # noqa: BLE001
+            failed += 1
+    t_done = time.monotonic()
+    fe.stop()
+    ttft, lat = np.asarray(fe.ttft or [float("nan")]) * 1e3, np.asarray(fe.latency or [float("nan")]) * 1e3
+    return {"arrival": f"open-loop Poisson, {rate:.0f} requests/s for {t_sent - t0:.2f} s ({n} distinct requests), one replica",
+            "offered_per_s": n / (t_sent - t0), "completed_per_s": (n - failed) / (t_done - t0), "failed": failed,
+            "ttft_p50_ms": float(np.percentile(ttft, 50)), "ttft_p99_ms": float(np.percentile(ttft, 99)),
+            "latency_p50_ms": float(np.percentile(lat, 50)), "latency_p99_ms": float(np.percentile(lat, 99)),
+            "admissions": int(fe.admissions), "decode_steps_per_poll": fe.steps_per_poll,
+            "ttft_definition": "submit -> the request's prefill has chosen its first token (its admission returned)",
+            "engine": "kx_engine_session_* (include/kx.h) driven by chat_model.ContinuousFrontend"}
+
+
 def run_generate(args):
     import torch
     import kubectl_b200  # noqa: F401
@@ -552,6 +592,11 @@ def run_generate(args):
         if dj.get("batch") == mine and dj.get("arch") == args.arch:
             dtraffic = dj["dram_bytes_per_step"]
     coalesced = int(model.frontend.coalesced)
+    # ---- streaming arrivals: half the burst throughput of this replica, offered as a Poisson process ----
+    poisson = None
+    if tp == 1 and not PFX and args.poisson_seconds > 0:
+        burst_rate = mine * args.steps / (dev_ms / 1e3)
+        poisson = poisson_block(eng, args.poisson_load * burst_rate, args.poisson_seconds)
     model.close()
     k9 = k9_block(dev, pk) if (args.k9 and tp == 1) else None
     line = {
@@ -570,6 +615,7 @@ def run_generate(args):
                    "validator_verdicts": {"safe": n_safe, "rejected": len(cmds) - n_safe},
                    "coalesced_duplicates": coalesced},
         "ttft_p50_ms": prefill_ms, "ttft_note": "all requests arrive at t = 0 and are prefilled as one batch: TTFT = the batch's prefill",
+        "poisson": poisson,
         "decode_ms_per_step": step_ms, "decode_hbm_gbs": decode_gbs,
         "decode_hbm_frac": decode_gbs / pk["hbm_gbs"], "prefill_tflops": prefill_flops / (prefill_ms * 1e-3) / 1e12,
         "prefill_tensor_frac": prefill_flops / (prefill_ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
@@ -658,6 +704,8 @@ def main():
     ap.add_argument("--seed", type=int, default=4)
     ap.add_argument("--cpu-requests", type=int, default=8, help="requests per CPU batch (cpu_baseline sample / reference-arm step)")
     ap.add_argument("--k9", type=int, default=1, help="1: add the validate+hash block (BASELINE configs[1]) to the generate line")
+    ap.add_argument("--poisson-seconds", type=float, default=3.0, help="length of the streaming-arrival run (0: skip)")
+    ap.add_argument("--poisson-load", type=float, default=0.5, help="offered load as a fraction of the measured burst throughput")
     ap.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per replica (config 5: 2)")
     ap.add_argument("--tp-allreduce", default="fused", choices=["fused", "nccl"], help="decode all-reduce of a TP=2 replica (A/B)")
     ap.add_argument("--prefix-len", type=int, default=0, help="tokens of shared, prefix-cached system prompt (config 5: 1024)")

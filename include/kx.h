@@ -275,6 +275,37 @@ int kx_engine_set_eos(kx_engine *e, int32_t eos_id);
 int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t batch, int32_t prompt_len, int32_t n_new,
                        int32_t *h_out, float *d_logits, kx_gen_stats *stats, void *stream);
 
+/*
+ * Continuous batching (kx_engine_session_*).  Replaces, in the reference, the way /kubectl-command serves requests:
+ * each one is awaited on its own as it arrives (app.py:183-186) and is cancelled on its own when its deadline passes
+ * (app.py:189-191).  The engine's max_batch sequence SLOTS are admitted, stepped and released independently, so a
+ * request that arrives while others are decoding joins at the next step boundary instead of waiting for their batch
+ * to end, and a cancelled or finished request frees its slot (and KV pages) at once.  Single-GPU replicas only.
+ * One host thread drives a session; kx_engine_generate and kx_engine_set_prefix refuse to run while slots are live
+ * and end the session (open it again afterwards).
+ *
+ *   open     every slot free.
+ *   admit    prefill n prompts of prompt_len tokens each (host int32 [n, prompt_len]) into slots slot0 .. slot0+n-1
+ *            (free ones: the caller keeps the slot map) and choose each one's first token; the slots then produce up
+ *            to max_new tokens, fewer if kx_engine_set_eos's id appears.  Blocks until the prefill is done; the
+ *            decoding slots keep their state across it.  stats (may be NULL): prefill_ms, launches, h2d_bytes.
+ *   step     n_steps decode steps over slots 0 .. n_slots-1 (n_slots = highest live slot + 1), enqueued on the engine's
+ *            stream as CUDA graph replays; returns without waiting.  Free and finished slots idle in place.
+ *   poll     waits for the enqueued steps; h_count[s] = tokens slot s has produced (-1: free), h_finished[s] = 1 once
+ *            it has ended (both host int32 [max_batch]).
+ *   read     the first n tokens of the outputs of slots slot0 .. slot0+n_slots-1 (host int32 [n_slots, n]).
+ *   release  slots slot0 .. slot0+n-1 become free (finished, or cancelled mid-sequence).
+ *   live     slots admitted and not yet released.
+ */
+int kx_engine_session_open(kx_engine *e);
+int kx_engine_session_admit(kx_engine *e, int32_t slot0, int32_t n, const int32_t *h_tokens, int32_t prompt_len, int32_t max_new,
+                            kx_gen_stats *stats);
+int kx_engine_session_step(kx_engine *e, int32_t n_steps, int32_t n_slots);
+int kx_engine_session_poll(kx_engine *e, int32_t *h_count, int32_t *h_finished);
+int kx_engine_session_read(kx_engine *e, int32_t slot0, int32_t n_slots, int32_t *h_out, int32_t n);
+int kx_engine_session_release(kx_engine *e, int32_t slot0, int32_t n);
+int32_t kx_engine_session_live(const kx_engine *e);
+
 /* frees the device scratch the library caches per (device, stream): the queue
  * kx_validate_hash uses to hand strings from its fast pass to its general pass
  * (4 bytes per string of the largest batch seen on that stream) */
