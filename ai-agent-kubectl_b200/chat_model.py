@@ -559,9 +559,62 @@ class B200ChatModel(_LCRunnable):
     def close(self):
         self.frontend.close()
 
+    # ---- BaseChatModel hooks (langchain_core/language_models/chat_models.py: what ChatOpenAI implements) ----
+    # The service only ever calls the Runnable methods above (app.py:118, app.py:183-186); these are for callers that
+    # hold the model as a chat model (callbacks, `.generate()`), and for `langchain_chat_model()` below.
     @property
     def _llm_type(self) -> str:
         return "b200-local"
+
+    @property
+    def _identifying_params(self) -> dict:
+        return {"model_name": self.arch, "temperature": 0}
+
+    @staticmethod
+    def _apply_stop(text: str, stop: Optional[Sequence[str]]) -> str:
+        for s in stop or ():
+            k = text.find(s)
+            if k >= 0:
+                text = text[:k]
+        return text
+
+    def _result(self, text: str):
+        msg = self._wrap(text)
+        try:
+            from langchain_core.outputs import ChatGeneration, ChatResult  # type: ignore
+            return ChatResult(generations=[ChatGeneration(message=msg)], llm_output={"model_name": self.arch})
+        except Exception:  # noqa: BLE001 - no LangChain here: same shape, plain objects
+            from types import SimpleNamespace
+            return SimpleNamespace(generations=[SimpleNamespace(message=msg, text=text)], llm_output={"model_name": self.arch})
+
+    def _generate(self, messages, stop: Optional[Sequence[str]] = None, run_manager=None, **kw):
+        return self._result(self._apply_stop(self.invoke(messages).content, stop))
+
+    async def _agenerate(self, messages, stop: Optional[Sequence[str]] = None, run_manager=None, **kw):
+        return self._result(self._apply_stop((await self.ainvoke(messages)).content, stop))
+
+    def langchain_chat_model(self):
+        """This model as a ``langchain_core`` ``BaseChatModel`` (needs LangChain; it is not in this image, so this
+        adapter has never run against the real package -- INTEGRATION.md)."""
+        from langchain_core.language_models.chat_models import BaseChatModel  # type: ignore
+        inner = self
+
+        class B200LangChainChatModel(BaseChatModel):  # type: ignore[misc]
+            @property
+            def _llm_type(self) -> str:
+                return inner._llm_type
+
+            @property
+            def _identifying_params(self) -> dict:
+                return inner._identifying_params
+
+            def _generate(self, messages, stop=None, run_manager=None, **kw):
+                return inner._generate(messages, stop=stop)
+
+            async def _agenerate(self, messages, stop=None, run_manager=None, **kw):
+                return await inner._agenerate(messages, stop=stop)
+
+        return B200LangChainChatModel()
 
 
 #: exported under the name the reference imports (app.py:11)

@@ -356,8 +356,21 @@ class B200Engine(SlotEngine):
             else:
                 live.append(i)
         if self.auto_prefix and live:
-            toks, live = self._with_learned_prefix([prompts[i] for i in live], live, out)
-        elif live:
+            # requests that continue the cached prefix keep it; the others form a second batch that learns its own
+            want = self._prefix_bytes
+            first = [i for i in live if want and prompts[i].encode("utf-8").startswith(want)]
+            taken = set(first)
+            rest = [i for i in live if i not in taken]
+            for part in (first, rest):
+                if not part:
+                    continue
+                toks, keep = self._with_learned_prefix([prompts[i] for i in part], part, out)
+                if keep:
+                    ids, _ = self.gen.generate_ids(toks, self.max_new)
+                    for i, text in zip(keep, tokenizer.decode_batch(ids)):
+                        out[i] = text
+            return out
+        if live:
             room = self.prompt_len - 1                                   # one slot is the BOS token
             if self.on_overflow == "error":
                 keep = []
@@ -425,8 +438,9 @@ class B200Engine(SlotEngine):
                 else:
                     keep.append(i)
             toks = tokenizer.encode_fixed_batch([prompts[i] for i in keep], self.prompt_len) if keep else []
-        elif idle:
-            # nothing is decoding: the cached prefix may be re-learned from these prompts (that ends the session)
+        elif idle and not (self._prefix_bytes and any(p.encode("utf-8").startswith(self._prefix_bytes) for p in prompts)):
+            # nothing is decoding and nobody continues the cached prefix: it is learned again from these prompts
+            # (which ends the session)
             sets = self.prefix_sets
             had = self._prefix_bytes
             toks, keep = self._with_learned_prefix(prompts, index, out)
@@ -434,7 +448,8 @@ class B200Engine(SlotEngine):
                 self.gen.session_open()
             toks = toks if keep else []
         else:
-            # sequences are decoding against the cached prefix: only prompts that continue it can join them
+            # sequences are decoding against the cached prefix (or some of these prompts continue it): only prompts that
+            # continue it are admitted, the others wait until the engine is idle and nobody needs this prefix
             want = self._prefix_bytes
             raw = [p.encode("utf-8") for p in prompts]
             room = self.prompt_len if want else self.prompt_len - 1
@@ -499,9 +514,9 @@ def default_engine_factory(arch: str) -> Engine:
         "tokenizer vocabulary can be loaded offline): completions are noise and the reference's validator will reject them (422).",
         arch)
 
-    def make(device: int) -> Engine:
-        return B200Engine(arch, prompt_len=128, auto_prefix=True, device=device)
+    def make(device: int, continuous: bool) -> Engine:
+        return B200Engine(arch, prompt_len=128, auto_prefix=True, device=device, continuous=continuous)
     if n <= 1:
-        return make(dev0)
+        return make(dev0, True)        # one replica: continuous batching (requests join and leave at step boundaries)
     from .router import ReplicaRouter
-    return ReplicaRouter([make(dev0 + i) for i in range(n)])
+    return ReplicaRouter([make(dev0 + i, False) for i in range(n)])   # the router hands each replica static batches

@@ -168,3 +168,25 @@ def test_identical_prompts_in_flight_are_generated_once():
     assert [o.content for o in outs] == [f"Q{i % 3}" for i in range(30)]
     assert sum(eng.batches) < 30 and m.frontend.coalesced == 30 - sum(eng.batches)
     m.close()
+
+
+def test_chat_model_hooks_generate_and_agenerate():
+    """The BaseChatModel hooks ChatOpenAI implements (_generate / _agenerate / _llm_type / _identifying_params); LangChain
+    itself is not in this image, so the result objects are the plain stand-ins with the same attributes."""
+    m, _ = make(lambda p: "kubectl get pods\nExplanation: lists pods")
+
+    class Msg:
+        def __init__(self, content):
+            self.content = content
+
+    res = m._generate([Msg("system text"), Msg("list pods")], stop=["\nExplanation"])
+    assert res.generations[0].message.content == "kubectl get pods" and res.llm_output["model_name"] == m.arch
+    res2 = asyncio.run(m._agenerate([Msg("list pods")]))
+    assert res2.generations[0].message.content.startswith("kubectl get pods\n")
+    assert m._llm_type == "b200-local" and m._identifying_params == {"model_name": m.arch, "temperature": 0}
+    try:
+        import langchain_core  # noqa: F401
+    except ImportError:
+        with pytest.raises(ImportError):
+            m.langchain_chat_model()
+    m.close()

@@ -135,3 +135,42 @@ def test_chat_model_over_the_continuous_engine():
     with pytest.raises(RuntimeError, match="prompt window"):
         m.invoke("x" * 500)
     m.close()
+
+
+def test_service_engine_continuous_with_the_learned_template_prefix():
+    """What default_engine_factory starts: the template's instruction prefix is learned from the first requests and its KV
+    shared; later requests that continue it join the running sequences; one that does not waits for an idle engine,
+    after which the prefix is learned again.  Completions equal the static engine's for the same prompts."""
+    import threading
+    import time
+    import kubectl_b200  # noqa: F401
+    from kubectl_b200 import engine
+    from kubectl_b200.chat_model import B200ChatModel
+    head = "You are a Kubernetes CLI specialist. " * 6 + "User Request: "
+    qs = [f"list pods in namespace team-{i}" for i in range(8)]
+    prompts = [head + q + "\nKubectl Command:\n" for q in qs]
+    kw = dict(max_batch=8, prompt_len=64, max_new=12, auto_prefix=True, max_prefix=256, eos=False)
+    static = engine.B200Engine("tiny-qwen2", **kw)
+    want = static.generate(prompts)
+    static.close()
+    eng = engine.B200Engine("tiny-qwen2", continuous=True, **kw)
+    m = B200ChatModel(engine=eng, max_wait_ms=500.0)
+    assert [o.content for o in m.batch(prompts)] == want
+    assert eng.prefix_sets == 1
+    # the same requests arriving a few at a time: same completions (the prefix is reused, slots are reused)
+    res = {}
+    ts = [threading.Thread(target=lambda i=i: res.__setitem__(i, m.invoke(prompts[i]).content)) for i in range(8)]
+    for i, t in enumerate(ts):
+        t.start()
+        if i % 3 == 2:
+            time.sleep(0.002)
+    for t in ts:
+        t.join(60)
+    assert [res[i] for i in range(8)] == want and eng.prefix_sets == 1
+    # a prompt with another beginning cannot join sequences that attend to the cached prefix: it is served once they are done
+    other = "Translate to kubectl: " + "x" * 20
+    got = m.batch([prompts[0], other, prompts[1]])
+    assert got[0].content == want[0] and got[2].content == want[1]       # served with the cached prefix ...
+    assert isinstance(got[1].content, str) and eng._prefix_bytes == b""   # ... which was dropped for `other` afterwards
+    assert [o.content for o in m.batch(prompts)] == want and eng.prefix_sets == 2    # and learned again
+    m.close()
