@@ -332,8 +332,12 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     return KX_OK;
 }
 
-// Decode on the deferred-RMSNorm path (single GPU replica, batch < 256: every projection is a swap-AB cluster GEMM).
-bool fused_norm_decode(const kx_engine *e, int B) { return e->fused_norm && e->d.tp_size <= 1 && B < 256; }
+// Decode on the deferred-RMSNorm path (batch < 256: every projection is a swap-AB cluster GEMM): single-GPU replicas, and
+// tensor-parallel pairs whose row-parallel projections all-reduce inside their epilogue over peer memory.
+bool fused_norm_decode(const kx_engine *e, int B) {
+    if (!e->fused_norm || B >= 256) return false;
+    return e->d.tp_size <= 1 || (e->d.tp_size == 2 && e->p2p_peer_recv && B <= e->p2p_rows);
+}
 
 // One layer of a decode step with the RMSNorms folded into the projections (kx_gemm.cuh): five launches --
 // QKV (scaled by 1 / rms), attention, wo (+ residual, prepares norm 2), gate/up (scaled, SwiGLU), down (+ residual,
@@ -351,6 +355,12 @@ int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st)
                     const char *label, bool ssq_in, const void *norm_g) {
         GemmCall c{w, x + bi, features, B, k, epi, 1, pick_splits(features, k, b_tiles), bn, out, ldo, bias};
         c.label = label; c.ssq_in = ssq_in; c.norm_g = norm_g;
+        if (epi == EPI_RESID_NORM && d.tp_size > 1) {      // row-parallel: the two ranks' partial sums meet in the epilogue
+            c.tp_fused = true;
+            const int rc = run_gemm(e, c, st);             // (receive half-buffer: parity of p2p_launches)
+            ++e->p2p_launches;
+            return rc;
+        }
         return run_gemm(e, c, st);
     };
     KX_TRY(gemm(&L.wqkv, e->xn_b, e->qkv_dim, d.hidden, EPI_BF16, e->qkv, e->qkv_dim, L.w.bqkv, "qkv", true, nullptr));

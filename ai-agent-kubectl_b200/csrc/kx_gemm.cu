@@ -894,17 +894,19 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 for (int c = 0; c < kCG; ++c) acc[c] += src[c * BM];
             }
         };
-        if (EPI == EPI_RESID && p.tp_peer_recv) {
-            // ---- fused tensor-parallel all-reduce (2 ranks) over peer memory ----
+        // ---- fused tensor-parallel all-reduce (2 ranks) over peer memory: this CTA's partial sums go to the peer's receive
+        // buffer, a flag per CTA publishes them, and the peer's partial is read back from this rank's own buffer ----
+        size_t tp_buf = 0;
+        auto tp_exchange = [&]() {
             const uint32_t slot = (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z;
             const uint32_t epoch = p.tp_epoch[slot] + 1;       // same count on both ranks: they run the same launches
-            const size_t buf = (size_t)(p.tp_seq & 1) * (size_t)p.tp_rows * p.ldo;   // receive half-buffer of this launch
+            tp_buf = (size_t)(p.tp_seq & 1) * (size_t)p.tp_rows * p.ldo;   // receive half-buffer of this launch
             for (int jg = j0; jg < j1; jg += kCG) {
                 float v[kCG];
                 column_sums(jg, v);
 #pragma unroll
                 for (int c = 0; c < kCG; ++c)
-                    if (ok && jg + c < j1) p.tp_peer_recv[buf + (size_t)(n0 + jg + c) * p.ldo + arow] = v[c];      // NVLink store
+                    if (ok && jg + c < j1) p.tp_peer_recv[tp_buf + (size_t)(n0 + jg + c) * p.ldo + arow] = v[c];      // NVLink store
             }
             __threadfence_system();
             asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -921,19 +923,25 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 p.tp_epoch[slot] = epoch;
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
+        };
+        if (EPI == EPI_RESID && p.tp_peer_recv) {
+            tp_exchange();
             for (int jg = j0; jg < j1; jg += kCG) {
                 float v[kCG];
                 column_sums(jg, v);                            // this rank's partial again (still in shared memory / TMEM)
 #pragma unroll
                 for (int c = 0; c < kCG; ++c) {
                     if (ok && jg + c < j1) {
-                        const float other = __ldcv(p.tp_recv + buf + (size_t)(n0 + jg + c) * p.ldo + arow);   // the peer's partial
+                        const float other = __ldcv(p.tp_recv + tp_buf + (size_t)(n0 + jg + c) * p.ldo + arow);   // the peer's partial
                         reinterpret_cast<float *>(p.out)[(size_t)(n0 + jg + c) * p.ldo + arow] += v[c] + other;
                     }
                 }
             }
         } else if (EPI == EPI_RESID_NORM) {
-            // residual update + preparation of the next RMSNorm (deferred: see kx_gemm.cuh)
+            // residual update + preparation of the next RMSNorm (deferred: see kx_gemm.cuh); under tensor parallelism the
+            // peer rank's partial sums are added first (both ranks then hold the same residual, bit for bit)
+            const bool tp = p.tp_peer_recv != nullptr;
+            if (tp) tp_exchange();
             const float g = ok ? __bfloat162float(reinterpret_cast<const __nv_bfloat16 *>(p.norm_g)[arow]) : 0.f;
             for (int jg = j0; jg < j1; jg += kCG) {
                 float x[kCG];
@@ -950,6 +958,11 @@ kx_gemm_bf16_ksplit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 float v[kCG];
                 column_sums(jg, v);
                 if (probe && jg == j0) ck1 = clock64();
+                if (tp) {
+#pragma unroll
+                    for (int c = 0; c < kCG; ++c)
+                        if (ok && jg + c < j1) v[c] += __ldcv(p.tp_recv + tp_buf + (size_t)(n0 + jg + c) * p.ldo + arow);
+                }
                 float sq[kCG];
 #pragma unroll
                 for (int c = 0; c < kCG; ++c) {
@@ -1206,7 +1219,7 @@ int gemm_launch(const CUtensorMap &ta, const CUtensorMap &tb, GemmParams p, int 
     p.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;      // no empty slice
     p.splits = splits;
-    KX_REQUIRE(p.epilogue != EPI_RESID_NORM || (p.swap && p.norm_g && p.norm_out && p.ssq_out && !p.tp_peer_recv), KX_EINVAL,
+    KX_REQUIRE(p.epilogue != EPI_RESID_NORM || (p.swap && p.norm_g && p.norm_out && p.ssq_out), KX_EINVAL,
                "kx_gemm: EPI_RESID_NORM needs the swap-AB kernel and its norm arguments");
     if (p.swap && (splits > 1 || p.tp_peer_recv || p.ssq_in || p.epilogue == EPI_RESID_NORM)) {
         // decode: split-K inside a cluster (portable cluster size <= 8), reduced over distributed shared memory

@@ -54,18 +54,23 @@ def test_tp2_matches_the_oracle(tmp_path, arch):
     mp.spawn(_worker, args=(2, _free_port(), arch, B, S, n_new, str(tmp_path)), nprocs=2, join=True)
     r = [torch.load(tmp_path / f"tp{i}.pt", weights_only=False) for i in range(2)]
     assert np.array_equal(r[0]["ids"], r[1]["ids"]) and np.array_equal(r[0]["ids"], r[0]["ids2"])
-    assert np.array_equal(r[0]["ids"], r[0]["ids3"])                       # fused P2P all-reduce == NCCL all-reduce
+    assert np.array_equal(r[0]["ids3"], r[1]["ids3"])
     assert r[0]["fused"] > 0 and r[1]["fused"] == r[0]["fused"] and r[0]["nccl_only_fused"] == 0
     cfg = model_config.get_config(arch)
     w = weights.make_weights(cfg, 3)
-    ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True, deferred_decode=False)
     toks = torch.randint(0, cfg.vocab, (B, S), generator=torch.Generator().manual_seed(103))
-    want_ids, want_logits = ref.generate(toks, n_new, return_logits=True)
     logits = torch.cat([r[0]["logits"], r[1]["logits"]], dim=-1)   # vocabulary shards side by side
-    for t in range(n_new):
-        err = (logits[t] - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
-        assert err <= 1e-2, f"step {t}: logits off by {err:.2e}"
-    assert np.array_equal(r[0]["ids"], want_ids.numpy())
+    # With the all-reduce fused into the projections' epilogues the pair decodes on the deferred-RMSNorm path (five
+    # launches per layer, as a single-GPU replica does); with NCCL all-reduces it keeps the separate norm kernels.  Each
+    # is checked against the oracle that rounds where it rounds.
+    for deferred, key in ((True, "ids"), (False, "ids3")):
+        ref = RefModel(cfg, w, weights.rope_table(cfg, cfg.max_pos), emulate_bf16=True, deferred_decode=deferred)
+        want_ids, want_logits = ref.generate(toks, n_new, return_logits=True)
+        if deferred:
+            for t in range(n_new):
+                err = (logits[t] - want_logits[t]).abs().max().item() / want_logits[t].abs().max().item()
+                assert err <= 1e-2, f"step {t}: logits off by {err:.2e}"
+        assert np.array_equal(r[0][key], want_ids.numpy()), key
 
 
 def _worker_8b(rank, world, port, B, S, n_new, out_dir):
@@ -125,10 +130,10 @@ def test_router_with_two_replicas_in_one_process():
     from kubectl_b200 import engine, router
     head = "You are a Kubernetes CLI specialist. " * 3 + "User Request: "
     prompts = [head + f"list pods in namespace ns{i % 11}" + "\nKubectl Command:\n" for i in range(24)]
-    single = engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=160, max_new=6, device=0)
+    single = engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=192, max_new=6, device=0)
     want = single.generate(prompts)
     single.close()
-    reps = [engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=160, max_new=6, device=d) for d in (0, 1)]
+    reps = [engine.B200Engine("tiny-llama-hd128", max_batch=32, prompt_len=192, max_new=6, device=d) for d in (0, 1)]
     r = router.ReplicaRouter(reps)
     got = r.generate(prompts)
     assert got == want
