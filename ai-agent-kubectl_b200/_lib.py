@@ -30,6 +30,7 @@ _SIGNATURES = {
     "kx_release_scratch": (None, []),
     "kx_gemm_bf16": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_void_p,
                              c_int64, c_void_p, c_int, c_void_p]),
+    "kx_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, ctypes.c_float, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "kx_argmax_parts": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "kx_attn_decode": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]
                        + [c_int] * 7 + [c_void_p]),

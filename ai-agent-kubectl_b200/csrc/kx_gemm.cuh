@@ -29,6 +29,7 @@ struct GemmParams {
     int epilogue;
     int splits;              // split-K factor requested (clamped to the number of 64-wide k blocks)
     int kb_per_split;        // filled by gemm_launch
+    int tile_band;           // pair kernel: feature tiles per band of its tile walk (filled by its launcher)
     size_t split_stride;     // token-major pair kernel with splits > 1 (EPI_F32 only): fp32 elements between the splits' partial outputs
     float *ws;               // split-K scratch, filled by gemm_launch
     uint32_t *tickets;

@@ -1506,6 +1506,14 @@ extern "C" int kx_attn_decode(const void *d_qkv, int32_t qkv_ld, void *d_out, in
                           key0, part_o, part_ml, n_part, st);
 }
 
+extern "C" int kx_rmsnorm(float *d_x, const void *d_g, void *d_y, int32_t M, int32_t H, float eps, const int32_t *d_row_map,
+                          const float *d_part, int32_t splits, int64_t split_stride, void *stream) {
+    using namespace kx;
+    KX_REQUIRE(d_x && d_g && d_y && M >= 1 && H >= 8 && H % 8 == 0, KX_EINVAL, "kx_rmsnorm: bad argument");
+    KX_REQUIRE(splits == 0 || (d_part && splits >= 1 && split_stride >= (int64_t)M * H), KX_EINVAL, "kx_rmsnorm: bad split-K partials");
+    return op_rmsnorm(d_x, d_g, d_y, M, H, eps, d_row_map, (cudaStream_t)stream, d_part, splits, (size_t)split_stride);
+}
+
 extern "C" int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream) {
     using namespace kx;
     KX_REQUIRE(d_parts && d_ids && n_parts >= 1 && B >= 1 && ld >= B, KX_EINVAL, "kx_argmax_parts: bad argument");

@@ -140,6 +140,17 @@ int kx_gemm_bf16(const void *d_a, int64_t a_rows, int64_t lda, const void *d_b, 
                  int k, int epilogue, int swap, void *d_out, int64_t ldo, const float *d_bias, int splits,
                  void *stream);
 
+/*
+ * kx_rmsnorm -- the decoder's RMSNorm as a stand-alone op (k5; defined by BASELINE.json's north_star, no reference code):
+ * d_y bf16 [M, H] = bf16( x * (1 / sqrt(mean(x^2) + eps)) * g ) for the rows of d_x fp32 [*, H] (row i of the output reads
+ * row d_row_map[i] of d_x, or row i when d_row_map is NULL); d_g bf16 [H].  splits > 0 (M <= 2048 only): the rows first
+ * receive the pending split-K partial sums of the preceding projection, x += d_part[0] + d_part[1] + ... (slice s at
+ * d_part + s * split_stride, added in slice order) and are written back -- what the engine does for decode batches
+ * of 256 and more.
+ */
+int kx_rmsnorm(float *d_x, const void *d_g, void *d_y, int32_t M, int32_t H, float eps, const int32_t *d_row_map,
+               const float *d_part, int32_t splits, int64_t split_stride, void *stream);
+
 /* Second stage of KX_EPI_ARGMAX: d_parts int2 [n_parts][ld] -> d_ids int32 [B]; ties go to the lowest id. */
 int kx_argmax_parts(const void *d_parts, int32_t n_parts, int32_t ld, int32_t B, int32_t *d_ids, void *stream);
 
