@@ -36,7 +36,7 @@ struct kx_engine {
     bool attn_tc = true;                           // prefill attention on tcgen05 (kx_attn_tc.cu) for head_dim 64
     int64_t attn_tc_launches = 0;
     bool share_prefix = true;                      // decode attention reads a cached prefix once per 64 query rows
-    bool fused_norm = true;                        // decode (batch < 256, no TP): RMSNorm deferred into the GEMM epilogues
+    bool fused_norm = true;                        // decode (batch <= 256): RMSNorm deferred into the GEMM epilogues
     float *ssq = nullptr, *col_rinv = nullptr;     // ... per-tile sums of squares [hidden / 128][max_batch]; 1 / rms per column
     int eos_id = -1;                               // kx_engine_set_eos: decode stops once every sequence has emitted it
     int *done = nullptr, *h_done = nullptr;        // device [1 + max_batch]: count, per-sequence flag; pinned host copy of the count
@@ -210,7 +210,7 @@ int linear_pair_bn(const Linear &l, int M) {
     const bool little_waste = (padded - l.features) * 100 <= waste_pct * l.features;   // partial last tile is cheap enough
     if ((l.features % 256 == 0 || l.features >= 2048 || little_waste) && t256 >= 64) return 256;
     // fewer 128-wide tiles than this leave most SMs idle: the weight-streaming kernel with split-K covers them
-    constexpr int min128 = 24;
+    constexpr int min128 = 24;     // (QKV of a 256 / 512-wide decode batch through the cluster kernel instead: 2.64 / 3.20 vs 2.47 / 3.07 ms per step)
     return t128 >= min128 ? 128 : 0;
 }
 
@@ -332,10 +332,12 @@ int layer_forward(kx_engine *e, int li, int M, bool decode, int nb, int S, int b
     return KX_OK;
 }
 
-// Decode on the deferred-RMSNorm path (batch < 256: every projection is a swap-AB cluster GEMM): single-GPU replicas, and
+// Decode on the deferred-RMSNorm path (batch <= 256: every projection is a swap-AB cluster GEMM): single-GPU replicas, and
 // tensor-parallel pairs whose row-parallel projections all-reduce inside their epilogue over peer memory.
 bool fused_norm_decode(const kx_engine *e, int B) {
-    if (!e->fused_norm || B >= 256) return false;
+    // (Llama-3.2-1B, ms per step on this path / on the token-major pair-kernel path: batch 192: 2.15 / 2.53, 256: 2.35 / 2.60,
+    // 320: 2.94 / 2.70, 384: 3.24 / 2.77, 512: 3.28 / 3.02)
+    if (!e->fused_norm || B > 256) return false;
     return e->d.tp_size <= 1 || (e->d.tp_size == 2 && e->p2p_peer_recv && B <= e->p2p_rows);
 }
 
@@ -346,7 +348,7 @@ bool fused_norm_decode(const kx_engine *e, int B) {
 int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st) {
     const kx_model_desc &d = e->d;
     LayerPlan &L = e->layers[li];
-    // batch tiles of at most 64 columns: a 128-wide tile doubles the split-K exchange and the epilogue of every CTA
+    // batch tiles of 64 columns (gate/up: see below): a 128-wide tile doubles the split-K exchange and the epilogue of every CTA
     // (Llama-3.2-1B, batch 128: 1.9 ms per step with one 128-wide tile, 1.55 with two 64-wide ones)
     const int bn = B <= 32 ? 32 : 64, bi = bn_index(bn);
     const int b_tiles = (B + bn - 1) / bn;
@@ -354,6 +356,12 @@ int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st)
     auto gemm = [&](const CUtensorMap *w, const CUtensorMap *x, int features, int k, int epi, void *out, int ldo, const float *bias,
                     const char *label, bool ssq_in, const void *norm_g) {
         GemmCall c{w, x + bi, features, B, k, epi, 1, pick_splits(features, k, b_tiles), bn, out, ldo, bias};
+        if (bn == 64 && ((features + 127) / 128) * b_tiles > 296) {
+            // more 64-wide tiles than one resident wave holds (gate/up from batch 129): 128-wide tiles, which then need
+            // no split-K exchange either (batch 256: 2.64 -> 2.35 ms per step, batch 192: 2.24 -> 2.15)
+            const int bt2 = (B + 127) / 128;
+            c.b = x + bn_index(128); c.bn = 128; c.splits = pick_splits(features, k, bt2);
+        }
         c.label = label; c.ssq_in = ssq_in; c.norm_g = norm_g;
         if (epi == EPI_RESID_NORM && d.tp_size > 1) {      // row-parallel: the two ranks' partial sums meet in the epilogue
             c.tp_fused = true;

@@ -73,14 +73,17 @@ def encode_suffix_batch(datas: Sequence[bytes], length: int, pad: int = 32) -> n
 
 def decode_batch(ids: np.ndarray) -> List[str]:
     ids = np.asarray(ids)
+    n = ids.shape[1]
     is_eos = ids == EOS
-    end = np.where(is_eos.any(axis=1), is_eos.argmax(axis=1), ids.shape[1])
-    low = (ids & 0xFF).astype(np.uint8)
+    end = np.where(is_eos.any(axis=1), is_eos.argmax(axis=1), n)
     bos = ids == BOS
+    has_bos = (bos & (np.arange(n)[None, :] < end[:, None])).any(axis=1)
+    low = (ids & 0xFF).astype(np.uint8)
+    buf = low.tobytes()                      # one copy; rows without a BOS are sliced out of it (the usual case)
     out = []
     for i in range(ids.shape[0]):
-        row = low[i, :end[i]]
-        if bos[i, :end[i]].any():
-            row = row[~bos[i, :end[i]]]
-        out.append(row.tobytes().decode("utf-8", errors="replace"))
+        if has_bos[i]:
+            out.append(low[i, :end[i]][~bos[i, :end[i]]].tobytes().decode("utf-8", errors="replace"))
+        else:
+            out.append(buf[i * n:i * n + end[i]].decode("utf-8", errors="replace"))
     return out

@@ -122,7 +122,7 @@ void kx_release_host_staging(void);
 #define KX_EPI_F32       3   /* out fp32 = acc    (logits)                             */
 #define KX_EPI_ARGMAX    5   /* lm_head + greedy pick without materialising the logits: out = int2 [parts][ldo],
                                 (max logit bits, lowest feature index attaining it) per token and part.
-                                swap = 1 (batch < 256): 4 parts per 128-feature tile; swap = 0: 1 part per
+                                swap = 1 (batch <= 256): 4 parts per 128-feature tile; swap = 0: 1 part per
                                 256-feature tile.  kx_argmax_parts reduces the parts to one id per token. */
 
 /*
@@ -269,7 +269,7 @@ const char *kx_engine_trace_name(const kx_engine *e, int32_t i);
 int kx_engine_set_prefix(kx_engine *e, const int32_t *h_tokens, int32_t n, void *stream);
 
 /*
- * kx_engine_set_eos -- end-of-sequence token id (negative: none, the default).  Decode steps of fewer than 256
+ * kx_engine_set_eos -- end-of-sequence token id (negative: none, the default).  Decode steps of at most 256
  * sequences on a single-GPU replica stop being launched once every sequence has emitted it (checked every 8 steps);
  * the remaining positions of h_out are filled with the id.  The reference's LLM ends a completion the same way
  * (the OpenAI service stops at its end-of-text token; app.py:117 only sees the finished text).

@@ -19,7 +19,7 @@ Two numeric modes:
     reference with the same quantisation points makes "ids equal" a statement
     about the kernels rather than about rounding luck.  DESIGN.md lists the
     rounding points.  ``deferred_decode`` (default on): single-token steps of
-    fewer than 256 sequences round the GEMM input BEFORE the division by the rms,
+    at most 256 sequences round the GEMM input BEFORE the division by the rms,
     bf16(x * g), and divide the GEMM's output, as the decode kernels do
     (kx_gemm.cuh, deferred RMSNorm); tensor-parallel engines keep the plain order.
   The full-architecture tests (tests/test_parity_full_gpu.py) use the fp32 mode.
@@ -72,7 +72,7 @@ class RefModel:
     def _pre(self, x, g):
         """Input of the projections behind a norm and the factor their outputs are multiplied by afterwards."""
         B, S, _ = x.shape
-        if self.emu and self.deferred_decode and S == 1 and B < 256:
+        if self.emu and self.deferred_decode and S == 1 and B <= 256:
             return _r(x * g, True), torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + self.cfg.eps)
         return _r(self._norm(x, g), self.emu), 1.0
 

@@ -53,7 +53,7 @@ def _run_session(gen, plan, n_slots_total, steps_per_poll=3, max_steps=200):
     return out
 
 
-@pytest.mark.parametrize("arch,n", [("tiny-qwen2", 32), ("tiny-llama", 32), ("tiny-llama", 256)])
+@pytest.mark.parametrize("arch,n", [("tiny-qwen2", 32), ("tiny-llama", 32), ("tiny-llama", 256), ("tiny-llama", 288)])
 def test_session_equals_static_batch(arch, n):
     gen = _gen(arch, n)
     toks = _prompts(gen.cfg.vocab, n)
