@@ -356,7 +356,7 @@ int layer_forward_fused(kx_engine *e, int li, int B, int max_T, cudaStream_t st)
     auto gemm = [&](const CUtensorMap *w, const CUtensorMap *x, int features, int k, int epi, void *out, int ldo, const float *bias,
                     const char *label, bool ssq_in, const void *norm_g) {
         GemmCall c{w, x + bi, features, B, k, epi, 1, pick_splits(features, k, b_tiles), bn, out, ldo, bias};
-        if (bn == 64 && ((features + 127) / 128) * b_tiles > 296) {
+        if (bn == 64 && ((features + 127) / 128) * b_tiles > 296) {   // (at batch 128, 256 tiles: 128-wide ones measure 1.65 vs 1.46 ms)
             // more 64-wide tiles than one resident wave holds (gate/up from batch 129): 128-wide tiles, which then need
             // no split-K exchange either (batch 256: 2.64 -> 2.35 ms per step, batch 192: 2.24 -> 2.15)
             const int bt2 = (B + 127) / 128;
@@ -900,8 +900,9 @@ extern "C" int kx_engine_generate(kx_engine *e, const int32_t *h_tokens, int32_t
 // --------------------------------------------------------------------------- //
 namespace {
 
-int session_bucket(const kx_engine *e, int n_slots) {   // decode batch for slots [0, n_slots): whole 32-column tiles
-    int B = ((n_slots < 1 ? 1 : n_slots) + 31) / 32 * 32;
+int session_bucket(const kx_engine *e, int n_slots) {   // decode batch for slots [0, n_slots): whole batch tiles
+    // 32 columns, then multiples of 64 (a ragged second tile costs more than a full one: batch 96 1.50 ms, 128 1.46)
+    int B = n_slots <= 32 ? 32 : (n_slots + 63) / 64 * 64;
     return B > e->d.max_batch ? e->d.max_batch : B;
 }
 

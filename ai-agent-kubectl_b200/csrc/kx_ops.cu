@@ -1274,9 +1274,11 @@ int op_attn_decode(const void *qkv, int qkv_ld, void *out, int out_ld, void *pag
     dim3 grid(n_kv, B);
     int rc;
     const int n_tasks = n_kv * B;
-    if ((hd == 64 || hd == 128) && n_tasks >= 96 && n_tasks <= 2048 && max_T - key0 > 128 && G <= 8) {
-        // up to ~2,000 pairs with long key lists: 2 or 4 warps share a pair (measured on Llama-3.2-1B, 272 keys: batch 64
-        // 12.1 -> 9.3 us per layer, batch 128 1.66 -> 1.51 ms per step, batch 256 2.45 -> 2.38; batch 512 is slower split)
+    if ((hd == 64 || hd == 128) && n_tasks >= 96 && n_tasks <= 1536 && max_T - key0 > 128 && G <= 8) {
+        // up to ~1,500 pairs with long key lists: 2 or 4 warps share a pair (measured on Llama-3.2-1B, 272 keys: batch 64
+        // 12.1 -> 9.3 us per layer, batch 128 1.67 -> 1.53 ms per step; batch 192 is a tie; from batch 256 the one-warp
+        // kernel with 16-key stages, four CTAs per SM, is faster: 2.42 -> 2.13 ms per step.  16-key stages in this kernel
+        // changed nothing at batch 128 - 256 and cost 10 % at batch 64.)
         const __nv_bfloat16 *q = (const __nv_bfloat16 *)qkv;
         __nv_bfloat16 *o = (__nv_bfloat16 *)out, *pg = (__nv_bfloat16 *)pages;
         const float2 *rp = (const float2 *)rope;
