@@ -114,7 +114,9 @@ def parse_outputs(texts: Sequence[str], device: int = 0) -> Tuple[List[str], np.
     data, off = to_csr(texts)
     r = validate_hash_host(data, off, FLAG_PARSE, hash=False, span=True, device=device)
     raw = data.tobytes()
-    cmds = [raw[off[i] + r["span"][i, 0]:off[i] + r["span"][i, 1]].decode("utf-8", "surrogatepass") for i in range(len(texts))]
+    lo = (off[:-1] + r["span"][:, 0]).tolist()
+    hi = (off[:-1] + r["span"][:, 1]).tolist()
+    cmds = [raw[a:b].decode("utf-8", "surrogatepass") for a, b in zip(lo, hi)]
     return cmds, r["verdict"]
 
 
