@@ -182,3 +182,64 @@ def test_one_bad_prompt_fails_alone_and_an_engine_failure_is_a_runtime_error_for
     assert m.invoke("again").content == "kubectl get again"  # the session was opened again
     assert [e for e in eng.log if e[0] == "open"].__len__() == 2
     m.close()
+
+
+# ---- B200Engine's admission rules (engine.py: slots_prepare), with the GPU generator replaced by a recorder ----
+class _GenStub:
+    def __init__(self):
+        self.calls = []
+
+    def set_prefix(self, toks):
+        self.calls.append(("set_prefix", len(toks)))
+
+    def session_open(self):
+        self.calls.append(("session_open",))
+
+
+def _engine(**kw):
+    from kubectl_b200 import engine
+    e = object.__new__(engine.B200Engine)                    # no GPU: only the host-side prompt handling is under test
+    e.gen = _GenStub()
+    e.on_overflow = kw.get("on_overflow", "error")
+    e.auto_prefix, e.max_prefix = kw.get("auto_prefix", True), 256
+    e._prefix_bytes, e.prefix_sets = b"", 0
+    e.prompt_len, e.max_new, e.max_batch = 64, 8, 8
+    return e
+
+
+HEAD = "You are a Kubernetes CLI specialist. " * 4 + "User Request: "
+
+
+def test_prepare_learns_the_prefix_when_idle_and_keeps_it_while_requests_continue_it():
+    from kubectl_b200 import engine, tokenizer
+    e = _engine()
+    prompts = [HEAD + q for q in ("list pods", "get nodes", "show services in ns1")]
+    rows = e.slots_prepare(prompts, idle=True)
+    assert all(isinstance(r, np.ndarray) and r.shape == (64,) for r in rows)
+    assert e.prefix_sets == 1 and e._prefix_bytes and HEAD.encode().startswith(e._prefix_bytes[:len(HEAD) - 16])
+    assert ("session_open",) in e.gen.calls                  # set_prefix ended the session: it is opened again
+    n_calls = len(e.gen.calls)
+    # busy engine: a prompt that continues the prefix joins, one that does not is held (None), a long one fails alone
+    rows = e.slots_prepare([HEAD + "describe pod x", "Translate: y", HEAD + "z" * 200], idle=False)
+    assert isinstance(rows[0], np.ndarray) and rows[1] is None and isinstance(rows[2], engine.PromptTooLong)
+    assert len(e.gen.calls) == n_calls                       # nothing touched the prefix while sequences depend on it
+    # the suffix is what follows the cached prefix, right-aligned in the window
+    tail = (HEAD + "describe pod x").encode()[len(e._prefix_bytes):]
+    assert bytes(rows[0][-len(tail):].astype(np.uint8)) == tail and rows[0][0] == 32
+    # idle again, but somebody still continues the prefix: it stays, the stranger keeps waiting
+    rows = e.slots_prepare([HEAD + "get pods", "Translate: y"], idle=True)
+    assert isinstance(rows[0], np.ndarray) and rows[1] is None and e.prefix_sets == 1
+    # idle and only strangers: the prefix is learned again from them (here: dropped, they share nothing page-sized)
+    rows = e.slots_prepare(["Translate: y"], idle=True)
+    assert isinstance(rows[0], np.ndarray) and rows[0][0] == tokenizer.BOS and e._prefix_bytes == b""
+
+
+def test_prepare_without_a_prefix_cache_checks_the_window():
+    from kubectl_b200 import engine, tokenizer
+    e = _engine(auto_prefix=False)
+    rows = e.slots_prepare(["kubectl get pods", "x" * 64], idle=False)
+    assert rows[0][0] == tokenizer.BOS and bytes(rows[0][-16:].astype(np.uint8)) == b"kubectl get pods"
+    assert isinstance(rows[1], engine.PromptTooLong)
+    e = _engine(auto_prefix=False, on_overflow="truncate")
+    rows = e.slots_prepare(["y" * 100], idle=True)
+    assert rows[0][0] == tokenizer.BOS and bytes(rows[0][1:].astype(np.uint8)) == b"y" * 63
