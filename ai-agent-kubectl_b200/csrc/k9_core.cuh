@@ -356,17 +356,20 @@ KX_HD bool kubectl_prefix(const uint32_t *W, int a, int b) {
     return funnel_r(w0, w1, sh) == 0x6562756bu && funnel_r(w1, w2, sh) == 0x206c7463u;   // "kube" "ctl "
 }
 
-// Returns true if the string must be redone by the general path (a byte >= 0x80 inside, or a fenced output in PARSE
+// Returns 1 if the string must be redone by the general path (a byte >= 0x80 inside, or a fenced output in PARSE
 // mode); otherwise fills r.  The byte loops (the quoting automaton for mixed quotes / backslashes, the whitespace
 // collapse) run only for the strings that need them, about one in fifteen of the synthetic mix.  (Moving those
-// strings to a second phase of the CTA, or splitting their loops, executed fewer instructions but measured slower:
-// 1.15 - 1.32 against 1.04 ms per 10 M strings.)
-template <bool PARSE>
-KX_HD bool fast_string(uint32_t *W, int lo, int hi, const uint8_t *lut, bool want_hash, uint8_t *san, Result &r) {
+// strings to a second phase of the same CTA, or splitting their loops, executed fewer instructions but measured slower:
+// 1.15 - 1.32 against 1.04 ms per 10 M strings -- seven of eight warps then wait for one.)
+// LOOPS = false: a string that needs one of the byte loops is not touched and 2 is returned (the kernel hands those to a
+// pass of their own, where every lane runs the loops, instead of letting one lane in fifteen hold its warp back).
+// Returns 0: r is filled; 1: general path; 2: byte loops needed.
+template <bool PARSE, bool LOOPS = true>
+KX_HD int fast_string(uint32_t *W, int lo, int hi, const uint8_t *lut, bool want_hash, uint8_t *san, Result &r) {
     uint8_t *B = (uint8_t *)W;
     int a, b;
     strip_ends(B, lo, hi, a, b);
-    if (PARSE && a < b && B[a] == 0x60) return true;
+    if (PARSE && a < b && B[a] == 0x60) return 1;
     const bool pfx = kubectl_prefix(W, a, b);
 
     // ---- word-at-a-time scan of [a, b) ----
@@ -391,12 +394,13 @@ KX_HD bool fast_string(uint32_t *W, int lo, int hi, const uint8_t *lut, bool wan
             step(W[w_last] & m1);
         }
     }
-    if (hibits & 0x80808080u) return true;
+    if (hibits & 0x80808080u) return 1;
     any |= any >> 16; any |= any >> 8;
     par ^= par >> 16; par ^= par >> 8;
     dbl |= dbl >> 16; dbl |= dbl >> 8;
     const bool meta = (any & B_META) || (dbl & (B_AMP | B_PIPE));
     const uint32_t qk = any & (B_SQ | B_DQ | B_BS);
+    if (!LOOPS && ((qk != 0 && qk != B_SQ && qk != B_DQ) || (dbl & B_WS) || (any & B_CTRL))) return 2;
     bool open_quote = false;
     if (qk == B_SQ || qk == B_DQ) {
         open_quote = (par & qk) != 0;                          // one kind of quote, no escapes: closed iff the count is even
@@ -430,7 +434,7 @@ KX_HD bool fast_string(uint32_t *W, int lo, int hi, const uint8_t *lut, bool wan
     r.san_len = sn;
     r.hash = want_hash ? sip_stream(W, s0, sn) : 0;
     if (san) for (int i = 0; i < sn; ++i) san[i] = B[s0 + i];
-    return false;
+    return 0;
 }
 
 }  // namespace k9

@@ -10,10 +10,11 @@
 // coalesced 16-byte loads (each HBM byte is read exactly once).  Strings are
 // handed to threads sorted by length (a counting sort in shared memory) so the
 // lanes of a warp finish together.  Each thread then runs the table-driven ASCII
-// fast path of k9_core.cuh on its string; the few strings it hands back
-// (non-ASCII, fenced output in PARSE mode, CTAs whose byte range exceeds the staging
-// buffer) are appended to a queue in global scratch memory, and a second kernel runs
-// the general code-point path over that queue, packed densely over its threads.
+// fast path of k9_core.cuh on its string.  Strings it cannot finish go to a queue in
+// global scratch memory: the ASCII strings that need a byte loop (mixed quoting,
+// whitespace to collapse) to the back of it, for pass 1b, where every lane has such a
+// loop to run; non-ASCII strings, fenced outputs in PARSE mode and CTAs whose byte range
+// exceeds the staging buffer to the front, for pass 2, the general code-point path.
 #include <atomic>
 #include "kx_common.cuh"
 #include "k9_core.cuh"
@@ -24,6 +25,9 @@ constexpr int kThreads = 256;
 constexpr int kStageBytes = 32 * 1024;
 constexpr int kStageSlack = 16;           // sip_stream may read two words past the last string
 constexpr int kGeneralThreads = 128;
+constexpr int kLoopThreads = 128;         // pass 1b: strings that need a byte loop
+constexpr int kLoopSlotWords = 65;        // per-thread staging slot: 64 words + 1 (slots start in different banks)
+constexpr int kLoopMaxLen = 228;          // longest string a slot takes: 15 alignment bytes + 228 + two words of look-ahead <= 256
 
 __device__ const k9::FastTables g_tables = k9::make_fast_tables();
 
@@ -32,9 +36,10 @@ struct __align__(16) Shared {
     int32_t soff[kThreads + 1];           // string offsets relative to the staged base
     int32_t hist[64];
     int32_t perm[kThreads];
-    int32_t slowq[kThreads];              // strings for the general pass (second kernel)
-    int32_t nslow;
-    uint32_t qbase;
+    int32_t slowq[kThreads];              // strings for the general pass
+    int32_t loopq[kThreads];              // strings for the byte-loop pass
+    int32_t nslow, nloop;
+    uint32_t qbase, qbase_loop;
 };
 
 __device__ __forceinline__ void store_result(const k9::Result &r, int64_t s, uint8_t *verdict, int64_t *hash,
@@ -65,7 +70,7 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
     const int64_t nbytes = lead + (g_end - g_beg);
     const bool staged = nbytes <= kStageBytes;             // CTA-uniform
 
-    if (tid == 0) sh.nslow = 0;
+    if (tid == 0) { sh.nslow = 0; sh.nloop = 0; }
     if (staged) {
         // ---- stage bytes (coalesced 16 B loads), tables and offsets ----
         const int nvec = (int)((nbytes + 15) >> 4);
@@ -101,11 +106,12 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
         if (tid < cnt) {
             const int i = sh.perm[tid];
             k9::Result r;
-            const bool slow = k9::fast_string<PARSE>(reinterpret_cast<uint32_t *>(stage), sh.soff[i], sh.soff[i + 1],
-                                                     sh.tab.flags, hash != nullptr,
-                                                     san ? san + g_beg + (sh.soff[i] - lead) : nullptr, r);
-            if (slow) sh.slowq[atomicAdd(&sh.nslow, 1)] = i;
-            else store_result(r, s0 + i, verdict, hash, span, san_len);
+            const int how = k9::fast_string<PARSE, false>(reinterpret_cast<uint32_t *>(stage), sh.soff[i], sh.soff[i + 1],
+                                                          sh.tab.flags, hash != nullptr,
+                                                          san ? san + g_beg + (sh.soff[i] - lead) : nullptr, r);
+            if (how == 0) store_result(r, s0 + i, verdict, hash, span, san_len);
+            else if (how == 2 && sh.soff[i + 1] - sh.soff[i] <= kLoopMaxLen) sh.loopq[atomicAdd(&sh.nloop, 1)] = i;
+            else sh.slowq[atomicAdd(&sh.nslow, 1)] = i;
         }
     } else {
         // strings too long to stage: the whole CTA goes to the general pass
@@ -113,11 +119,80 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
         if (tid < cnt) sh.slowq[atomicAdd(&sh.nslow, 1)] = tid;
     }
     __syncthreads();
-    const int nslow = sh.nslow;
-    if (nslow == 0) return;
-    if (tid == 0) sh.qbase = atomicAdd(queue, (uint32_t)nslow);
+    const int nslow = sh.nslow, nloop = sh.nloop;
+    if (nslow == 0 && nloop == 0) return;
+    if (tid == 0) {
+        if (nslow) sh.qbase = atomicAdd(queue, (uint32_t)nslow);
+        if (nloop) sh.qbase_loop = atomicAdd(queue + 1, (uint32_t)nloop);
+    }
     __syncthreads();
+    // one array, two queues: the general pass's entries grow from the front, the byte-loop pass's from the back
+    // (a string is in at most one of them, so together they never exceed n entries)
     for (int q = tid; q < nslow; q += kThreads) queue[2 + sh.qbase + q] = (uint32_t)(s0 + sh.slowq[q]);
+    for (int q = tid; q < nloop; q += kThreads) queue[2 + n - 1 - (sh.qbase_loop + q)] = (uint32_t)(s0 + sh.loopq[q]);
+}
+
+// Pass 1b: the ASCII strings that need one of fast_string's byte loops -- the quoting automaton (mixed quotes or a
+// backslash) or the whitespace collapse; about one string in fifteen of the synthetic mix.  Inside pass 1 such a string
+// made its whole warp walk the loops with one or two lanes active (19 of 32 lanes active on average, a third of the
+// warp's instructions); here every lane has one.  Each thread copies its string (at most kLoopMaxLen bytes, a few L2
+// hits: pass 1 has just read it) into a private shared-memory slot and runs the same fast_string with the loops enabled.
+template <bool PARSE>
+__global__ void __launch_bounds__(kLoopThreads)
+k9_validate_hash_loops(const uint8_t *__restrict__ data, const int64_t *__restrict__ off, int64_t n,
+                       uint8_t *__restrict__ verdict, int64_t *__restrict__ hash, int32_t *__restrict__ span,
+                       uint8_t *__restrict__ san, int32_t *__restrict__ san_len, const uint32_t *__restrict__ queue) {
+    __shared__ uint32_t slots[kLoopThreads * kLoopSlotWords];
+    __shared__ uint8_t lut[256];
+    __shared__ int32_t hist[32];
+    __shared__ uint32_t order[kLoopThreads];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 256; i += kLoopThreads) lut[i] = g_tables.flags[i];
+    const uint32_t count = queue[1];
+    uint32_t *slot = slots + tid * kLoopSlotWords;
+    for (uint32_t base = blockIdx.x * kLoopThreads; base < count; base += gridDim.x * kLoopThreads) {
+        // the CTA's 128 queue entries, handed to its threads by length (counting sort on len / 8): both loops are
+        // O(length), and the queue arrives in the order pass 1's CTAs finished
+        const int cnt = (int)min((uint32_t)kLoopThreads, count - base);
+        if (tid < 32) hist[tid] = 0;
+        __syncthreads();
+        uint32_t sidx = 0;
+        int bucket = 0, rank = 0;
+        if (tid < cnt) {
+            sidx = queue[2 + n - 1 - (base + tid)];
+            bucket = (int)min((off[sidx + 1] - off[sidx]) >> 3, (int64_t)31);
+            rank = atomicAdd(&hist[bucket], 1);
+        }
+        __syncthreads();
+        if (tid < 32) {
+            const int c = hist[tid];
+            int incl = c;
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (tid >= d) incl += t;
+            }
+            hist[tid] = incl - c;
+        }
+        __syncthreads();
+        if (tid < cnt) order[hist[bucket] + rank] = sidx;
+        __syncthreads();
+        if (tid < cnt) {
+            const int64_t s = order[tid];
+            const int64_t o0 = off[s], o1 = off[s + 1];
+            const uintptr_t sa = (uintptr_t)(data + o0);
+            const uint4 *src = (const uint4 *)(sa & ~(uintptr_t)15);
+            const int lo = (int)(sa & 15), hi = lo + (int)(o1 - o0);
+            const int nvec = (hi + 15) >> 4;
+            for (int v = 0; v < nvec; ++v) {
+                const uint4 x = __ldg(src + v);
+                slot[4 * v] = x.x; slot[4 * v + 1] = x.y; slot[4 * v + 2] = x.z; slot[4 * v + 3] = x.w;
+            }
+            k9::Result r;
+            k9::fast_string<PARSE, true>(slot, lo, hi, lut, hash != nullptr, san ? san + o0 : nullptr, r);
+            store_result(r, s, verdict, hash, span, san_len);
+        }
+        __syncthreads();                                       // order / hist are reused by the next batch
+    }
 }
 
 // Pass 2: general code-point path (k9::process_string) over the queued strings, read from global memory, one
@@ -125,7 +200,8 @@ k9_validate_hash_fast(const uint8_t *__restrict__ data, const int64_t *__restric
 // (counting sort on len / 8, as pass 1 does): the queue arrives in no particular order and the strings are
 // 12 - 200 bytes long, so without the sort a warp runs as long as its longest string with a third of its lanes
 // active (8.9 of 32 measured); adjacent threads now hold strings of similar length.
-constexpr int kGeneralPer = 2;                                  // strings per thread and batch
+constexpr int kGeneralPer = 2;                                  // strings per thread and batch (64-thread CTAs with one string
+                                                                // per thread: 0.93 instead of 0.85 ms per 10 M strings)
 template <bool PARSE>
 __global__ void __launch_bounds__(kGeneralThreads)
 k9_validate_hash_general(const uint8_t *__restrict__ data, const int64_t *__restrict__ off,
@@ -200,14 +276,17 @@ int launch_passes(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t gbatch = kGeneralThreads * kGeneralPer;
     const unsigned gblocks = (unsigned)min((int64_t)sms * 32, (n + gbatch - 1) / gbatch);
+    const unsigned lblocks = (unsigned)min((int64_t)sms * 16, (n + kLoopThreads - 1) / kLoopThreads);
     if (flags & KX_FLAG_PARSE) {
         k9_validate_hash_fast<true><<<blocks, kThreads, kSmemBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+        k9_validate_hash_loops<true><<<lblocks, kLoopThreads, 0, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
         k9_validate_hash_general<true><<<gblocks, kGeneralThreads, 0, st>>>(d_data, d_off, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
     } else {
         k9_validate_hash_fast<false><<<blocks, kThreads, kSmemBytes, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
+        k9_validate_hash_loops<false><<<lblocks, kLoopThreads, 0, st>>>(d_data, d_off, n, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
         k9_validate_hash_general<false><<<gblocks, kGeneralThreads, 0, st>>>(d_data, d_off, d_verdict, d_hash, d_span, d_san, d_san_len, queue);
     }
-    kx::count_launch(2);
+    kx::count_launch(3);
     KX_CUDA(cudaGetLastError());
     return KX_OK;
 }
