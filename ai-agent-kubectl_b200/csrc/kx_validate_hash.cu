@@ -265,7 +265,7 @@ k9_validate_hash_general(const uint8_t *__restrict__ data, const int64_t *__rest
 constexpr int kSmemBytes = kStageBytes + kStageSlack + (int)sizeof(Shared);
 constexpr int64_t kMaxStringsPerLaunch = 1ll << 31;   // queue entries are uint32 string indices
 
-// Both passes for n strings whose offsets start at `off`; `queue` holds 2 + n words.
+// All passes for n strings whose offsets start at `off`; `queue` holds 2 + n words.
 int launch_passes(const uint8_t *d_data, const int64_t *d_off, int64_t n, uint32_t flags, uint8_t *d_verdict,
                   int64_t *d_hash, int32_t *d_span, uint8_t *d_san, int32_t *d_san_len, uint32_t *queue,
                   cudaStream_t st) {
@@ -317,7 +317,7 @@ extern "C" int kx_validate_hash(const uint8_t *d_data, const int64_t *d_off, int
 }
 
 // ---------------------------------------------------------------------------
-// kx_validate_hash_noalloc: the same two passes, with the hand-over queue in a
+// kx_validate_hash_noalloc: the same passes, with the hand-over queue in a
 // fixed array that is part of the loaded module instead of cudaMalloc'ed scratch.
 //
 // Who needs this: a host process that cannot (or must not) allocate device memory
